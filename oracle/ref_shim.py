@@ -1,0 +1,143 @@
+"""TEST INFRASTRUCTURE — loads the reference's own hot-path files UNMODIFIED.
+
+Runs ``/root/reference/pyscf/mpcc/dfrmpcc_lowlevel.py`` and
+``/root/reference/pyscf/lib/diis.py`` exactly as written by installing a tiny
+fake ``pyscf`` / ``pyscf.lib`` package in ``sys.modules`` (real PySCF cannot be
+imported in this image: no h5py, no compiled ``libnp_helper``).
+
+``/root/reference`` exists only in the build container, never on the GPU box:
+only ``tests/golden/generate_golden.py`` (run here, output committed) and the
+``not gpu`` tests that re-validate the oracle (skipped when the tree is absent)
+may call :func:`load_reference`. Nothing under ``pyscf_mpcc_b200/`` imports this.
+
+The fake helpers restate:
+  * ``lib.pack_tril``   — ``pyscf/lib/numpy_helper.py:256-294`` + ``np_helper/pack_tril.c:99-107``
+  * ``lib.unpack_tril`` — ``numpy_helper.py:297-358`` + ``pack_tril.c:24-37,58-69`` (symmetric fill)
+  * ``lib.direct_sum``  — ``numpy_helper.py:1060-1127`` (only the two strings MPCC_LL uses)
+  * ``lib.StreamObject``— ``pyscf/lib/misc.py:578-612``
+"""
+from __future__ import annotations
+
+import importlib.util
+import os
+import sys
+import types
+
+import numpy as np
+
+REFERENCE_ROOT = os.environ.get("MPCC_REFERENCE_ROOT", "/root/reference")
+
+
+def reference_available() -> bool:
+    return os.path.isfile(os.path.join(REFERENCE_ROOT, "pyscf", "mpcc", "dfrmpcc_lowlevel.py"))
+
+
+def _tril_pack(mat, axis=-1, out=None):
+    mat = np.asarray(mat)
+    n = mat.shape[0]
+    dst = np.ndarray(n * (n + 1) // 2, mat.dtype, buffer=out)
+    r, c = np.tril_indices(n)
+    dst[:] = mat[r, c]
+    return dst
+
+
+def _tril_unpack(tril, filltriu=1, axis=-1, out=None):
+    tril = np.asarray(tril)
+    if tril.ndim == 1:
+        n = int(np.sqrt(2 * tril.size))
+        full = np.zeros((n, n), tril.dtype)
+        r, c = np.tril_indices(n)
+        full[c, r] = tril
+        full[r, c] = tril
+        return full
+    cnt, npair = tril.shape
+    n = int(np.sqrt(2 * npair))
+    full = np.zeros((cnt, n, n), tril.dtype)
+    r, c = np.tril_indices(n)
+    full[:, c, r] = tril
+    full[:, r, c] = tril
+    return full
+
+
+def _direct_sum(spec, *ops):
+    if spec == "a-i->ia":
+        ev, eo = ops
+        return np.ascontiguousarray((np.asarray(ev)[:, None] - np.asarray(eo)[None, :]).T)
+    if spec == "-ia-jb->aibj":
+        x, y = ops
+        four = -x[:, :, None, None] - y[None, None, :, :]        # [i,a,j,b]
+        return np.einsum("iajb->aibj", four)
+    raise NotImplementedError(spec)
+
+
+class _MemFile(dict):
+    """Stand-in for ``misc.H5TmpFile`` (diis.py:123-139 spills vectors >= 1e7 doubles)."""
+
+    def __init__(self, *a, **k):
+        super().__init__()
+
+    def flush(self):
+        pass
+
+    def create_dataset(self, key, shape, dtype):
+        self[key] = np.empty(shape, dtype)
+        return self[key]
+
+
+_loaded = None
+
+
+def load_reference():
+    """Return (lowlevel_module, diis_module) executed from the reference tree."""
+    global _loaded
+    if _loaded is not None:
+        return _loaded
+    if not reference_available():
+        raise FileNotFoundError(f"reference tree not found under {REFERENCE_ROOT}")
+    os.environ["PYTHONBREAKPOINT"] = "0"       # kernel() ends in breakpoint() (dfrmpcc_lowlevel.py:98)
+    saved = {k: v for k, v in sys.modules.items() if k == "pyscf" or k.startswith("pyscf.")}
+
+    def mod(name):
+        m = types.ModuleType(name)
+        sys.modules[name] = m
+        return m
+
+    pyscf = mod("pyscf"); pyscf.__path__ = []
+    pyscf.__config__ = mod("pyscf.__config__")
+    lib = mod("pyscf.lib"); lib.__path__ = []; pyscf.lib = lib
+    logger = mod("pyscf.lib.logger"); lib.logger = logger
+    logger.INFO = 4
+    logger.debug = logger.debug1 = logger.warn = lambda *a, **k: None
+    misc = mod("pyscf.lib.misc"); lib.misc = misc
+
+    class StreamObject:
+        stdout = sys.stdout
+        verbose = 0
+
+    misc.StreamObject = StreamObject
+    misc.prange = lambda lo, hi, step: ((p, min(p + step, hi)) for p in range(lo, hi, step))
+    misc.H5TmpFile = _MemFile
+    misc.to_gpu = None
+    nh = mod("pyscf.lib.numpy_helper"); lib.numpy_helper = nh
+    for m in (nh, lib):
+        m.pack_tril, m.unpack_tril, m.direct_sum = _tril_pack, _tril_unpack, _direct_sum
+        m.einsum = lambda s, *t, **k: np.einsum(s, *t, optimize=True)
+        m.SYMMETRIC, m.HERMITIAN = 3, 1
+    lib.StreamObject = StreamObject
+
+    def run(name, rel):
+        spec = importlib.util.spec_from_file_location(name, os.path.join(REFERENCE_ROOT, "pyscf", rel))
+        m = importlib.util.module_from_spec(spec)
+        sys.modules[name] = m
+        spec.loader.exec_module(m)
+        return m
+
+    diis = run("pyscf.lib.diis", "lib/diis.py")
+    lib.diis = diis
+    lowlevel = run("pyscf.mpcc.dfrmpcc_lowlevel", "mpcc/dfrmpcc_lowlevel.py")
+    # leave the fake package installed only under private aliases
+    for k in [k for k in sys.modules if k == "pyscf" or k.startswith("pyscf.")]:
+        sys.modules["_mpcc_refshim_" + k] = sys.modules.pop(k)
+    sys.modules.update(saved)
+    _loaded = (lowlevel, diis)
+    return _loaded
