@@ -1,0 +1,111 @@
+/* libmpcc_b200 — C ABI of the B200 (sm_100a) DF-MPCC low-level iteration.
+ *
+ * Drop-in boundary for the hot path of FabianFaulstich/pyscf_mpcc
+ * (pyscf/mpcc/dfrmpcc_lowlevel.py::MPCC_LL). The reference has no native code
+ * on this path besides lib.pack_tril/unpack_tril (ctypes -> NPdpack_tril_2d /
+ * NPdunpack_tril_2d, pyscf/lib/numpy_helper.py:286-289,355-357); it follows the
+ * same calling convention — plain pointers and integer sizes, the caller owns
+ * every tensor — with two deliberate differences: every entry point returns an
+ * int status (0 = ok; CUDA can fail) and an opaque context owns launch state.
+ *
+ * Pointer arguments named *_dev are device pointers (the Python host owns them
+ * through torch tensors); *_host are host pointers. All arrays are C-contiguous
+ * float64. Calls are asynchronous on the context's stream unless stated.
+ *
+ * Index names: o = nocc, v = nvir, L = naux, nov = o*v. A context works on the
+ * virtual-index slab a in [a_begin, a_end) (whole range on one GPU).
+ */
+#ifndef MPCC_B200_H
+#define MPCC_B200_H
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct mpccb_ctx mpccb_ctx;
+
+/* ---- lifetime -------------------------------------------------------------------- */
+/* replaces the size bookkeeping of MPCC_LL.__init__ (dfrmpcc_lowlevel.py:23-31) */
+int mpccb_create(mpccb_ctx** out, int nocc, int nvir, int naux, int a_begin, int a_end, int device);
+void mpccb_destroy(mpccb_ctx* ctx);
+const char* mpccb_last_error(const mpccb_ctx* ctx);
+const char* mpccb_version(void);
+int mpccb_set_stream(mpccb_ctx* ctx, void* cuda_stream);
+int mpccb_synchronize(mpccb_ctx* ctx);
+
+/* scratch: the caller allocates `mpccb_workspace_bytes` bytes of device memory and binds it */
+size_t mpccb_workspace_bytes(const mpccb_ctx* ctx);
+int mpccb_bind_workspace(mpccb_ctx* ctx, void* ws_dev, size_t bytes);
+
+/* MO-basis three-index tensors and Fock blocks, the attributes MPCC_LL keeps after
+ * compute_three_center_ints (dfrmpcc_lowlevel.py:46-69, :35-42):
+ * Loo (L,o,o), Lov (L,o,v), Lvv (L,v,v), foo (o,o), fvv (v,v), eps_o (o), eps_v (v).
+ * Builds the (L,v,o) transpose of Lov in the workspace (the reference's unused `Lvo`). */
+int mpccb_bind_integrals(mpccb_ctx* ctx, const double* Loo_dev, const double* Lov_dev,
+                         const double* Lvv_dev, const double* foo_dev, const double* fvv_dev,
+                         const double* eps_o_dev, const double* eps_v_dev);
+/* t2 buffer in [a - a_begin, b, i, j] order: (a_end-a_begin)*v*o*o doubles */
+int mpccb_bind_t2(mpccb_ctx* ctx, double* t2_abij_dev);
+
+/* ---- one residual evaluation: MPCC_LL.updated_amps (dfrmpcc_lowlevel.py:103-152) --- */
+/* phase 1, :119-133 — T1 dressing, singles intermediates, Fov (rank-replicated work) */
+int mpccb_dress(mpccb_ctx* ctx, const double* t1_dev);
+/* phase 2, :135-147 — eris/t2 (fused), Yvo, doubles->singles, energy, for the local slab.
+ * Writes the slab's partial sums to red_dev[0..nov) = Omega part [a,i], red_dev[nov] = dE part;
+ * with several ranks the caller all-reduces red_dev (nov+1 doubles) before phase 3. */
+int mpccb_doubles(mpccb_ctx* ctx, double* red_dev);
+/* phase 3, :128-131,:149-151 — assemble Omega, t1_new = -Omega^T/eia, scal_dev = {res^2, dE} */
+int mpccb_finish(mpccb_ctx* ctx, const double* red_dev, double* t1_new_dev, double* scal_dev);
+/* all three phases with HOST buffers and a final synchronize (single rank):
+ * t1 (o,v) in, t1_new (o,v), res and dE out — the reference call with numpy arrays. */
+int mpccb_updated_amps_host(mpccb_ctx* ctx, const double* t1_host, double* t1_new_host,
+                            double* res_host, double* dE_host);
+
+/* ---- amplitude <-> vector layouts (dfrmpcc_lowlevel.py:162-176; NPdpack_tril /
+ *      NPdunpack_tril + NPdsymm_triu, pyscf/lib/np_helper/pack_tril.c:24-37,58-69,99-107) - */
+/* (v,o,v,o) view of the bound t2 slab, as updated_amps returns it: out[(a-a_begin),i,b,j] */
+int mpccb_t2_to_aibj(mpccb_ctx* ctx, double* out_dev);
+/* lower-triangle rows [a_begin*o, a_end*o) of the t2 buffer read as an (nov,nov) matrix */
+int mpccb_pack_tril_rows(mpccb_ctx* ctx, double* seg_dev);
+/* packed (nov(nov+1)/2) -> symmetric (nov,nov) -> (o,v,o,v) -> transpose(0,2,1,3): out (o,o,v,v) */
+int mpccb_unpack_oovv(mpccb_ctx* ctx, const double* packed_dev, double* out_dev);
+
+/* ---- DIIS vector algebra: lib.diis.DIIS.push_vec / update / extrapolate
+ *      (pyscf/lib/diis.py:148-185, 221-231, 268-275). The 7x7 system is solved by the
+ *      Python host with the same SciPy/NumPy calls as diis.py:251-265. ------------------ */
+/* x_slot = [t1_new | packed local rows of the bound t2]; unless first_call:
+ * e_slot = x_slot - xprev and dots_dev[k] = e_slot . e_k for k < nd (e_list[slot] is ignored:
+ * e_slot itself is used). count_t1 = 0 leaves the (replicated) t1 part out of the dots.
+ * first_call != 0: only x_slot is written (it is the DIIS `xprev`). */
+int mpccb_diis_push(mpccb_ctx* ctx, const double* t1_new_dev, const double* xprev_dev,
+                    double* x_slot_dev, double* e_slot_dev, const double* const* e_list_dev,
+                    int nd, int slot, int first_call, int count_t1, double* dots_dev);
+/* xnew = sum_{k<nd} coeff[k] * x_list[k]  (n doubles each) */
+int mpccb_diis_combine(mpccb_ctx* ctx, const double* const* x_list_dev, const double* coeff_host,
+                       int nd, double* xnew_dev, long long n);
+
+/* ---- introspection for tests and profiling -------------------------------------------- */
+/* named scratch tensor (e.g. "JK", "Y", "Xoo", "Fvo"); see DESIGN.md for layouts */
+int mpccb_get_buffer(mpccb_ctx* ctx, const char* name, double** ptr_dev, long long* count);
+int mpccb_copy_to_host(mpccb_ctx* ctx, const double* src_dev, double* dst_host, long long count);
+int mpccb_copy_to_device(mpccb_ctx* ctx, const double* src_host, double* dst_dev, long long count);
+/* number of kernel launches issued by this context so far */
+long long mpccb_launch_count(const mpccb_ctx* ctx);
+/* per-stage device timing (CUDA events on the context's stream), enabled by option "profile":
+ * stage names via mpccb_profile_stage_name(0..mpccb_profile_stages()-1); mpccb_profile_read
+ * synchronises and returns summed milliseconds + counts per stage since the previous read */
+int mpccb_profile_stages(void);
+const char* mpccb_profile_stage_name(int stage);
+int mpccb_profile_read(mpccb_ctx* ctx, double* ms_out, long long* count_out);
+/* option by name: "tma" (0/1 use the TMA-fed kernels when shapes allow; default 1),
+ * "profile" (0/1 record stage timings; default 0) */
+int mpccb_set_option(mpccb_ctx* ctx, const char* name, long long value);
+/* standalone C[m,n] = sum_k A[m,k] B[n,k] through the generic DMMA kernel (row-major, test hook) */
+int mpccb_gemm_nt(mpccb_ctx* ctx, const double* A_dev, const double* B_dev, double* C_dev,
+                  int M, int N, int K);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MPCC_B200_H */

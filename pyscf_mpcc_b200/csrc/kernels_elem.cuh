@@ -1,0 +1,319 @@
+// Memory-bound kernels of the DF-MPCC iteration: layout changes, the fused
+// dressing finalisation, reductions (deterministic: fixed trees, no atomics),
+// the T1 update and the DIIS vector algebra. All are HBM-bandwidth bound; they
+// are written for coalesced 8-byte (or wider) accesses with lanes along the
+// unit-stride index and warp-shuffle reductions.
+#pragma once
+#include "common.cuh"
+
+namespace mpccb {
+
+// out[b][c][r] = in[b][r][c]      (Lov -> Lvo, t1 -> t1T)
+__global__ void __launch_bounds__(256)
+k_transpose_batched(const double* __restrict__ in, double* __restrict__ out, int R, int C) {
+  __shared__ double tile[32][33];
+  const i64 boff = (i64)blockIdx.z * R * C;
+  const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+  for (int dy = threadIdx.y; dy < 32; dy += 8) {
+    const int r = r0 + dy, c = c0 + threadIdx.x;
+    if (r < R && c < C) tile[dy][threadIdx.x] = in[boff + (i64)r * C + c];
+  }
+  __syncthreads();
+  for (int dy = threadIdx.y; dy < 32; dy += 8) {
+    const int c = c0 + dy, r = r0 + threadIdx.x;
+    if (r < R && c < C) out[boff + (i64)c * R + r] = tile[threadIdx.x][dy];
+  }
+}
+
+// X[L] = sum_i Xoo[L,i,i]   ( == einsum("Lia,ia->L", Lov, t1), reference :121 )
+__global__ void __launch_bounds__(128)
+k_trace(const double* __restrict__ Xoo, double* __restrict__ X, int L, int o) {
+  const int l = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (l >= L) return;
+  const int lane = threadIdx.x & 31;
+  double s = 0.0;
+  for (int i = lane; i < o; i += 32) s += Xoo[((i64)l * o + i) * o + i];
+  s = warp_sum(s);
+  if (lane == 0) X[l] = s;
+}
+
+// Fused end of the T1 dressing (reference :124, :126-127 integrand, :146).
+// Inputs, all [L][i][a]:  Xov = (Lvv.t1)^T, Lov, JT = Joo.t1, XT = Xoo.t1
+//   J  = Xov + Lov - JT                      -> JK [(a,i)][ldk]   (K-major for the eris GEMM)
+//   e1 = XT + X[L]*t1[i,a] + J               -> E1K[(a,i)][ldk]
+//   W  = XT - Xov                            -> Wov[L][i][a]
+// grid (ceil(v/32), ceil(L/32), o), block (32, 8)
+__global__ void __launch_bounds__(256)
+k_dress_finalize(const double* __restrict__ Xov, const double* __restrict__ Lov,
+                 const double* __restrict__ JT, const double* __restrict__ XT,
+                 const double* __restrict__ X, const double* __restrict__ t1,
+                 double* __restrict__ JK, double* __restrict__ E1K, double* __restrict__ Wov,
+                 int L, int o, int v, int ldk) {
+  __shared__ double tj[32][33];
+  __shared__ double te[32][33];
+  const int i = blockIdx.z;
+  const int a0 = blockIdx.x * 32, l0 = blockIdx.y * 32;
+  const int a = a0 + threadIdx.x;
+  const double t1ia = (a < v) ? t1[(i64)i * v + a] : 0.0;
+  for (int dy = threadIdx.y; dy < 32; dy += 8) {
+    const int l = l0 + dy;
+    if (l < L && a < v) {
+      const i64 off = ((i64)l * o + i) * v + a;
+      const double xov = Xov[off], xt = XT[off];
+      const double j = xov + Lov[off] - JT[off];
+      Wov[off] = xt - xov;
+      tj[dy][threadIdx.x] = j;
+      te[dy][threadIdx.x] = xt + X[l] * t1ia + j;
+    }
+  }
+  __syncthreads();
+  for (int dy = threadIdx.y; dy < 32; dy += 8) {
+    const int aa = a0 + dy, l = l0 + threadIdx.x;
+    if (aa < v && l < L) {
+      const i64 off = ((i64)aa * o + i) * ldk + l;
+      JK[off] = tj[threadIdx.x][dy];
+      E1K[off] = te[threadIdx.x][dy];
+    }
+  }
+}
+
+// y[r] = sum_k M[r*ld + k] * x[k]; one warp per row
+__global__ void __launch_bounds__(256)
+k_gemv_rows(const double* __restrict__ M, const double* __restrict__ x, double* __restrict__ y,
+            int rows, int K, i64 ld) {
+  const int r = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (r >= rows) return;
+  const int lane = threadIdx.x & 31;
+  const double* row = M + (i64)r * ld;
+  double s = 0.0;
+  for (int k = lane; k < K; k += 32) s += row[k] * x[k];
+  s = warp_sum(s);
+  if (lane == 0) y[r] = s;
+}
+
+// dst[i] = beta*dst[i] + alpha * sum_s P[s*stride + i]   (split-K / tile partial reduction, fixed order)
+__global__ void __launch_bounds__(256)
+k_reduce_splits(double* __restrict__ dst, const double* __restrict__ P, int nsplit, i64 n, i64 stride,
+                double alpha, double beta) {
+  const i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  double s = 0.0;
+  for (int k = 0; k < nsplit; ++k) s += P[(i64)k * stride + i];
+  dst[i] = (beta == 0.0 ? 0.0 : beta * dst[i]) + alpha * s;
+}
+
+// Fvo[b][j] = w[b*o + j] - F2[b][j]        (reference :133, stored transposed)
+__global__ void __launch_bounds__(256)
+k_make_fvo(const double* __restrict__ w, const double* __restrict__ F2, double* __restrict__ Fvo, i64 n) {
+  const i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) Fvo[i] = w[i] - F2[i];
+}
+
+// OmLoc[a][i] += sum_j t1[j][a] * Z[j][i]     (second half of Jvv.Yvo, reference :141-142)
+__global__ void __launch_bounds__(256)
+k_add_t1T_Z(double* __restrict__ Om, const double* __restrict__ t1, const double* __restrict__ Z,
+            int o, int v) {
+  const i64 idx = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (i64)o * v) return;
+  const int a = (int)(idx / o), i = (int)(idx % o);
+  double s = 0.0;
+  for (int j = 0; j < o; ++j) s += t1[(i64)j * v + a] * Z[(i64)j * o + i];
+  Om[idx] += s;
+}
+
+// partial[block] = sum over a grid-stride range of x[r*ldx + k]*y[r*ldy + k], rows r in [0,rows), k in [0,K)
+__global__ void __launch_bounds__(256)
+k_dot_rows_partial(const double* __restrict__ x, const double* __restrict__ y, double* __restrict__ partial,
+                   int rows, int K, i64 ldx, i64 ldy) {
+  __shared__ double scratch[32];
+  double s = 0.0;
+  const int wpb = blockDim.x >> 5, lane = threadIdx.x & 31;
+  for (int r = blockIdx.x * wpb + (threadIdx.x >> 5); r < rows; r += gridDim.x * wpb) {
+    const double* xr = x + (i64)r * ldx;
+    const double* yr = y + (i64)r * ldy;
+    for (int k = lane; k < K; k += 32) s += xr[k] * yr[k];
+  }
+  s = block_sum(s, scratch);
+  if (threadIdx.x == 0) partial[blockIdx.x] = s;
+}
+
+// out[q] = sum_b partial[b*nq + q]   (single block; fixed order)
+__global__ void __launch_bounds__(256)
+k_final_sums(const double* __restrict__ partial, double* __restrict__ out, int nblocks, int nq) {
+  __shared__ double scratch[32];
+  for (int q = 0; q < nq; ++q) {
+    double s = 0.0;
+    for (int b = threadIdx.x; b < nblocks; b += blockDim.x) s += partial[(i64)b * nq + q];
+    s = block_sum(s, scratch);
+    if (threadIdx.x == 0) out[q] = s;
+    __syncthreads();
+  }
+}
+
+// Singles residual assembly + T1 update (reference :128-131, :149-151).
+//   Om[a,i]  = OmRep[a,i] + w[(a,i)] + OmLoc[a,i] + sum_b t1[i,b] fvv[b,a] - sum_k t1[k,a] foo[i,k]
+//   t1n[i,a] = -Om[a,i]/(ev[a]-eo[i]);  partial[block] = sum (t1[i,a] - t1n[i,a])^2
+__global__ void __launch_bounds__(256)
+k_t1_update(const double* __restrict__ OmRep, const double* __restrict__ w, const double* __restrict__ OmLoc,
+            const double* __restrict__ t1, const double* __restrict__ fvv, const double* __restrict__ foo,
+            const double* __restrict__ eo, const double* __restrict__ ev,
+            double* __restrict__ t1n, double* __restrict__ OmOut, double* __restrict__ partial, int o, int v) {
+  __shared__ double scratch[32];
+  const i64 idx = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  double r2 = 0.0;
+  if (idx < (i64)o * v) {
+    const int i = (int)(idx / v), a = (int)(idx % v);   // lanes along a: t1/t1n/fvv coalesced
+    const i64 ai = (i64)a * o + i;
+    double om = OmRep[ai] + w[ai] + OmLoc[ai];
+    double s = 0.0;
+    for (int b = 0; b < v; ++b) s += t1[(i64)i * v + b] * fvv[(i64)b * v + a];
+    om += s;
+    s = 0.0;
+    for (int k = 0; k < o; ++k) s += t1[(i64)k * v + a] * foo[(i64)i * o + k];
+    om -= s;
+    const double q = om / (ev[a] - eo[i]);
+    t1n[idx] = -q;
+    OmOut[ai] = om;
+    const double d = t1[idx] + q;
+    r2 = d * d;
+  }
+  r2 = block_sum(r2, scratch);
+  if (threadIdx.x == 0) partial[blockIdx.x] = r2;
+}
+
+// ---------------------------------------------------------------------------
+// DIIS vector algebra. The vector is x = [ t1 (nov) | rows r of the t2 buffer
+// viewed as (nov x nov), columns 0..r ] (reference dfrmpcc_lowlevel.py:162-168
+// fed the (v,o,v,o) tensor == our [a,b,i,j] buffer read row-major).
+// A rank owning rows [r0, r1) of that matrix holds the matching packed segment
+//   seg = x[nov + r0(r0+1)/2 : nov + r1(r1+1)/2].
+// ---------------------------------------------------------------------------
+struct DiisPtrs {
+  const double* e[6];
+};
+
+// Row blocks: blockIdx.x = local row (r - r0) for the t2 part, one extra block
+// (blockIdx.x == nrows) for the t1 part (skipped when t1 == nullptr).
+//   xs[...] = value;  es[...] = value - xprev[...];  dots[k] += es . e_k  (k < nd; e_slot is `es` itself)
+// partial layout: [gridDim.x][7] (slot k -> column k; column 6 unused)
+__global__ void __launch_bounds__(256)
+k_diis_push(const double* __restrict__ T, const double* __restrict__ t1new,
+            const double* __restrict__ xprev, double* __restrict__ xs, double* __restrict__ es,
+            DiisPtrs eptr, int nd, int slot, int first_call, int count_t1,
+            i64 nov, i64 r0, int nrows, double* __restrict__ partial) {
+  __shared__ double scratch[32];
+  const int blk = blockIdx.x;
+  i64 len, src_off, dst_off;
+  const double* src;
+  if (blk < nrows) {
+    const i64 r = r0 + blk;
+    len = r + 1;
+    src = T + (i64)blk * nov;          // T holds local rows only
+    src_off = 0;
+    dst_off = nov + (r * (r + 1)) / 2 - (r0 * (r0 + 1)) / 2;   // t1 part first, then local packed rows
+  } else {
+    if (t1new == nullptr) { len = 0; src = nullptr; src_off = 0; dst_off = 0; }
+    else { len = nov; src = t1new; src_off = 0; dst_off = 0; }
+  }
+  double d[6] = {0, 0, 0, 0, 0, 0};
+  for (i64 c = threadIdx.x; c < len; c += blockDim.x) {
+    const double val = src[src_off + c];
+    if (first_call) {
+      xs[dst_off + c] = val;           // becomes xprev
+    } else {
+      const double e = val - xprev[dst_off + c];
+      xs[dst_off + c] = val;
+      es[dst_off + c] = e;
+#pragma unroll
+      for (int k = 0; k < 6; ++k)
+        if (k < nd) d[k] += e * ((k == slot) ? e : eptr.e[k][dst_off + c]);
+    }
+  }
+  if (!first_call) {
+    const double wgt = (blk < nrows || count_t1) ? 1.0 : 0.0;   // replicated t1 part counted by one rank only
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+      if (k < nd) {
+        const double s = wgt * block_sum(d[k], scratch);
+        if (threadIdx.x == 0) partial[(i64)blk * 7 + k] = s;
+      }
+    }
+  }
+}
+
+// xnew[i] = sum_k c[k] * x_k[i]  (slot order, like diis.py:268-275)
+struct DiisComb {
+  const double* x[6];
+  double c[6];
+};
+__global__ void __launch_bounds__(256)
+k_diis_combine(DiisComb cb, int nd, double* __restrict__ xnew, i64 n) {
+  const i64 stride = (i64)gridDim.x * blockDim.x;
+  for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    double s = 0.0;
+#pragma unroll
+    for (int k = 0; k < 6; ++k)
+      if (k < nd) s += cb.x[k][i] * cb.c[k];
+    xnew[i] = s;
+  }
+}
+
+// t2_out[i][j][a][b] = S[(i*v + a), (j*v + b)],  S = symmetric fill of the packed lower triangle
+// (reference vector_to_amplitudes :170-176 + NPdunpack_tril/NPdsymm_triu)
+__global__ void __launch_bounds__(256)
+k_unpack_oovv(const double* __restrict__ packed, double* __restrict__ out, int o, int v) {
+  const i64 nov = (i64)o * v;
+  const i64 total = nov * nov;
+  const i64 stride = (i64)gridDim.x * blockDim.x;
+  for (i64 idx = (i64)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += stride) {
+    const int b = (int)(idx % v);
+    i64 q = idx / v;
+    const int a = (int)(q % v); q /= v;
+    const int j = (int)(q % o);
+    const int i = (int)(q / o);
+    i64 r = (i64)i * v + a, c = (i64)j * v + b;
+    if (c > r) { const i64 t = r; r = c; c = t; }
+    out[idx] = packed[r * (r + 1) / 2 + c];
+  }
+}
+
+// out[a][i][b][j] = T[a][b][i][j]   (the (v,o,v,o) tensor updated_amps returns, reference :137,:152)
+__global__ void __launch_bounds__(256)
+k_abij_to_aibj(const double* __restrict__ T, double* __restrict__ out, int o, int v, int na) {
+  const i64 total = (i64)na * v * o * o;
+  const i64 stride = (i64)gridDim.x * blockDim.x;
+  for (i64 idx = (i64)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += stride) {
+    const int j = (int)(idx % o);
+    i64 q = idx / o;
+    const int b = (int)(q % v); q /= v;
+    const int i = (int)(q % o);
+    const int a = (int)(q / o);
+    out[idx] = T[(((i64)a * v + b) * o + i) * o + j];
+  }
+}
+
+// plain row-prefix pack (amplitudes_to_vector without the DIIS bookkeeping)
+__global__ void __launch_bounds__(256)
+k_pack_rows(const double* __restrict__ T, double* __restrict__ seg, i64 nov, i64 r0) {
+  const i64 r = r0 + blockIdx.x;
+  const double* src = T + (i64)blockIdx.x * nov;
+  double* dst = seg + (r * (r + 1)) / 2 - (r0 * (r0 + 1)) / 2;
+  for (i64 c = threadIdx.x; c <= r; c += blockDim.x) dst[c] = src[c];
+}
+
+}  // namespace mpccb
+
+namespace mpccb {
+// out[q] = sum_b partial[b*ld + q] for q < nq  (single block; fixed order)
+__global__ void __launch_bounds__(256)
+k_final_sums_strided(const double* __restrict__ partial, double* __restrict__ out, int nblocks, int ld, int nq) {
+  __shared__ double scratch[32];
+  for (int q = 0; q < nq; ++q) {
+    double s = 0.0;
+    for (int b = threadIdx.x; b < nblocks; b += blockDim.x) s += partial[(i64)b * ld + q];
+    s = block_sum(s, scratch);
+    if (threadIdx.x == 0) out[q] = s;
+    __syncthreads();
+  }
+}
+}  // namespace mpccb

@@ -1,0 +1,657 @@
+// C ABI of libmpcc_b200 (see include/mpcc_b200.h). Host orchestration of one
+// DF-MPCC residual evaluation = reference MPCC_LL.updated_amps
+// (pyscf/mpcc/dfrmpcc_lowlevel.py:103-152) as a fixed sequence of DMMA GEMMs and
+// HBM-bound kernels on one stream.
+#include "../../include/mpcc_b200.h"
+#include "gemm_dmma.cuh"
+#include "kernels_elem.cuh"
+
+#include <algorithm>
+#include <climits>
+#include <cmath>
+#include <cstdarg>
+#include <cstring>
+#include <string>
+#include <vector>
+
+using namespace mpccb;
+
+namespace {
+constexpr int BIG = 1 << 30;
+constexpr int NSM = 148;
+
+// tile configurations of the generic DMMA GEMM (warps m x n, fragments m x n, A K-major?, B K-major?)
+typedef GemmCfg<2, 4, 8, 4, true, true> CfgBigKK;     // 128 x 128
+typedef GemmCfg<4, 2, 4, 4, true, true> CfgN64KK;     // 128 x 64
+typedef GemmCfg<4, 2, 4, 4, false, false> CfgN64RR;
+typedef GemmCfg<4, 2, 4, 4, true, false> CfgN64KR;
+typedef GemmCfg<4, 2, 4, 4, false, true> CfgN64RK;
+}  // namespace
+
+struct mpccb_ctx {
+  int o, v, L, device, a_begin, a_end, na, ldk;
+  i64 nov;
+  cudaStream_t stream;
+  long long launches;
+  int use_tma;
+  char err[512];
+  // bound tensors
+  const double *Loo, *Lov, *Lvv, *foo, *fvv, *eo, *ev;
+  double* T;
+  unsigned char* ws;
+  size_t ws_bytes;
+  // workspace carve-up (doubles)
+  double *Lvo, *t1, *t1T, *t1n, *Xov, *Xoo, *Joo, *X, *XT, *JT, *JK, *E1K, *Wov, *w, *F2, *Fvo, *OmP, *Y,
+      *P, *OmRep, *OmLoc, *OmTot, *Z, *scal, *red;
+  i64 P_count, OmP_count;
+  int t2_na, t2_nb, t2_tiles_m, t2_tiles_n;
+  // optional per-stage CUDA-event timing (mpccb_set_option("profile", 1))
+  int profile;
+  std::vector<cudaEvent_t>* prof_ev;   // [stage] -> start/stop pairs
+  int prof_used[16];
+};
+
+enum Stage { ST_DRESS = 0, ST_ERIS_T2, ST_YVO, ST_SINGLES_FROM_Y, ST_FINISH, ST_DIIS_PUSH, ST_DIIS_COMBINE, ST_COUNT };
+static const char* kStageNames[ST_COUNT] = {"dress", "eris_t2", "yvo", "singles_from_y", "finish", "diis_push",
+                                            "diis_combine"};
+
+namespace {
+
+int fail(mpccb_ctx* c, const char* fmt, ...) {
+  if (c) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(c->err, sizeof(c->err), fmt, ap);
+    va_end(ap);
+  }
+  return 1;
+}
+
+struct StageTimer {
+  mpccb_ctx* c;
+  int stage;
+  bool on;
+  StageTimer(mpccb_ctx* ctx, int st) : c(ctx), stage(st), on(false) {
+    if (!c->profile) return;
+    std::vector<cudaEvent_t>& v = c->prof_ev[stage];
+    const int need = c->prof_used[stage] + 2;
+    while ((int)v.size() < need) {
+      cudaEvent_t e;
+      if (cudaEventCreate(&e) != cudaSuccess) return;
+      v.push_back(e);
+    }
+    cudaEventRecord(v[c->prof_used[stage]], c->stream);
+    on = true;
+  }
+  ~StageTimer() {
+    if (!on) return;
+    cudaEventRecord(c->prof_ev[stage][c->prof_used[stage] + 1], c->stream);
+    c->prof_used[stage] += 2;
+  }
+};
+
+#define CUDA_OK(c, call)                                                                   \
+  do {                                                                                     \
+    cudaError_t e_ = (call);                                                               \
+    if (e_ != cudaSuccess)                                                                 \
+      return fail(c, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+  } while (0)
+
+#define LAUNCH_OK(c, what)                                                                 \
+  do {                                                                                     \
+    (c)->launches++;                                                                       \
+    cudaError_t e_ = cudaGetLastError();                                                   \
+    if (e_ != cudaSuccess) return fail(c, "launch of %s failed: %s", what, cudaGetErrorString(e_)); \
+  } while (0)
+
+inline i64 align_up(i64 x, i64 a) { return (x + a - 1) / a * a; }
+inline int cdiv(i64 a, i64 b) { return (int)((a + b - 1) / b); }
+
+Operand flat_operand(const double* base, int rows, i64 row_stride, i64 k_stride) {
+  Operand op;
+  op.base = base; op.rows = rows;
+  op.r_hi = 0; op.r_lo = row_stride; op.rdiv = BIG;
+  op.k_hi = 0; op.k_lo = k_stride; op.kdiv = BIG;
+  return op;
+}
+
+Output flat_output(double* base, i64 m_stride, i64 n_stride) {
+  Output c;
+  c.base = base; c.base2 = nullptr; c.aux = nullptr;
+  c.m_hi = 0; c.m_lo = m_stride; c.mdiv = BIG;
+  c.n_hi = 0; c.n_lo = n_stride; c.ndiv = BIG;
+  c.split_stride = 0;
+  return c;
+}
+
+// number of K splits so that a small-output GEMM still fills the machine
+int choose_splits(int tiles, int K) {
+  if (tiles >= NSM) return 1;
+  int s = cdiv(2 * NSM, tiles);
+  const int max_s = K / 64 > 0 ? K / 64 : 1;
+  if (s > max_s) s = max_s;
+  return s < 1 ? 1 : s;
+}
+
+template <class Cfg>
+int launch_gemm(mpccb_ctx* c, const char* what, const Operand& A, const Operand& B, Output C,
+                int M, int N, int K, int splits, double* partial) {
+  GemmDims d;
+  d.M = M; d.N = N; d.K = K;
+  d.tm_eff = Cfg::TM; d.tn_eff = Cfg::TN;
+  d.tiles_m = cdiv(M, Cfg::TM); d.tiles_n = cdiv(N, Cfg::TN);
+  d.kchunk = (int)align_up(cdiv(K, splits), TK);
+  splits = cdiv(K, d.kchunk);
+  if (splits > 1) {
+    // partial[s][m][n] row-major, reduced by the caller
+    C = flat_output(partial, N, 1);
+    C.split_stride = (i64)M * N;
+  }
+  static bool attr_done = false;
+  if (!attr_done) {
+    CUDA_OK(c, cudaFuncSetAttribute(gemm_store_kernel<Cfg>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)Cfg::MAIN_SMEM));
+    attr_done = true;
+  }
+  dim3 grid(d.tiles_m * d.tiles_n, 1, splits);
+  gemm_store_kernel<Cfg><<<grid, Cfg::NTH, Cfg::MAIN_SMEM, c->stream>>>(A, B, C, d);
+  LAUNCH_OK(c, what);
+  return 0;
+}
+
+int reduce_splits(mpccb_ctx* c, double* dst, const double* P, int nsplit, i64 n, i64 stride,
+                  double alpha, double beta) {
+  k_reduce_splits<<<cdiv(n, 256), 256, 0, c->stream>>>(dst, P, nsplit, n, stride, alpha, beta);
+  LAUNCH_OK(c, "k_reduce_splits");
+  return 0;
+}
+
+// split-K GEMM with tiny M x N: partials then a fixed-order reduction into dst (row-major M x N)
+template <class Cfg>
+int splitk_gemm(mpccb_ctx* c, const char* what, const Operand& A, const Operand& B, double* dst,
+                int M, int N, int K, double alpha, double beta) {
+  const int tiles = cdiv(M, Cfg::TM) * cdiv(N, Cfg::TN);
+  int splits = choose_splits(tiles, K);
+  const int kchunk = (int)align_up(cdiv(K, splits), TK);
+  splits = cdiv(K, kchunk);
+  if ((i64)splits * M * N > c->P_count) return fail(c, "%s: split-K scratch too small", what);
+  if (splits == 1) {
+    // still go through the partial buffer so alpha/beta apply uniformly
+    Output C = flat_output(c->P, N, 1);
+    if (launch_gemm<Cfg>(c, what, A, B, C, M, N, K, 1, c->P)) return 1;
+  } else {
+    Output C = flat_output(c->P, N, 1);
+    if (launch_gemm<Cfg>(c, what, A, B, C, M, N, K, splits, c->P)) return 1;
+  }
+  return reduce_splits(c, dst, c->P, splits, (i64)M * N, (i64)M * N, alpha, beta);
+}
+
+i64 splitk_scratch(int M, int N, int K, int TM, int TN) {
+  const int tiles = cdiv(M, TM) * cdiv(N, TN);
+  const int splits = choose_splits(tiles, K);
+  return (i64)(splits + 1) * M * N;
+}
+
+}  // namespace
+
+// ===========================================================================
+// lifetime / binding
+// ===========================================================================
+namespace {
+
+struct Carve {
+  unsigned char* base;
+  i64 off;
+  double* take(i64 count) {
+    double* p = base ? reinterpret_cast<double*>(base + off) : nullptr;
+    off += align_up(count * (i64)sizeof(double), 256);
+    return p;
+  }
+};
+
+// lays the scratch tensors out in the workspace; with base == nullptr only sizes it
+i64 carve_workspace(mpccb_ctx* c, unsigned char* base) {
+  const i64 o = c->o, v = c->v, L = c->L, nov = c->nov, ldk = c->ldk, na = c->na;
+  Carve w{base, 0};
+  c->Lvo = w.take(L * v * o);
+  c->t1 = w.take(nov);
+  c->t1T = w.take(nov);
+  c->t1n = w.take(nov);
+  c->Xov = w.take(L * o * v);
+  c->Xoo = w.take(2 * L * o * o);           // [Xoo | Joo] adjacent: one GEMM dresses both with t1
+  c->Joo = c->Xoo ? c->Xoo + L * o * o : nullptr;
+  c->X = w.take(L);
+  c->XT = w.take(2 * L * o * v);            // [XT | JT]
+  c->JT = c->XT ? c->XT + L * o * v : nullptr;
+  c->JK = w.take(nov * ldk);
+  c->E1K = w.take(nov * ldk);
+  c->Wov = w.take(L * o * v);
+  c->w = w.take(nov);
+  c->F2 = w.take(nov);
+  c->Fvo = w.take(nov);
+  c->OmP_count = (i64)c->t2_tiles_n * na * o;
+  c->OmP = w.take(c->OmP_count);
+  c->Y = w.take(nov * L);
+  i64 p = 0;
+  auto mx = [&](i64 x) { if (x > p) p = x; };
+  mx(splitk_scratch((int)v, (int)o, (int)(L * o), 128, 64));   // S5, S6
+  mx(splitk_scratch((int)na, (int)o, (int)(o * L), 128, 64));  // S7
+  mx(splitk_scratch((int)v, (int)o, (int)(na * L), 128, 64));  // G2
+  mx(splitk_scratch((int)o, (int)o, (int)(na * L), 128, 64));  // S8
+  mx((na * o + 1) * 7);                                        // DIIS dot partials
+  c->P_count = p;
+  c->P = w.take(p);
+  c->OmRep = w.take(nov);
+  c->OmLoc = w.take(nov);
+  c->OmTot = w.take(nov);
+  c->Z = w.take(o * o);
+  c->red = w.take(nov + 8);
+  c->scal = w.take(8192);
+  return w.off;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* mpccb_version(void) { return "mpcc_b200 0.1 (sm_100a, DMMA.8x8x4)"; }
+
+int mpccb_create(mpccb_ctx** out, int nocc, int nvir, int naux, int a_begin, int a_end, int device) {
+  if (!out) return 1;
+  *out = nullptr;
+  mpccb_ctx* c = new mpccb_ctx();
+  memset(c, 0, sizeof(*c));
+  *out = c;   // returned even on failure so the caller can read the message
+  if (nocc <= 0 || nvir <= 0 || naux <= 0) return fail(c, "sizes must be positive");
+  if (a_begin < 0 || a_end > nvir || a_begin >= a_end) return fail(c, "bad slab [%d,%d) of %d", a_begin, a_end, nvir);
+  if (nocc > 128) return fail(c, "nocc=%d > 128: fused t2 epilogue needs a whole (i,j) block per tile", nocc);
+  if ((i64)nocc * nvir * (i64)nocc * nvir / nocc > (i64)INT_MAX) return fail(c, "problem too large for 32-bit row indices");
+  c->o = nocc; c->v = nvir; c->L = naux; c->device = device;
+  c->a_begin = a_begin; c->a_end = a_end; c->na = a_end - a_begin;
+  c->nov = (i64)nocc * nvir;
+  c->ldk = (int)align_up(naux, 2);
+  c->use_tma = 1;
+  c->profile = 0;
+  c->prof_ev = new std::vector<cudaEvent_t>[ST_COUNT];
+  c->t2_na = 128 / nocc; c->t2_nb = 128 / nocc;
+  c->t2_tiles_m = cdiv(c->na, c->t2_na);
+  c->t2_tiles_n = cdiv(nvir, c->t2_nb);
+  CUDA_OK(c, cudaSetDevice(device));
+  c->ws_bytes = 0;
+  return 0;
+}
+
+void mpccb_destroy(mpccb_ctx* ctx) {
+  if (!ctx) return;
+  if (ctx->prof_ev) {
+    for (int s = 0; s < ST_COUNT; ++s)
+      for (cudaEvent_t e : ctx->prof_ev[s]) cudaEventDestroy(e);
+    delete[] ctx->prof_ev;
+  }
+  delete ctx;
+}
+
+int mpccb_profile_stages(void) { return ST_COUNT; }
+const char* mpccb_profile_stage_name(int stage) { return (stage >= 0 && stage < ST_COUNT) ? kStageNames[stage] : ""; }
+
+// synchronises, then returns per-stage summed milliseconds and launch-group counts since the last read
+int mpccb_profile_read(mpccb_ctx* c, double* ms_out, long long* count_out) {
+  CUDA_OK(c, cudaStreamSynchronize(c->stream));
+  for (int s = 0; s < ST_COUNT; ++s) {
+    double tot = 0.0;
+    for (int k = 0; k + 1 < c->prof_used[s]; k += 2) {
+      float ms = 0.f;
+      CUDA_OK(c, cudaEventElapsedTime(&ms, c->prof_ev[s][k], c->prof_ev[s][k + 1]));
+      tot += ms;
+    }
+    ms_out[s] = tot;
+    count_out[s] = c->prof_used[s] / 2;
+    c->prof_used[s] = 0;
+  }
+  return 0;
+}
+
+const char* mpccb_last_error(const mpccb_ctx* ctx) { return ctx ? ctx->err : "null context"; }
+
+int mpccb_set_stream(mpccb_ctx* c, void* s) { c->stream = reinterpret_cast<cudaStream_t>(s); return 0; }
+
+int mpccb_synchronize(mpccb_ctx* c) { CUDA_OK(c, cudaStreamSynchronize(c->stream)); return 0; }
+
+long long mpccb_launch_count(const mpccb_ctx* c) { return c->launches; }
+
+int mpccb_set_option(mpccb_ctx* c, const char* name, long long value) {
+  if (!strcmp(name, "tma")) { c->use_tma = value != 0; return 0; }
+  if (!strcmp(name, "profile")) { c->profile = value != 0; return 0; }
+  return fail(c, "unknown option %s", name);
+}
+
+size_t mpccb_workspace_bytes(const mpccb_ctx* c) {
+  mpccb_ctx tmp = *c;
+  return (size_t)carve_workspace(&tmp, nullptr);
+}
+
+int mpccb_bind_workspace(mpccb_ctx* c, void* ws, size_t bytes) {
+  const size_t need = mpccb_workspace_bytes(c);
+  if (bytes < need) return fail(c, "workspace too small: %zu < %zu", bytes, need);
+  if ((reinterpret_cast<uintptr_t>(ws) & 255) != 0) return fail(c, "workspace must be 256-byte aligned");
+  c->ws = static_cast<unsigned char*>(ws);
+  c->ws_bytes = bytes;
+  carve_workspace(c, c->ws);
+  // K padding columns of JK / E1K (ldk > L) must read as zero for the TMA path
+  CUDA_OK(c, cudaMemsetAsync(c->JK, 0, sizeof(double) * c->nov * c->ldk, c->stream));
+  CUDA_OK(c, cudaMemsetAsync(c->E1K, 0, sizeof(double) * c->nov * c->ldk, c->stream));
+  return 0;
+}
+
+int mpccb_bind_integrals(mpccb_ctx* c, const double* Loo, const double* Lov, const double* Lvv,
+                         const double* foo, const double* fvv, const double* eo, const double* ev) {
+  if (!c->ws) return fail(c, "bind the workspace first");
+  c->Loo = Loo; c->Lov = Lov; c->Lvv = Lvv; c->foo = foo; c->fvv = fvv; c->eo = eo; c->ev = ev;
+  // Lvo[L][b][j] = Lov[L][j][b]
+  dim3 grid(cdiv(c->v, 32), cdiv(c->o, 32), c->L), block(32, 8);
+  k_transpose_batched<<<grid, block, 0, c->stream>>>(Lov, c->Lvo, c->o, c->v);
+  LAUNCH_OK(c, "k_transpose_batched(Lov)");
+  return 0;
+}
+
+int mpccb_bind_t2(mpccb_ctx* c, double* T) { c->T = T; return 0; }
+
+}  // extern "C"
+
+// ===========================================================================
+// phase 1: T1 dressing + singles intermediates (reference :119-133)
+// ===========================================================================
+extern "C" int mpccb_dress(mpccb_ctx* c, const double* t1_dev) {
+  if (!c->ws || !c->Lov) return fail(c, "workspace/integrals not bound");
+  StageTimer timer(c, ST_DRESS);
+  const int o = c->o, v = c->v, L = c->L;
+  const i64 nov = c->nov;
+  if (t1_dev != c->t1)
+    CUDA_OK(c, cudaMemcpyAsync(c->t1, t1_dev, sizeof(double) * nov, cudaMemcpyDeviceToDevice, c->stream));
+  {  // t1T[a][i] = t1[i][a]
+    dim3 grid(cdiv(v, 32), cdiv(o, 32), 1), block(32, 8);
+    k_transpose_batched<<<grid, block, 0, c->stream>>>(c->t1, c->t1T, o, v);
+    LAUNCH_OK(c, "k_transpose_batched(t1)");
+  }
+  {  // :119  Xov[L][i][a] = sum_b Lvv[L][a][b] t1[i][b]      M=(L,a) N=i K=b
+    Operand A = flat_operand(c->Lvv, L * v, v, 1);
+    Operand B = flat_operand(c->t1, o, v, 1);
+    Output C = flat_output(c->Xov, 0, v);
+    C.mdiv = v; C.m_hi = (i64)o * v; C.m_lo = 1;
+    if (launch_gemm<CfgN64KK>(c, "Xvo", A, B, C, L * v, o, v, 1, nullptr)) return 1;
+  }
+  {  // :120,:123  Xoo[(L,i)][j] = sum_a Lov[(L,i)][a] t1[j][a];  Joo = Xoo + Loo
+    Operand A = flat_operand(c->Lov, L * o, v, 1);
+    Operand B = flat_operand(c->t1, o, v, 1);
+    Output C = flat_output(c->Xoo, o, 1);
+    C.base2 = c->Joo; C.aux = c->Loo;
+    if (launch_gemm<CfgN64KK>(c, "Xoo", A, B, C, L * o, o, v, 1, nullptr)) return 1;
+  }
+  // :121  X[L] = trace_i Xoo[L]
+  k_trace<<<cdiv(L, 4), 128, 0, c->stream>>>(c->Xoo, c->X, L, o);
+  LAUNCH_OK(c, "k_trace");
+  {  // [XT | JT][(L,i)][a] = sum_k [Xoo | Joo][(L,i)][k] t1[k][a]    (:124 last term, :127, :146)
+    Operand A = flat_operand(c->Xoo, 2 * L * o, o, 1);
+    Operand B = flat_operand(c->t1T, v, o, 1);
+    Output C = flat_output(c->XT, v, 1);
+    if (launch_gemm<CfgBigKK>(c, "XT|JT", A, B, C, 2 * L * o, v, o, 1, nullptr)) return 1;
+  }
+  {  // :124, :146 integrand, W = XT - Xov
+    dim3 grid(cdiv(v, 32), cdiv(L, 32), o), block(32, 8);
+    k_dress_finalize<<<grid, block, 0, c->stream>>>(c->Xov, c->Lov, c->JT, c->XT, c->X, c->t1, c->JK, c->E1K,
+                                                    c->Wov, L, o, v, c->ldk);
+    LAUNCH_OK(c, "k_dress_finalize");
+  }
+  {  // :126-127  OmRep[a][i] = sum_{(L,j)} W[(L,j)][a] Joo[(L,j)][i]
+    Operand A = flat_operand(c->Wov, v, 1, v);
+    Operand B = flat_operand(c->Joo, o, 1, o);
+    if (splitk_gemm<CfgN64RR>(c, "W.Joo", A, B, c->OmRep, v, o, L * o, 1.0, 0.0)) return 1;
+  }
+  // :128 and first half of :133   w[(a,i)] = sum_L J[(a,i)][L] X[L]
+  k_gemv_rows<<<cdiv(nov, 8), 256, 0, c->stream>>>(c->JK, c->X, c->w, (int)nov, L, c->ldk);
+  LAUNCH_OK(c, "k_gemv_rows");
+  {  // :133 second half   F2[b][j] = sum_{(L,i)} Lov[(L,i)][b] Xoo[(L,i)][j];  Fvo = w - F2
+    Operand A = flat_operand(c->Lov, v, 1, v);
+    Operand B = flat_operand(c->Xoo, o, 1, o);
+    if (splitk_gemm<CfgN64RR>(c, "Xoo.Lov", A, B, c->F2, v, o, L * o, 1.0, 0.0)) return 1;
+    k_make_fvo<<<cdiv(nov, 256), 256, 0, c->stream>>>(c->w, c->F2, c->Fvo, nov);
+    LAUNCH_OK(c, "k_make_fvo");
+  }
+  return 0;
+}
+
+// ===========================================================================
+// phase 2: doubles for the local slab (reference :135-147)
+// ===========================================================================
+namespace {
+
+int launch_eris_t2(mpccb_ctx* c) {
+  typedef CfgBigKK Cfg;
+  const int o = c->o, v = c->v, L = c->L;
+  Operand A = flat_operand(c->JK + (i64)c->a_begin * o * c->ldk, c->na * o, c->ldk, 1);
+  Operand B = flat_operand(c->JK, v * o, c->ldk, 1);
+  T2Params p;
+  p.T = c->T; p.eo = c->eo; p.ev = c->ev; p.Fvo = c->Fvo; p.OmP = c->OmP;
+  p.o = o; p.v = v; p.a_begin = c->a_begin; p.a_end = c->a_end; p.n_a = c->t2_na; p.n_b = c->t2_nb;
+  GemmDims d;
+  d.M = c->na * o; d.N = v * o; d.K = L;
+  d.tm_eff = c->t2_na * o; d.tn_eff = c->t2_nb * o;
+  d.tiles_m = c->t2_tiles_m; d.tiles_n = c->t2_tiles_n;
+  d.kchunk = L;
+  static bool attr_done = false;
+  if (!attr_done) {
+    CUDA_OK(c, cudaFuncSetAttribute(gemm_t2_kernel<Cfg>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)T2Smem<Cfg>::BYTES));
+    attr_done = true;
+  }
+  gemm_t2_kernel<Cfg><<<d.tiles_m * d.tiles_n, Cfg::NTH, T2Smem<Cfg>::BYTES, c->stream>>>(A, B, p, d);
+  LAUNCH_OK(c, "gemm_t2_kernel");
+  return 0;
+}
+
+int launch_yvo(mpccb_ctx* c) {
+  const int o = c->o, v = c->v, L = c->L;
+  // :138  Y[(a,i)][L] = sum_{(b,j)} T[a][b][i][j] Lvo[L][(b,j)]
+  Operand A;
+  A.base = c->T; A.rows = c->na * o;
+  A.rdiv = o; A.r_hi = (i64)v * o * o; A.r_lo = o;
+  A.kdiv = o; A.k_hi = (i64)o * o; A.k_lo = 1;
+  Operand B = flat_operand(c->Lvo, L, (i64)v * o, 1);
+  Output C = flat_output(c->Y + (i64)c->a_begin * o * L, L, 1);
+  return launch_gemm<CfgBigKK>(c, "Yvo", A, B, C, c->na * o, L, v * o, 1, nullptr);
+}
+
+}  // namespace
+
+extern "C" int mpccb_doubles(mpccb_ctx* c, double* red_dev) {
+  if (!c->T) return fail(c, "t2 buffer not bound");
+  const int o = c->o, v = c->v, L = c->L, na = c->na;
+  const i64 nov = c->nov;
+  double* Om = red_dev;   // [a][i] partial over the local slab
+  CUDA_OK(c, cudaMemsetAsync(red_dev, 0, sizeof(double) * (nov + 1), c->stream));
+  {
+    StageTimer timer(c, ST_ERIS_T2);
+    if (launch_eris_t2(c)) return 1;                                 // :135-137 (+ :139 partials)
+  }
+  // :139  Om[a_loc][i] = sum_tiles OmP
+  if (reduce_splits(c, Om + (i64)c->a_begin * o, c->OmP, c->t2_tiles_n, (i64)na * o, (i64)na * o, 1.0, 0.0))
+    return 1;
+  {
+    StageTimer timer(c, ST_YVO);
+    if (launch_yvo(c)) return 1;                                     // :138
+  }
+  StageTimer timer(c, ST_SINGLES_FROM_Y);
+  const double* Yslab = c->Y + (i64)c->a_begin * o * L;
+  {  // :143  Om[a][i] -= sum_{(j,L)} Y[(a,j)][L] Joo[L][j][i]          (a in slab)
+    Operand A = flat_operand(Yslab, na, (i64)o * L, 1);
+    Operand B;
+    B.base = c->Joo; B.rows = o; B.rdiv = BIG; B.r_hi = 0; B.r_lo = 1;
+    B.kdiv = L; B.k_hi = o; B.k_lo = (i64)o * o;
+    if (splitk_gemm<CfgN64KR>(c, "Joo.Yvo", A, B, Om + (i64)c->a_begin * o, na, o, o * L, -1.0, 1.0)) return 1;
+  }
+  Operand By;   // Y[(b,i)][L] read as rows i, K = (b in slab, L)
+  By.base = Yslab; By.rows = o; By.rdiv = BIG; By.r_hi = 0; By.r_lo = L;
+  By.kdiv = L; By.k_hi = (i64)o * L; By.k_lo = 1;
+  {  // :141-142 (Lvv part)  Om[a][i] += sum_{(b,L)} Lvv[L][b][a] Y[(b,i)][L]     (b in slab, all a)
+    Operand A;
+    A.base = c->Lvv + (i64)c->a_begin * v; A.rows = v; A.rdiv = BIG; A.r_hi = 0; A.r_lo = 1;
+    A.kdiv = L; A.k_hi = v; A.k_lo = (i64)v * v;
+    if (splitk_gemm<CfgN64RK>(c, "Lvv.Yvo", A, By, Om, v, o, na * L, 1.0, 1.0)) return 1;
+  }
+  {  // :141-142 (Lov.t1 part)  Z[j][i] = sum_{(b,L)} Lvo[L][b][j] Y[(b,i)][L];  Om[a][i] += sum_j t1[j][a] Z[j][i]
+    Operand A;
+    A.base = c->Lvo + (i64)c->a_begin * o; A.rows = o; A.rdiv = BIG; A.r_hi = 0; A.r_lo = 1;
+    A.kdiv = L; A.k_hi = o; A.k_lo = (i64)v * o;
+    if (splitk_gemm<CfgN64RK>(c, "Lov.Yvo", A, By, c->Z, o, o, na * L, 1.0, 0.0)) return 1;
+    k_add_t1T_Z<<<cdiv(nov, 256), 256, 0, c->stream>>>(Om, c->t1, c->Z, o, v);
+    LAUNCH_OK(c, "k_add_t1T_Z");
+  }
+  {  // :146-147  dE part = sum_{(a,i) in slab, L} e1 * Y
+    const int nb = 592;
+    k_dot_rows_partial<<<nb, 256, 0, c->stream>>>(c->E1K + (i64)c->a_begin * o * c->ldk, Yslab, c->scal, na * o, L,
+                                                  c->ldk, L);
+    LAUNCH_OK(c, "k_dot_rows_partial");
+    k_final_sums<<<1, 256, 0, c->stream>>>(c->scal, red_dev + nov, nb, 1);
+    LAUNCH_OK(c, "k_final_sums");
+  }
+  return 0;
+}
+
+// ===========================================================================
+// phase 3: T1 update (reference :128-131, :149-151)
+// ===========================================================================
+extern "C" int mpccb_finish(mpccb_ctx* c, const double* red_dev, double* t1_new_dev, double* scal_dev) {
+  StageTimer timer(c, ST_FINISH);
+  const i64 nov = c->nov;
+  const int nb = cdiv(nov, 256);
+  if (nb > 8000) return fail(c, "nov too large for the residual scratch");
+  k_t1_update<<<nb, 256, 0, c->stream>>>(c->OmRep, c->w, red_dev, c->t1, c->fvv, c->foo, c->eo, c->ev, t1_new_dev,
+                                         c->OmTot, c->scal, c->o, c->v);
+  LAUNCH_OK(c, "k_t1_update");
+  k_final_sums<<<1, 256, 0, c->stream>>>(c->scal, scal_dev, nb, 1);
+  LAUNCH_OK(c, "k_final_sums");
+  CUDA_OK(c, cudaMemcpyAsync(scal_dev + 1, red_dev + nov, sizeof(double), cudaMemcpyDeviceToDevice, c->stream));
+  return 0;
+}
+
+extern "C" int mpccb_updated_amps_host(mpccb_ctx* c, const double* t1_host, double* t1_new_host,
+                                       double* res_host, double* dE_host) {
+  const i64 nov = c->nov;
+  CUDA_OK(c, cudaMemcpyAsync(c->t1, t1_host, sizeof(double) * nov, cudaMemcpyHostToDevice, c->stream));
+  if (mpccb_dress(c, c->t1)) return 1;
+  if (mpccb_doubles(c, c->red)) return 1;
+  double* sc = c->scal + 8000;
+  if (mpccb_finish(c, c->red, c->t1n, sc)) return 1;
+  double host_sc[2];
+  CUDA_OK(c, cudaMemcpyAsync(t1_new_host, c->t1n, sizeof(double) * nov, cudaMemcpyDeviceToHost, c->stream));
+  CUDA_OK(c, cudaMemcpyAsync(host_sc, sc, sizeof(double) * 2, cudaMemcpyDeviceToHost, c->stream));
+  CUDA_OK(c, cudaStreamSynchronize(c->stream));
+  *res_host = sqrt(host_sc[0]);
+  *dE_host = host_sc[1];
+  return 0;
+}
+
+// ===========================================================================
+// amplitude <-> vector layouts, DIIS algebra
+// ===========================================================================
+extern "C" int mpccb_t2_to_aibj(mpccb_ctx* c, double* out_dev) {
+  if (!c->T) return fail(c, "t2 buffer not bound");
+  const i64 total = (i64)c->na * c->v * c->o * c->o;
+  const int nb = (int)std::min<i64>(cdiv(total, 256), 148 * 16);
+  k_abij_to_aibj<<<nb, 256, 0, c->stream>>>(c->T, out_dev, c->o, c->v, c->na);
+  LAUNCH_OK(c, "k_abij_to_aibj");
+  return 0;
+}
+
+extern "C" int mpccb_pack_tril_rows(mpccb_ctx* c, double* seg_dev) {
+  if (!c->T) return fail(c, "t2 buffer not bound");
+  k_pack_rows<<<c->na * c->o, 256, 0, c->stream>>>(c->T, seg_dev, c->nov, (i64)c->a_begin * c->o);
+  LAUNCH_OK(c, "k_pack_rows");
+  return 0;
+}
+
+extern "C" int mpccb_unpack_oovv(mpccb_ctx* c, const double* packed_dev, double* out_dev) {
+  const i64 total = c->nov * c->nov;
+  const int nb = (int)std::min<i64>(cdiv(total, 256), 148 * 16);
+  k_unpack_oovv<<<nb, 256, 0, c->stream>>>(packed_dev, out_dev, c->o, c->v);
+  LAUNCH_OK(c, "k_unpack_oovv");
+  return 0;
+}
+
+extern "C" int mpccb_diis_push(mpccb_ctx* c, const double* t1_new_dev, const double* xprev_dev,
+                               double* x_slot_dev, double* e_slot_dev, const double* const* e_list_dev,
+                               int nd, int slot, int first_call, int count_t1, double* dots_dev) {
+  if (!c->T) return fail(c, "t2 buffer not bound");
+  if (nd < 0 || nd > 6 || slot < 0 || slot > 5) return fail(c, "bad DIIS slot/nd");
+  StageTimer timer(c, ST_DIIS_PUSH);
+  const int nrows = c->na * c->o;
+  const int nblk = nrows + 1;
+  // partial sums live in the (idle) split-K scratch
+  if ((i64)nblk * 7 > c->P_count) return fail(c, "DIIS partial scratch too small");
+  DiisPtrs ep;
+  for (int k = 0; k < 6; ++k) ep.e[k] = (k < nd && e_list_dev) ? e_list_dev[k] : nullptr;
+  double* partial = c->P;
+  k_diis_push<<<nblk, 256, 0, c->stream>>>(c->T, t1_new_dev, xprev_dev, x_slot_dev, e_slot_dev, ep, nd, slot,
+                                           first_call, count_t1, c->nov, (i64)c->a_begin * c->o, nrows, partial);
+  LAUNCH_OK(c, "k_diis_push");
+  if (!first_call) {
+    k_final_sums_strided<<<1, 256, 0, c->stream>>>(partial, dots_dev, nblk, 7, nd);
+    LAUNCH_OK(c, "k_final_sums_strided");
+  }
+  return 0;
+}
+
+extern "C" int mpccb_diis_combine(mpccb_ctx* c, const double* const* x_list_dev, const double* coeff_host,
+                                  int nd, double* xnew_dev, long long n) {
+  if (nd < 1 || nd > 6) return fail(c, "bad DIIS nd");
+  StageTimer timer(c, ST_DIIS_COMBINE);
+  DiisComb cb;
+  for (int k = 0; k < 6; ++k) {
+    cb.x[k] = k < nd ? x_list_dev[k] : nullptr;
+    cb.c[k] = k < nd ? coeff_host[k] : 0.0;
+  }
+  const int nb = (int)std::min<i64>(cdiv(n, 256), 148 * 16);
+  k_diis_combine<<<nb, 256, 0, c->stream>>>(cb, nd, xnew_dev, n);
+  LAUNCH_OK(c, "k_diis_combine");
+  return 0;
+}
+
+// ===========================================================================
+// introspection / test hooks
+// ===========================================================================
+extern "C" int mpccb_get_buffer(mpccb_ctx* c, const char* name, double** ptr, long long* count) {
+  const i64 o = c->o, v = c->v, L = c->L, nov = c->nov;
+  struct Ent { const char* n; double* p; i64 cnt; };
+  const Ent tab[] = {
+      {"Lvo", c->Lvo, L * v * o},   {"t1", c->t1, nov},          {"t1n", c->t1n, nov},
+      {"Xov", c->Xov, L * o * v},   {"Xoo", c->Xoo, L * o * o},   {"Joo", c->Joo, L * o * o},
+      {"X", c->X, L},               {"XT", c->XT, L * o * v},     {"JT", c->JT, L * o * v},
+      {"JK", c->JK, nov * c->ldk},  {"E1K", c->E1K, nov * c->ldk}, {"Wov", c->Wov, L * o * v},
+      {"w", c->w, nov},             {"Fvo", c->Fvo, nov},         {"Y", c->Y, nov * L},
+      {"OmRep", c->OmRep, nov},     {"OmTot", c->OmTot, nov},     {"Z", c->Z, o * o},
+      {"red", c->red, nov + 1},     {"T", c->T, (i64)c->na * v * o * o},
+  };
+  for (const Ent& e : tab)
+    if (!strcmp(e.n, name)) { *ptr = e.p; *count = e.cnt; return 0; }
+  return fail(c, "unknown buffer %s", name);
+}
+
+extern "C" int mpccb_copy_to_host(mpccb_ctx* c, const double* src, double* dst, long long count) {
+  CUDA_OK(c, cudaMemcpyAsync(dst, src, sizeof(double) * count, cudaMemcpyDeviceToHost, c->stream));
+  CUDA_OK(c, cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+extern "C" int mpccb_copy_to_device(mpccb_ctx* c, const double* src, double* dst, long long count) {
+  CUDA_OK(c, cudaMemcpyAsync(dst, src, sizeof(double) * count, cudaMemcpyHostToDevice, c->stream));
+  CUDA_OK(c, cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+extern "C" int mpccb_gemm_nt(mpccb_ctx* c, const double* A_dev, const double* B_dev, double* C_dev,
+                             int M, int N, int K) {
+  Operand A = flat_operand(A_dev, M, K, 1);
+  Operand B = flat_operand(B_dev, N, K, 1);
+  Output C = flat_output(C_dev, N, 1);
+  return launch_gemm<CfgBigKK>(c, "gemm_nt", A, B, C, M, N, K, 1, nullptr);
+}

@@ -1,0 +1,376 @@
+"""B200 low-level DF-MPCC solver — drop-in for the reference's plug-in module.
+
+The reference solver object takes a *module* and instantiates
+``lowlevel.MPCC_LL(mf)`` (``pyscf/mpcc/mpcc.py:5,13``; ``pyscf/mpcc/dfrmpcc.py:6``
+passes ``dfrmpcc_lowlevel``). This module exports ``MPCC_LL`` with the same
+constructor, attributes and methods (``pyscf/mpcc/dfrmpcc_lowlevel.py:6-176``):
+
+    kernel() -> dE                           (:72-100)
+    updated_amps() -> (res, dE, t1, t2)      (:103-152)   aliases: update_amps, energy
+    run_diis(t1, t2, adiis) -> (t1, t2)      (:155-160)
+    amplitudes_to_vector / vector_to_amplitudes (:162-176)
+    compute_three_center_ints()              (:46-69)
+
+Everything numerical runs in hand-written sm_100a kernels behind the C ABI of
+``libmpcc_b200.so`` (``include/mpcc_b200.h``); PyTorch only owns the device
+buffers and the NCCL process group. There is no CPU fallback: constructing the
+solver without a CUDA device or without the built library raises.
+
+Bug-compatible details kept on purpose: the ``+`` sign in Jvv,
+the dressed ``Jvo`` in ``Fov``, t2 returned as (v,o,v,o) from ``updated_amps``
+and as (o,o,v,v) after DIIS, the non-symmetric lower-triangle DIIS vector, the
+energy lagging the amplitudes by one update, convergence tested on T1 only.
+"""
+from __future__ import annotations
+
+import sys
+
+import numpy as np
+import torch
+
+from . import _cabi, sharding
+from .diis import DIIS, AmplitudeVector
+
+
+class DeviceT2:
+    """Lazy host view of doubles amplitudes that live on the GPU.
+
+    ``layout == "aibj"``: the (v,o,v,o) tensor ``updated_amps`` returns (:137,:152),
+    backed by the solver's [a,b,i,j] buffer. ``layout == "oovv"``: the (o,o,v,v)
+    tensor ``vector_to_amplitudes`` returns (:170-176), backed by a packed vector.
+    ``numpy()`` / ``np.asarray`` materialise it; nothing on the hot path does.
+    """
+
+    def __init__(self, solver, layout, packed=None, serial=0):
+        self.solver = solver
+        self.layout = layout
+        self.packed = packed
+        self.serial = serial
+        o, v = solver.nocc, solver.nvir
+        self.shape = (v, o, v, o) if layout == "aibj" else (o, o, v, v)
+        self.dtype = np.dtype(np.float64)
+        self.ndim = 4
+
+    def numpy(self):
+        ll = self.solver
+        if ll.world_size > 1:
+            raise NotImplementedError("gather of sharded t2; read the local slab with local_numpy()")
+        return self.local_numpy()
+
+    def local_numpy(self):
+        ll = self.solver
+        o, v = ll.nocc, ll.nvir
+        if self.layout == "aibj":
+            if self.serial != ll._t2_serial:
+                raise RuntimeError("this t2 handle is stale: the device buffer was overwritten by a later updated_amps()")
+            out = torch.empty((ll._na, o, v, o), dtype=torch.float64, device=ll.device)
+            ll._ctx.call("mpccb_t2_to_aibj", out.data_ptr())
+        else:
+            if ll.world_size > 1:
+                raise NotImplementedError("oovv unpack of a sharded vector")
+            out = torch.empty((o, o, v, v), dtype=torch.float64, device=ll.device)
+            ll._ctx.call("mpccb_unpack_oovv", self.packed.data_ptr(), out.data_ptr())
+        ll._sync()
+        return out.cpu().numpy()
+
+    def __array__(self, dtype=None, copy=None):
+        a = self.numpy()
+        return a if dtype is None else a.astype(dtype)
+
+
+class MPCC_LL:
+    """GPU-resident equivalent of ``pyscf.mpcc.dfrmpcc_lowlevel.MPCC_LL``."""
+
+    def __init__(self, mf=None, *, blocks=None, device=None, group=None, use_tma=True):
+        """``MPCC_LL(mf)`` as in the reference (:7-43). Extensions (keyword only):
+
+        blocks : (Loo, Lov, Lvv, foo, fvv, mo_energy) numpy arrays or CUDA tensors
+                 already in the MO basis — skips ``compute_three_center_ints``.
+        device : torch device (default ``cuda:<LOCAL_RANK or 0>``).
+        group  : torch.distributed process group to shard the doubles over
+                 (default: the WORLD group if torch.distributed is initialised).
+        """
+        if not torch.cuda.is_available():
+            raise RuntimeError("pyscf_mpcc_b200 needs a CUDA device (B200, sm_100a); there is no CPU path")
+        self.mf = mf
+        self.with_df = getattr(mf, "with_df", None) if mf is not None else None
+        if mf is not None and self.with_df is None:
+            # the reference's no-with_df branch raises NameError (df is not imported, :13); be explicit
+            raise RuntimeError("MPCC_LL needs a density-fitted mean field (mf.density_fit())")
+        self.t1 = None
+        self.t2 = None
+        self.diis = True
+        self.con_tol = 1e-6
+        self.max_its = 50
+        self.verbose_print = True
+        self.stdout = sys.stdout
+
+        if torch.distributed.is_available() and torch.distributed.is_initialized():
+            self.group = group if group is not None else torch.distributed.group.WORLD
+            self.world_size = torch.distributed.get_world_size(self.group)
+            self.rank = torch.distributed.get_rank(self.group)
+        else:
+            self.group, self.world_size, self.rank = None, 1, 0
+        if device is None:
+            device = torch.device("cuda", torch.cuda.current_device())
+        self.device = torch.device(device)
+        if self.device.index is None:
+            self.device = torch.device("cuda", torch.cuda.current_device())
+        torch.cuda.set_device(self.device)
+
+        if mf is not None:
+            self.nao = int(mf.mol.nao)
+            self.nocc = int(mf.mol.nelec[0])
+            self.nvir = self.nao - self.nocc
+            self.naux = int(self.with_df.get_naoaux())
+            self.mo_energy = np.asarray(mf.mo_energy, dtype=np.float64)
+            self.mo_coeff = np.asarray(mf.mo_coeff, dtype=np.float64)
+        else:
+            Loo, Lov, Lvv, foo, fvv, mo_energy = blocks
+            self.naux, self.nocc, self.nvir = (int(s) for s in Lov.shape)
+            self.nao = self.nocc + self.nvir
+            self.mo_energy = self._to_host(mo_energy)
+            self.mo_coeff = None
+        self.nvir_pair = self.nvir * (self.nvir + 1) // 2
+        self.nov = self.nocc * self.nvir
+        o, v, L = self.nocc, self.nvir, self.naux
+
+        # --- native context, workspace, device buffers (torch owns the memory) ---
+        self._a_begin, self._a_end = sharding.slab_bounds(v, self.world_size, self.rank)
+        self._na = self._a_end - self._a_begin
+        self._count_t1 = (self.rank == 0)
+        self._vec_len_local = sharding.local_vector_length(o, v, self._a_begin, self._a_end)
+        self._ctx = _cabi.Context(o, v, L, self._a_begin, self._a_end, self.device.index)
+        self._ctx.call("mpccb_set_option", b"tma", int(bool(use_tma)))
+        self._bind_stream()
+        f64 = dict(dtype=torch.float64, device=self.device)
+        self._ws = torch.empty(self._ctx.workspace_bytes() + 256, dtype=torch.uint8, device=self.device)
+        ws_ptr = (self._ws.data_ptr() + 255) // 256 * 256
+        self._ctx.call("mpccb_bind_workspace", ws_ptr, self._ctx.workspace_bytes())
+        self._T = torch.empty(self._na * v * o * o, **f64)
+        self._ctx.call("mpccb_bind_t2", self._T.data_ptr())
+        self._t2_serial = 0
+        self._red = torch.zeros(self.nov + 1, **f64)
+        self._t1_dev = torch.zeros(self.nov, **f64)
+        self._t1n_dev = torch.zeros(self.nov, **f64)
+        self._scal_dev = torch.zeros(2, **f64)
+        self._dots_dev = torch.zeros(7, **f64)
+        self._t1_host = torch.zeros(self.nov, dtype=torch.float64).pin_memory()
+        self._t1n_host = torch.zeros(self.nov, dtype=torch.float64).pin_memory()
+        self._scal_host = torch.zeros(2, dtype=torch.float64).pin_memory()
+        self._dots_host = torch.zeros(7, dtype=torch.float64).pin_memory()
+
+        if mf is not None:
+            self.compute_three_center_ints()
+            fock_mo = self.mo_coeff.T @ np.asarray(mf.get_fock()) @ self.mo_coeff
+            foo = np.ascontiguousarray(fock_mo[:o, :o])
+            fvv = np.ascontiguousarray(fock_mo[o:, o:])
+        else:
+            self._d = {"Loo": self._to_dev(Loo), "Lov": self._to_dev(Lov), "Lvv": self._to_dev(Lvv)}
+        self._d["foo"] = self._to_dev(foo)
+        self._d["fvv"] = self._to_dev(fvv)
+        self._d["eo"] = self._to_dev(self.mo_energy[:o])
+        self._d["ev"] = self._to_dev(self.mo_energy[o:])
+        d = self._d
+        self._ctx.call("mpccb_bind_integrals", d["Loo"].data_ptr(), d["Lov"].data_ptr(), d["Lvv"].data_ptr(),
+                       d["foo"].data_ptr(), d["fvv"].data_ptr(), d["eo"].data_ptr(), d["ev"].data_ptr())
+        # eia[i,a] = e_a - e_i  (:40-42)
+        self.eia = self.mo_energy[o:][None, :] - self.mo_energy[:o][:, None]
+        self.h2d_bytes = 0
+        self.d2h_bytes = 0
+
+    # ------------------------------------------------------------------ plumbing
+    def _bind_stream(self):
+        self._stream = torch.cuda.current_stream(self.device)
+        self._ctx.call("mpccb_set_stream", self._stream.cuda_stream)
+
+    def _sync(self):
+        self._stream.synchronize()
+
+    def _to_dev(self, x):
+        if isinstance(x, torch.Tensor):
+            return x.to(device=self.device, dtype=torch.float64).contiguous()
+        return torch.from_numpy(np.ascontiguousarray(x, dtype=np.float64)).to(self.device)
+
+    @staticmethod
+    def _to_host(x):
+        if isinstance(x, torch.Tensor):
+            return x.detach().cpu().numpy().astype(np.float64)
+        return np.asarray(x, dtype=np.float64)
+
+    def _host_attr(self, name):
+        self._sync()
+        return self._d[name].cpu().numpy()
+
+    # host-readable views of the device-resident tensors (reference attribute names, :66-69,:36-37)
+    Loo = property(lambda self: self._host_attr("Loo"))
+    Lov = property(lambda self: self._host_attr("Lov"))
+    Lvv = property(lambda self: self._host_attr("Lvv"))
+    foo = property(lambda self: self._host_attr("foo"))
+    fvv = property(lambda self: self._host_attr("fvv"))
+
+    @property
+    def Lvo(self):
+        """(L,v,o) transpose of Lov — the reference builds it (:50,:63) and never uses it; here it
+        is the K-major operand of the Yvo GEMM."""
+        p, n = self._ctx.buffer("Lvo")
+        return self._read_device(p, n).reshape(self.naux, self.nvir, self.nocc)
+
+    @property
+    def D(self):
+        """D[a,i,b,j] = -eia[i,a] - eia[j,b] (:43). Never materialised on the device."""
+        e = self.eia.T
+        return -(e[:, :, None, None] + e[None, None, :, :])
+
+    def _read_device(self, ptr, count):
+        out = np.empty(count, dtype=np.float64)
+        self._ctx.call("mpccb_copy_to_host", ptr, out.ctypes.data, count)
+        return out
+
+    def debug_buffer(self, name):
+        """Host copy of a named scratch tensor (tests / profiling only)."""
+        p, n = self._ctx.buffer(name)
+        return self._read_device(p, n)
+
+    # ------------------------------------------------------------------ :46-69
+    def compute_three_center_ints(self):
+        """AO->MO transform of the Cholesky tensor, block by block as ``with_df.loop()``
+        yields it, then upload. Host BLAS; T1-independent, once per solve (device
+        version is SURVEY.md §8f row f3)."""
+        nao, o = self.nao, self.nocc
+        C = self.mo_coeff
+        r, c = np.tril_indices(nao)
+        Loo = torch.empty((self.naux, o, o), dtype=torch.float64, device=self.device)
+        Lov = torch.empty((self.naux, o, nao - o), dtype=torch.float64, device=self.device)
+        Lvv = torch.empty((self.naux, nao - o, nao - o), dtype=torch.float64, device=self.device)
+        identity = C.shape == (nao, nao) and np.array_equal(C, np.eye(nao))
+        p1 = 0
+        for packed in self.with_df.loop():
+            nb = packed.shape[0]
+            full = np.empty((nb, nao, nao))
+            full[:, r, c] = packed
+            full[:, c, r] = packed
+            if not identity:
+                half = (full.reshape(nb * nao, nao) @ C).reshape(nb, nao, nao)        # [L, mu, q]
+                full = np.matmul(C.T[None, :, :], half)                                # [L, p, q]
+            p0, p1 = p1, p1 + nb
+            Loo[p0:p1] = torch.from_numpy(np.ascontiguousarray(full[:, :o, :o]))
+            Lov[p0:p1] = torch.from_numpy(np.ascontiguousarray(full[:, :o, o:]))
+            Lvv[p0:p1] = torch.from_numpy(np.ascontiguousarray(full[:, o:, o:]))
+        self._d = {"Loo": Loo, "Lov": Lov, "Lvv": Lvv}
+
+    # ------------------------------------------------------------------ :103-152
+    def updated_amps(self):
+        """One residual evaluation from ``self.t1``; returns (res, dE, t1_new, t2) with
+        t1_new a host (o,v) array and t2 a lazy (v,o,v,o) handle on the device buffer."""
+        self._bind_stream()
+        t1 = self.t1
+        if isinstance(t1, torch.Tensor) and t1.is_cuda:
+            self._t1_dev.copy_(t1.reshape(-1))
+        else:
+            self._t1_host.copy_(torch.from_numpy(np.ascontiguousarray(t1, dtype=np.float64).reshape(-1)))
+            self._t1_dev.copy_(self._t1_host, non_blocking=True)
+            self.h2d_bytes += self.nov * 8
+        ctx = self._ctx
+        ctx.call("mpccb_dress", self._t1_dev.data_ptr())
+        ctx.call("mpccb_doubles", self._red.data_ptr())
+        self._t2_serial += 1
+        if self.world_size > 1:
+            torch.distributed.all_reduce(self._red, group=self.group)
+        ctx.call("mpccb_finish", self._red.data_ptr(), self._t1n_dev.data_ptr(), self._scal_dev.data_ptr())
+        self._t1n_host.copy_(self._t1n_dev, non_blocking=True)
+        self._scal_host.copy_(self._scal_dev, non_blocking=True)
+        self._sync()
+        self.d2h_bytes += self.nov * 8 + 16
+        res = float(np.sqrt(self._scal_host[0].item()))
+        dE = float(self._scal_host[1].item())
+        t1_new = self._t1n_host.numpy().reshape(self.nocc, self.nvir).copy()
+        self._last_t1_new = t1_new          # lets run_diis reuse the device copy instead of re-uploading
+        return res, dE, t1_new, DeviceT2(self, "aibj", serial=self._t2_serial)
+
+    update_amps = updated_amps       # north_star / PySCF-CC spelling
+
+    def energy(self, t1=None):
+        """Correlation energy dE of ``t1`` (default ``self.t1``): the second return value
+        of ``updated_amps`` (:146-147; standalone form ``compute_CC2_energy``,
+        ``pyscf/cc/rmpcc_lowlevel.py:82-109``)."""
+        keep = self.t1
+        if t1 is not None:
+            self.t1 = t1
+        try:
+            return self.updated_amps()[1]
+        finally:
+            self.t1 = keep
+
+    # ------------------------------------------------------------------ :155-176
+    def amplitudes_to_vector(self, t1, t2, out=None):
+        """[t1 | tril(M)] (:162-168) as a device-side handle; ``.numpy()`` gives the flat host vector."""
+        if isinstance(t2, DeviceT2):
+            if t2.layout != "aibj" or t2.serial != self._t2_serial:
+                raise RuntimeError("amplitudes_to_vector needs the t2 of the latest updated_amps()")
+        else:
+            self._upload_t2(np.asarray(t2))
+        if t1 is getattr(self, "_last_t1_new", None):
+            t1_dev = self._t1n_dev
+        elif isinstance(t1, torch.Tensor):
+            t1_dev = t1.to(self.device).reshape(-1)
+        else:
+            t1_dev = self._to_dev(np.ascontiguousarray(t1).reshape(-1))
+            self.h2d_bytes += self.nov * 8
+        return AmplitudeVector(self, vec=None, t1_dev=t1_dev)
+
+    def _upload_t2(self, t2):
+        """Accept a host 4-index array the way the reference would (:166): M = t2.transpose(0,2,1,3)
+        read as (nov,nov). Stored into the device buffer in that order (single-rank, small cases)."""
+        if self.world_size > 1:
+            raise NotImplementedError("host t2 upload with several ranks")
+        m = np.ascontiguousarray(t2.transpose(0, 2, 1, 3)).reshape(-1)
+        if m.size != self._T.numel():
+            raise ValueError("t2 has the wrong size")
+        self._T.copy_(torch.from_numpy(m))
+        self._t2_serial += 1
+
+    def vector_to_amplitudes(self, vector):
+        """(:170-176) t1 (o,v) host copy; t2 (o,o,v,v) lazy handle."""
+        if isinstance(vector, AmplitudeVector):
+            vec = vector.packed_device()
+        else:
+            vec = self._to_dev(np.asarray(vector))
+        self._t1n_host.copy_(vec[:self.nov], non_blocking=True)
+        self._sync()
+        self.d2h_bytes += self.nov * 8
+        t1 = self._t1n_host.numpy().reshape(self.nocc, self.nvir).copy()
+        return t1, DeviceT2(self, "oovv", packed=vec[self.nov:])
+
+    def run_diis(self, t1, t2, adiis):
+        vec = self.amplitudes_to_vector(t1, t2)
+        t1, t2 = self.vector_to_amplitudes(adiis.update(vec))
+        return t1, t2
+
+    # ------------------------------------------------------------------ :72-100
+    def kernel(self):
+        self.t1 = np.zeros((self.nocc, self.nvir))
+        self.t2 = np.zeros((self.nocc, self.nocc, self.nvir, self.nvir)) if self.nov ** 2 < 2 ** 24 else None
+        err = np.inf
+        count = 0
+        adiis = DIIS()
+        self.history = []
+        DE = None
+        while err > self.con_tol and count < self.max_its:
+            res, DE, t1_new, t2_new = self.updated_amps()
+            if self.diis:
+                t1, t2 = self.run_diis(t1_new, t2_new, adiis)
+            else:
+                t1, t2 = t1_new, t2_new
+            self.t1 = t1
+            self.t2 = t2
+            count += 1
+            err = res
+            self.history.append((count, DE, res))
+            if self.verbose_print and self.rank == 0:
+                print(f"It {count} Energy progress {DE:.6e} residual progress {res:.6e}", file=self.stdout)
+        if self.verbose_print and self.rank == 0:
+            print("In Kernel!", file=self.stdout)
+        self.iterations = count
+        self._adiis = adiis
+        return DE

@@ -64,13 +64,13 @@ __device__ __forceinline__ double dfma_body(int iters, double seed) {
 }
 
 template <int MT, int NT>
-__global__ void __launch_bounds__(512) k_dmma(double* out, int iters) {
+__global__ void __launch_bounds__(256) k_dmma(double* out, int iters) {
   out[blockIdx.x * blockDim.x + threadIdx.x] = dmma_body<MT, NT>(iters, 1.0 + threadIdx.x * 1e-9);
 }
-__global__ void __launch_bounds__(512) k_dfma(double* out, int iters) {
+__global__ void __launch_bounds__(256) k_dfma(double* out, int iters) {
   out[blockIdx.x * blockDim.x + threadIdx.x] = dfma_body(iters, 1.0 + threadIdx.x * 1e-9);
 }
-__global__ void __launch_bounds__(512) k_mixed(double* out, int it_dmma, int it_dfma) {
+__global__ void __launch_bounds__(256) k_mixed(double* out, int it_dmma, int it_dfma) {
   int w = threadIdx.x >> 5;
   double r;
   if (w & 1) r = dfma_body(it_dfma, 1.0 + threadIdx.x * 1e-9);
@@ -100,7 +100,7 @@ int main() {
     printf("%-28s warps/SM=%2d  %8.3f ms  %6.2f TFLOP/s  %.1f FMA/clk/SM @1965\n", name, warps, ms, tf,
            fma_total / nsm / (ms * 1e-3 * clk));
   };
-  int wl[] = {4, 8, 12, 16};
+  int wl[] = {4, 8};
   for (int w : wl) {
     int it = 40000;
     { float ms = timeit([&] { k_dmma<8, 4><<<nsm, w * 32>>>(out, it / 2); });
@@ -115,8 +115,12 @@ int main() {
   // two CTAs per SM of 8 warps
   { int it = 40000; float ms = timeit([&] { k_dmma<4, 4><<<nsm * 2, 8 * 32>>>(out, it); });
     report("DMMA 4x4, 2 CTA/SM x 8 warps", 16, ms, (double)it * 16 * 256 * 8 * nsm * 2); }
+  { int it = 40000; float ms = timeit([&] { k_dmma<4, 4><<<nsm, 16 * 32>>>(out, it); });
+    report("DMMA 4x4, 16 warps", 16, ms, (double)it * 16 * 256 * 16 * nsm); }
+  { int it = 20000; float ms = timeit([&] { k_dmma<8, 8><<<nsm, 4 * 32>>>(out, it); });
+    report("DMMA 8x8 frags (64x64), 4 warps", 4, ms, (double)it * 64 * 256 * 4 * nsm); }
   // mixed: 8 warps (4 DMMA + 4 DFMA) and 16 warps
-  for (int w : {8, 16}) {
+  for (int w : {8}) {
     int itm = 40000, itf = 40000 * 2;
     // balance so both halves take similar time at their solo rates (DMMA 4x4: 16*256 FMA/iter/warp; DFMA: 64*32)
     float ms = timeit([&] { k_mixed<<<nsm, w * 32>>>(out, itm, itf * 2); });
