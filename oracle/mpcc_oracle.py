@@ -40,7 +40,7 @@ import scipy.linalg
 
 __all__ = [
     "tril_pack", "tril_unpack_symmetric", "amps_to_vector", "vector_to_amps",
-    "PulayDIIS", "LowLevelOracle", "flops_per_updated_amps",
+    "PulayDIIS", "LowLevelOracle", "flops_per_updated_amps", "doubles_sample",
 ]
 
 
@@ -189,6 +189,27 @@ def flops_per_updated_amps(o: int, v: int, L: int) -> float:
     nov = o * v
     return (4.0 * L * nov * nov + 2.0 * nov * nov + 6.0 * L * v * v * o
             + 14.0 * L * o * o * v + 8.0 * L * o * v)
+
+
+def doubles_sample(Jvo, Lov, eo, ev, a0, a1, mode="einsum"):
+    """The two O(L·nov²) contractions and the t2 build (dfrmpcc_lowlevel.py:135-138)
+    restricted to rows a0 <= a < a1 — the bounded CPU sample timed by bench.py.
+    Returns (t2_slab [a,i,b,j], Yvo_slab [L,a,i], flops)."""
+    L, v, o = Jvo.shape
+    na = a1 - a0
+    D = (eo[None, :, None, None] + eo[None, None, None, :]
+         - ev[a0:a1, None, None, None] - ev[None, None, :, None])
+    if mode == "einsum":
+        eris = np.einsum("Lai,Ljb->aijb", Jvo[:, a0:a1], Jvo)
+        t2 = (2 * eris - np.transpose(eris, (0, 3, 2, 1))) / D
+        Y = np.einsum("aibj,Ljb->Lai", t2, Lov)
+    else:
+        Jm = Jvo.reshape(L, v * o)
+        eris = (Jm[:, a0 * o:a1 * o].T @ Jm).reshape(na, o, v, o)
+        t2 = (2 * eris - eris.transpose(0, 3, 2, 1)) / D
+        Lvo = np.ascontiguousarray(Lov.transpose(0, 2, 1)).reshape(L, v * o)
+        Y = (Lvo @ t2.reshape(na * o, v * o).T).reshape(L, na, o)
+    return t2, Y, 4.0 * L * (na * o) * (o * v)
 
 
 class LowLevelOracle:

@@ -290,6 +290,26 @@ class MPCC_LL:
 
     update_amps = updated_amps       # north_star / PySCF-CC spelling
 
+    def step_device(self, t1_dev, adiis=None):
+        """One trip of the ``kernel()`` loop (:84-86) with the amplitudes resident in HBM:
+        ``t1_dev`` (nov doubles, CUDA) in, next t1 (CUDA view) out; only the two scalars and
+        the <= 6 DIIS dot products cross PCIe. Returns (res, dE, t1_next_dev)."""
+        self._bind_stream()
+        ctx = self._ctx
+        ctx.call("mpccb_dress", t1_dev.data_ptr())
+        ctx.call("mpccb_doubles", self._red.data_ptr())
+        self._t2_serial += 1
+        if self.world_size > 1:
+            torch.distributed.all_reduce(self._red, group=self.group)
+        ctx.call("mpccb_finish", self._red.data_ptr(), self._t1n_dev.data_ptr(), self._scal_dev.data_ptr())
+        self._scal_host.copy_(self._scal_dev, non_blocking=True)
+        if adiis is not None:
+            nxt = adiis.update(AmplitudeVector(self, vec=None, t1_dev=self._t1n_dev)).vec[:self.nov]
+        else:
+            nxt = self._t1n_dev
+        self._sync()
+        return float(np.sqrt(self._scal_host[0].item())), float(self._scal_host[1].item()), nxt
+
     def energy(self, t1=None):
         """Correlation energy dE of ``t1`` (default ``self.t1``): the second return value
         of ``updated_amps`` (:146-147; standalone form ``compute_CC2_energy``,

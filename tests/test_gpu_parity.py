@@ -1,0 +1,192 @@
+"""GPU parity tests (-m gpu): the CUDA path through the C ABI / MPCC_LL drop-in against
+(1) the fixtures the reference produced (tests/golden) and (2) the oracle on the same seeded inputs.
+Tolerances are north_star's: |dE| <= 1e-8 Eh, amplitudes max-abs <= 1e-10, identical iteration counts."""
+import ctypes
+import os
+
+import numpy as np
+import pytest
+
+from conftest import golden_cases
+
+pytestmark = pytest.mark.gpu
+
+E_TOL = 1e-8
+AMP_TOL = 1e-10
+STRIDE = 97
+
+
+def _solver(o, v, L, scale, seed=0, **kw):
+    from pyscf_mpcc_b200.lowlevel import MPCC_LL
+    from pyscf_mpcc_b200.synthetic import SyntheticMF
+    mf = SyntheticMF(o, v, L, seed=seed, scale=scale)
+    ll = MPCC_LL(mf, **kw)
+    ll.verbose_print = False
+    return mf, ll
+
+
+def _load(path):
+    g = np.load(path)
+    o, v, L = (int(x) for x in g["shape"])
+    return g, o, v, L, float(g["scale"])
+
+
+@pytest.mark.parametrize("path", golden_cases(), ids=os.path.basename)
+def test_kernel_against_reference_fixture(path):
+    g, o, v, L, scale = _load(path)
+    mf, ll = _solver(o, v, L, scale)
+    ll.con_tol, ll.max_its = 1e-6, 50
+    e = ll.kernel()
+    assert ll.iterations == int(g["iterations"])
+    tr = np.array(ll.history)
+    assert np.abs(tr[:, 1] - g["trace_dE"]).max() <= E_TOL
+    np.testing.assert_allclose(tr[:, 2], g["trace_res"], rtol=1e-6, atol=1e-12)
+    assert abs(e - g["trace_dE"][-1]) <= E_TOL
+    assert np.abs(ll.t1 - g["final_t1"]).max() <= AMP_TOL
+    t2 = np.asarray(ll.t2)
+    assert t2.shape == (o, o, v, v)                       # (o,o,v,v) after DIIS, as the reference leaves it
+    assert np.abs(t2.reshape(-1)[::STRIDE] - g["final_t2_samples"]).max() <= AMP_TOL
+    assert abs(np.linalg.norm(t2) - g["final_t2_norm"]) <= 1e-9
+    if "final_t2" in g:
+        assert np.abs(t2 - g["final_t2"]).max() <= AMP_TOL
+
+
+@pytest.mark.parametrize("path", golden_cases(), ids=os.path.basename)
+@pytest.mark.parametrize("tag", ["zero", "rand"])
+def test_updated_amps_known_answers(path, tag):
+    g, o, v, L, scale = _load(path)
+    mf, ll = _solver(o, v, L, scale)
+    ll.t1 = g[f"kat_{tag}_t1_in"]
+    res, dE, t1n, t2 = ll.updated_amps()
+    assert abs(dE - g[f"kat_{tag}_dE"]) <= E_TOL
+    assert abs(res - g[f"kat_{tag}_res"]) <= 1e-10 * max(1.0, float(g[f"kat_{tag}_res"]))
+    assert np.abs(t1n - g[f"kat_{tag}_t1_new"]).max() <= AMP_TOL
+    assert t2.shape == (v, o, v, o)                       # (v,o,v,o) from updated_amps
+    t2h = np.asarray(t2)
+    assert np.abs(t2h.reshape(-1)[::STRIDE] - g[f"kat_{tag}_t2_samples"]).max() <= AMP_TOL
+    vec = ll.amplitudes_to_vector(t1n, t2).numpy()
+    assert np.abs(vec[::STRIDE] - g[f"kat_{tag}_vec_samples"]).max() <= AMP_TOL
+    assert abs(np.linalg.norm(vec) - g[f"kat_{tag}_vec_norm"]) <= 1e-9
+    # energy() alias = second return value; update_amps alias
+    assert abs(ll.energy() - dE) <= 1e-13
+    assert ll.update_amps.__func__ is ll.updated_amps.__func__
+
+
+@pytest.mark.parametrize("shape", [(5, 19, 116, 0.1), (7, 33, 65, 0.15), (16, 48, 150, 0.1), (33, 70, 129, 0.05),
+                                   (64, 66, 130, 0.05), (128, 130, 64, 0.03)])
+def test_intermediates_against_oracle(shape):
+    """Every stage of updated_amps vs the oracle on the same seeded inputs (odd sizes, o up to the
+    128 limit of the fused epilogue, naux not a multiple of the K tile)."""
+    from oracle.mpcc_oracle import LowLevelOracle
+    o, v, L, scale = shape
+    mf, ll = _solver(o, v, L, scale, seed=3)
+    orc = LowLevelOracle(mf, mode="blas")
+    t1 = 0.03 * np.random.default_rng(11).standard_normal((o, v))
+    ll.t1 = t1
+    res, dE, t1n, t2 = ll.updated_amps()
+    res_o, dE_o, t1n_o, t2_o = orc.updated_amps(t1)
+    Lov, Lvv, Loo = orc.Lov, orc.Lvv, orc.Loo
+    Xvo = np.einsum("Lab,ib->Lai", Lvv, t1, optimize=True)
+    Xoo = np.einsum("Lia,ja->Lij", Lov, t1, optimize=True)
+    Joo = Xoo + Loo
+    Jvo = Xvo + Lov.transpose(0, 2, 1) - np.einsum("Lij,ja->Lai", Joo, t1, optimize=True)
+    Y = np.einsum("aibj,Ljb->Lai", t2_o, Lov, optimize=True)
+    B = ll.debug_buffer
+    ldk = (L + 1) // 2 * 2
+
+    def close(a, b, name):
+        scale_ = max(1.0, np.abs(b).max())
+        assert np.abs(a - b).max() <= 1e-12 * scale_, name
+
+    close(B("Xov").reshape(L, o, v), Xvo.transpose(0, 2, 1), "Xvo")
+    close(B("Xoo").reshape(L, o, o), Xoo, "Xoo")
+    close(B("Joo").reshape(L, o, o), Joo, "Joo")
+    close(B("X"), np.einsum("Lii->L", Xoo), "X")
+    close(B("JK").reshape(v * o, ldk)[:, :L], Jvo.transpose(1, 2, 0).reshape(v * o, L), "Jvo")
+    close(B("T").reshape(v, v, o, o), t2_o.transpose(0, 2, 1, 3), "t2")
+    close(B("Y").reshape(v * o, L), Y.transpose(1, 2, 0).reshape(v * o, L), "Yvo")
+    assert abs(dE - dE_o) <= E_TOL and abs(res - res_o) <= 1e-10 * max(1, res_o)
+    assert np.abs(t1n - t1n_o).max() <= AMP_TOL
+    assert np.abs(np.asarray(t2) - t2_o).max() <= AMP_TOL
+
+
+def test_dropin_factory_and_print_format(capsys):
+    """mpcc.MPCC(mf): construction runs the solve with con_tol 1e-6 / max_its 50 (pyscf/mpcc/mpcc.py:13-17)
+    and prints the reference's progress lines (dfrmpcc_lowlevel.py:95,97)."""
+    import pyscf_mpcc_b200
+    from pyscf_mpcc_b200.synthetic import SyntheticMF
+    g = np.load(golden_cases()[0])
+    o, v, L = (int(x) for x in g["shape"])
+    obj = pyscf_mpcc_b200.MPCC(SyntheticMF(o, v, L, seed=0, scale=float(g["scale"])))
+    out = capsys.readouterr().out.strip().splitlines()
+    assert obj.lowlevel.con_tol == 1e-6 and obj.lowlevel.max_its == 50
+    assert out[-1] == "In Kernel!"
+    its = [l for l in out if l.startswith("It ")]
+    assert len(its) == int(g["iterations"])
+    k = len(its)
+    assert its[-1] == f"It {k} Energy progress {g['trace_dE'][-1]:.6e} residual progress {g['trace_res'][-1]:.6e}"
+    assert abs(obj.kernel() - g["trace_dE"][-1]) <= E_TOL and obj.with_df is not None
+
+
+def test_reference_seam_accepts_the_module():
+    """The reference's own solver object only needs `lowlevel.MPCC_LL(mf)` + attribute pokes (mpcc.py:13-17)."""
+    import pyscf_mpcc_b200.lowlevel as module
+    from pyscf_mpcc_b200.synthetic import SyntheticMF
+    mf = SyntheticMF(4, 10, 30, seed=0, scale=0.3)
+    low = module.MPCC_LL(mf)
+    low.verbose_print = False
+    low.con_tol = 1e-6
+    low.max_its = 50
+    e = low.kernel()
+    assert abs(e - (-7.1793901067873866e-01)) <= E_TOL and low.iterations == 9
+    for name in ("mf", "with_df", "t1", "t2", "diis", "nao", "nocc", "nvir", "naux", "mo_energy", "mo_coeff",
+                 "nvir_pair", "Loo", "Lov", "Lvo", "Lvv", "foo", "fvv", "eia", "D"):
+        assert hasattr(low, name), name
+    assert low.Lov.shape == (30, 4, 10) and low.Lvo.shape == (30, 10, 4) and low.D.shape == (10, 4, 10, 4)
+    np.testing.assert_array_equal(low.Lvo, low.Lov.transpose(0, 2, 1))
+
+
+def test_diis_off_and_max_its():
+    """diis=False keeps t2 (v,o,v,o) and does not converge on these problems: loop stops at max_its."""
+    from oracle.mpcc_oracle import LowLevelOracle
+    mf, ll = _solver(5, 19, 116, 0.1)
+    ll.diis = False
+    ll.max_its = 7
+    e = ll.kernel()
+    orc = LowLevelOracle(mf, mode="blas"); orc.diis = False; orc.max_its = 7
+    e_o = orc.kernel()
+    assert ll.iterations == 7 == orc.iterations
+    assert abs(e - e_o) <= E_TOL and np.abs(ll.t1 - orc.t1).max() <= AMP_TOL
+    assert ll.t2.shape == (19, 5, 19, 5)
+    assert np.abs(np.asarray(ll.t2) - orc.t2).max() <= AMP_TOL
+
+
+def test_host_pointer_cabi_call():
+    """mpccb_updated_amps_host: the reference call with host arrays (t1 in; t1_new, res, dE out)."""
+    from oracle.mpcc_oracle import LowLevelOracle
+    mf, ll = _solver(8, 40, 120, 0.1)
+    orc = LowLevelOracle(mf, mode="blas")
+    t1 = 0.02 * np.random.default_rng(2).standard_normal((8, 40))
+    t1n = np.empty_like(t1)
+    res, dE = ctypes.c_double(), ctypes.c_double()
+    ll._ctx.call("mpccb_updated_amps_host", t1.ctypes.data, t1n.ctypes.data, ctypes.byref(res), ctypes.byref(dE))
+    r_o, e_o, t_o, _ = orc.updated_amps(t1)
+    assert abs(dE.value - e_o) <= E_TOL and abs(res.value - r_o) <= 1e-10 and np.abs(t1n - t_o).max() <= AMP_TOL
+
+
+@pytest.mark.parametrize("mnk", [(1, 1, 1), (17, 5, 3), (128, 128, 16), (129, 257, 70), (300, 64, 1000), (64, 300, 33)])
+def test_dmma_gemm_against_fp64_matmul(mnk):
+    import torch
+    from pyscf_mpcc_b200 import _cabi
+    m, n, k = mnk
+    ctx = _cabi.Context(2, 3, 4, 0, 3, 0)
+    g = torch.Generator(device="cuda").manual_seed(m * 7 + n)
+    a = torch.randn(m, k, dtype=torch.float64, device="cuda", generator=g)
+    b = torch.randn(n, k, dtype=torch.float64, device="cuda", generator=g)
+    c = torch.full((m, n), float("nan"), dtype=torch.float64, device="cuda")
+    ctx.call("mpccb_set_stream", torch.cuda.current_stream().cuda_stream)
+    ctx.call("mpccb_gemm_nt", a.data_ptr(), b.data_ptr(), c.data_ptr(), m, n, k)
+    torch.cuda.synchronize()
+    ref = a @ b.T
+    assert torch.isfinite(c).all()
+    assert (c - ref).abs().max().item() <= 1e-12 * max(1.0, ref.abs().max().item()) * max(1, k) ** 0.5

@@ -1,0 +1,149 @@
+"""Host-side logic of the package that needs no GPU: factory dispatch, sharding arithmetic,
+the DIIS bookkeeping (driven through a NumPy stand-in for the device kernels), flop counts."""
+import ctypes
+import os
+import types
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN
+import pyscf_mpcc_b200
+from pyscf_mpcc_b200 import sharding, flops
+from pyscf_mpcc_b200.diis import DIIS, AmplitudeVector, solve_diis_system
+from pyscf_mpcc_b200.synthetic import SyntheticMF, pack_lower
+
+
+def test_factory_rejects_unrestricted_and_non_df():
+    class UHF: pass
+    class GHF: pass
+    class RHF: with_df = None
+    with pytest.raises(RuntimeError, match="UMPCC is not implemented"):
+        pyscf_mpcc_b200.MPCC(UHF())
+    with pytest.raises(RuntimeError, match="GMPCC is not implemented"):
+        pyscf_mpcc_b200.MPCC(GHF())
+    with pytest.raises(RuntimeError, match="Chosen RMPCC variant is not implemented"):
+        pyscf_mpcc_b200.MPCC(RHF())
+
+
+def test_no_cpu_fallback():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        pyscf_mpcc_b200.MPCC(SyntheticMF(2, 3, 5))
+
+
+def test_synthetic_generator_contract():
+    mf = SyntheticMF(4, 10, 30, seed=0, scale=0.3)
+    assert mf.mol.nao == 14 and mf.mol.nelec == (4, 4) and mf.with_df.get_naoaux() == 30
+    blocks = list(mf.with_df.loop())
+    assert blocks[0].shape == (30, 14 * 15 // 2) and blocks[0].flags.c_contiguous
+    np.testing.assert_array_equal(blocks[0][3], pack_lower(mf._full[3]))
+    assert np.all(np.diff(mf.mo_energy[:4]) > 0) and mf.mo_energy[3] < -0.5 < 0.3 < mf.mo_energy[4]
+    np.testing.assert_array_equal(mf.get_fock(), np.diag(mf.mo_energy))
+    # first draws are part of the fixture contract (tests/golden was generated from them)
+    assert abs(mf._full[0, 0, 0] - 2 * 0.3 / np.sqrt(30) * np.random.default_rng(0).standard_normal()) < 1e-15
+    assert [b.shape[0] for b in SyntheticMF(2, 3, 500).with_df.loop()] == [240, 240, 20]
+
+
+@pytest.mark.parametrize("v,p", [(512, 8), (243, 4), (19, 2), (7, 7), (10, 3)])
+def test_slab_bounds_partition(v, p):
+    spans = [sharding.slab_bounds(v, p, r) for r in range(p)]
+    assert spans[0][0] == 0 and spans[-1][1] == v
+    assert all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
+    sizes = [e - b for b, e in spans]
+    assert max(sizes) - min(sizes) <= 1 and min(sizes) >= 1
+    o = 5
+    segs = [sharding.packed_segment(o, b, e) for b, e in spans]
+    nov = o * v
+    assert segs[0][0] == 0 and segs[-1][1] == nov * (nov + 1) // 2
+    assert sum(sharding.local_vector_length(o, v, b, e) - nov for b, e in spans) == nov * (nov + 1) // 2
+    with pytest.raises(ValueError):
+        sharding.slab_bounds(3, 4, 0)
+
+
+def test_solve_diis_system_matches_reference_branches():
+    h = np.array([[0.0, 1.0], [1.0, 2.5]])
+    np.testing.assert_allclose(solve_diis_system(h), [-2.5, 1.0])
+    # singular B (two identical error vectors) takes the pseudo-inverse branch (diis.py:257-259)
+    h = np.array([[0, 1, 1], [1, 1e-3, 1e-3], [1, 1e-3, 1e-3]], dtype=float)
+    c = solve_diis_system(h)
+    assert abs(c[1] + c[2] - 1.0) < 1e-9 and abs(c[1] - c[2]) < 1e-9
+
+
+class _FakeCtx:
+    """NumPy stand-in for mpccb_diis_push / mpccb_diis_combine so the ring/B-matrix logic of
+    pyscf_mpcc_b200.diis.DIIS can be pinned to the reference's DIIS fixture without a GPU."""
+
+    def __init__(self):
+        self.mem = {}
+        self.next = 1000
+
+    def alloc(self, arr):
+        self.next += 16
+        self.mem[self.next] = arr
+        return self.next
+
+    def call(self, name, *a):
+        if name == "mpccb_diis_push":
+            t1p, xprev, xs, es, elist, nd, slot, first, count_t1, dots = a
+            x = self.mem[t1p]
+            self.mem[xs][:] = x
+            if not first:
+                self.mem[es][:] = x - self.mem[xprev]
+                d = self.mem[dots]
+                for k in range(nd):
+                    ek = self.mem[es] if k == slot else self.mem[elist[k]]
+                    d[k] = float(np.dot(self.mem[es], ek))
+        elif name == "mpccb_diis_combine":
+            xl, coeff, nd, out, n = a
+            acc = np.zeros(n)
+            for k in range(nd):
+                acc += self.mem[xl[k]] * coeff[k]
+            self.mem[out][:] = acc
+        else:
+            raise AssertionError(name)
+
+
+class _FakeTensor:
+    def __init__(self, ctx, arr):
+        self.ctx, self.arr = ctx, arr
+        self.ptr = ctx.alloc(arr)
+
+    def data_ptr(self):
+        return self.ptr
+
+    def __getitem__(self, s):
+        return self
+
+    def numpy(self):
+        return self.arr
+
+    def copy_(self, other, non_blocking=False):
+        self.arr[:len(other.arr)] = other.arr
+        return self
+
+
+def test_device_diis_bookkeeping_against_reference_fixture(monkeypatch):
+    g = np.load(os.path.join(GOLDEN, "diis_kat.npz"))
+    n = g["inputs"].shape[1]
+    ctx = _FakeCtx()
+    ll = types.SimpleNamespace(_ctx=ctx, _vec_len_local=n, device="cpu", nov=n, _count_t1=True, world_size=1,
+                               _sync=lambda: None)
+    ll._dots_dev = _FakeTensor(ctx, np.zeros(7))
+    ll._dots_host = _FakeTensor(ctx, np.zeros(7))
+    d = DIIS()
+    monkeypatch.setattr(DIIS, "_alloc", lambda self, k, dev: _FakeTensor(ctx, np.zeros(k)))
+    for x, want in zip(g["inputs"], g["outputs"]):
+        out = d.update(AmplitudeVector(ll, vec=None, t1_dev=_FakeTensor(ctx, x.copy())))
+        np.testing.assert_allclose(out.vec.arr, want, rtol=1e-9, atol=1e-11)
+    np.testing.assert_allclose(d._H, g["H"], rtol=1e-10, atol=1e-14)
+    assert d._head == 3 and d.get_num_vec() == 6          # 9 pushes into a ring of 6 wrapped once
+
+
+def test_flop_and_byte_counts():
+    assert abs(flops.updated_amps_flops(64, 512, 1536) / 6.799e12 - 1) < 1e-3
+    assert flops.eris_flops(64, 512, 1536, 512) == 2.0 * 1536 * 32768 ** 2
+    n = 32768 + 32768 * 32769 // 2
+    assert flops.diis_bytes(64, 512, 6) == 8.0 * n * 16
