@@ -1,0 +1,236 @@
+// TMA-fed, warp-specialised FP64 DMMA GEMM for the two O(naux * nov^2) products of the DF-MPCC
+// iteration (reference pyscf/mpcc/dfrmpcc_lowlevel.py:135 "eris" and :138 "Yvo").
+//
+//   C[m, n] = sum_k A[m, k] * B[n, k],  A and B K-major in global memory.
+//
+// Blackwell has no tcgen05 kind for FP64, so the math is DMMA.8x8x4 from registers;
+// what is sm_100a-native here is the data path: one producer warp issues cp.async.bulk.tensor (TMA)
+// loads of 128-row x 16-k operand boxes into a 4-stage shared-memory ring (SWIZZLE_128B), completion
+// is signalled on mbarriers, and 16 consumer warps (4 per SM sub-partition, 32x32 accumulators each)
+// never touch global memory or block-wide barriers inside the K loop.
+//
+// Bank conflicts: a fragment load reads element (row, k = 4*ks + tig) for the 8 rows `g` of a group.
+// With the 128-byte swizzle the 16-byte chunk index is (k/2) ^ (row % 8); mapping fragment row g to
+// tile row rho(g) = {0,2,4,6,1,3,5,7}[g] makes the 16 lanes of each half-warp hit 16 distinct 8-byte
+// banks. rho is a permutation inside every 8-row group, applied to both operands; the epilogues
+// simply use the permuted coordinates.
+#pragma once
+#include <cuda.h>
+
+#include "gemm_dmma.cuh"
+
+namespace mpccb {
+
+constexpr int TMA_TM = 128, TMA_TN = 128, TMA_TK = 16;
+constexpr int TMA_STAGES = 4;
+constexpr int TMA_CONSUMER_WARPS = 16;
+constexpr int TMA_THREADS = (TMA_CONSUMER_WARPS + 1) * 32;
+constexpr int TMA_STAGE_BYTES = (TMA_TM + TMA_TN) * TMA_TK * 8;   // 32 KB
+constexpr int TMA_RING_BYTES = TMA_STAGES * TMA_STAGE_BYTES;       // 128 KB
+constexpr int TMA_BAR_BYTES = 128;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_4d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1,
+                                            int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+      ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+
+// fragment row g (0..7) -> tile row inside its 8-row group
+__device__ __forceinline__ int rho(int g) { return ((g & 3) << 1) | (g >> 2); }
+
+// 8-byte element (row, k) of a [rows][16] swizzle-128B tile, as a double index
+__device__ __forceinline__ int swz(int row, int k) { return row * 16 + ((((k >> 1) ^ (row & 7)) << 1) | (k & 1)); }
+
+struct TmaGemmParams {
+  int M, N;              // valid rows of A / B for this launch
+  int tm_eff, tn_eff;    // rows a tile advances by
+  int tiles_m, tiles_n;
+  int nk;                // number of 16-wide K steps
+  // A-operand addressing: mode 0 = 2-D map (k, row); mode 1 = 4-D map over T[a][b][i][j]:
+  //   k step kt -> (b = kt / jsteps, j0 = 16 * (kt % jsteps)), rows = (a, i)
+  int a_mode, jsteps, o, n_a;
+  uint32_t a_bytes, b_bytes;   // bytes one stage receives for A / B (box sizes)
+  // plain store epilogue
+  double* C;
+  i64 ldc;
+};
+
+// EPI: 0 = plain row-major store (Yvo), 1 = fused eris -> t2 epilogue
+template <int EPI>
+__global__ void __launch_bounds__(TMA_THREADS, 1)
+gemm_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
+                TmaGemmParams p, T2Params t2p) {
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  double* ring = reinterpret_cast<double*>(smem_raw);
+  constexpr size_t STAGE_AREA = (EPI == 1 && sizeof(double) * TMA_TM * (TMA_TN + 1) > (size_t)TMA_RING_BYTES)
+                                    ? sizeof(double) * TMA_TM * (TMA_TN + 1)
+                                    : (size_t)TMA_RING_BYTES;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + STAGE_AREA);
+  uint64_t* empty = full + TMA_STAGES;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  int tm, tn;
+  tile_coords(blockIdx.x, p.tiles_m, p.tiles_n, tm, tn);
+  const int m0 = tm * p.tm_eff, n0 = tn * p.tn_eff;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < TMA_STAGES; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], TMA_CONSUMER_WARPS);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  __syncthreads();
+
+  if (warp == TMA_CONSUMER_WARPS) {
+    // ===== producer warp: one lane feeds the ring =====
+    if (lane == 0) {
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&mapA) : "memory");
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&mapB) : "memory");
+      for (int kt = 0; kt < p.nk; ++kt) {
+        const int s = kt % TMA_STAGES;
+        const uint32_t use = kt / TMA_STAGES;
+        if (use > 0) mbar_wait(&empty[s], (use - 1) & 1);
+        double* a_dst = ring + s * (TMA_STAGE_BYTES / 8);
+        double* b_dst = a_dst + TMA_TM * TMA_TK;
+        mbar_expect_tx(&full[s], p.a_bytes + p.b_bytes);
+        if (p.a_mode == 0) {
+          tma_load_2d(a_dst, &mapA, &full[s], kt * TMA_TK, m0);
+        } else {
+          const int b = kt / p.jsteps, j0 = (kt - b * p.jsteps) * TMA_TK;
+          tma_load_4d(a_dst, &mapA, &full[s], j0, 0, b, tm * p.n_a);
+        }
+        tma_load_2d(b_dst, &mapB, &full[s], kt * TMA_TK, n0);
+      }
+    }
+    __syncwarp();
+    if (EPI == 0) return;          // plain epilogue needs no block-wide sync afterwards
+  }
+
+  double acc[4][4][2];
+  const int g = lane >> 2, tig = lane & 3;
+  const int wm = warp >> 2, wn = warp & 3;     // 4 x 4 consumer warps, 32 x 32 each
+  if (warp < TMA_CONSUMER_WARPS) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) { acc[i][j][0] = 0.0; acc[i][j][1] = 0.0; }
+    const int rg = rho(g);
+    for (int kt = 0; kt < p.nk; ++kt) {
+      const int s = kt % TMA_STAGES;
+      mbar_wait(&full[s], (kt / TMA_STAGES) & 1);
+      const double* as = ring + s * (TMA_STAGE_BYTES / 8);
+      const double* bs = as + TMA_TM * TMA_TK;
+#pragma unroll
+      for (int ks = 0; ks < TMA_TK / 4; ++ks) {
+        double a[4], b[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) a[i] = as[swz(wm * 32 + i * 8 + rg, ks * 4 + tig)];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) b[j] = bs[swz(wn * 32 + j * 8 + rg, ks * 4 + tig)];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty[s]);
+    }
+  }
+
+  if (EPI == 0) {
+    // C[m][n] row-major; fragment (row g, cols 2*tig, 2*tig+1) sits at tile (rho(g), rho(2*tig + c))
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int ml = wm * 32 + i * 8 + rho(g);
+      const int m = m0 + ml;
+      if (ml >= p.tm_eff || m >= p.M) continue;
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          const int nl = wn * 32 + j * 8 + rho(2 * tig + c);
+          const int n = n0 + nl;
+          if (nl < p.tn_eff && n < p.N) p.C[(i64)m * p.ldc + n] = acc[i][j][c];
+        }
+    }
+  } else {
+    // all consumers have drained the ring (every full barrier was waited on) before the staging
+    // buffer, which aliases it, is written
+    __syncthreads();
+    constexpr int PITCH = TMA_TN + 1;
+    double* S = reinterpret_cast<double*>(smem_raw);
+    if (warp < TMA_CONSUMER_WARPS) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+#pragma unroll
+          for (int c = 0; c < 2; ++c)
+            S[(wm * 32 + i * 8 + rho(g)) * PITCH + wn * 32 + j * 8 + rho(2 * tig + c)] = acc[i][j][c];
+    }
+    __syncthreads();
+    const int o = t2p.o;
+    const int nwarps = TMA_THREADS / 32;
+    const int mslab = (t2p.a_end - t2p.a_begin) * o;
+    for (int r = warp; r < p.tm_eff; r += nwarps) {
+      const int al = r / o, i = r - al * o;
+      const int a = t2p.a_begin + tm * t2p.n_a + al;
+      if (a >= t2p.a_end) break;
+      const double dai = t2p.ev[a] - t2p.eo[i];
+      double fsum = 0.0;
+      for (int bl = 0; bl < t2p.n_b; ++bl) {
+        const int b = tn * t2p.n_b + bl;
+        if (b >= t2p.v) break;
+        const double evb = t2p.ev[b];
+        double* trow = t2p.T + (((i64)(a - t2p.a_begin) * t2p.v + b) * o + i) * o;
+        const double* frow = t2p.Fvo + (i64)b * o;
+        for (int j = lane; j < o; j += 32) {
+          const double e1 = S[r * PITCH + bl * o + j];
+          const double e2 = S[(al * o + j) * PITCH + bl * o + i];
+          const double den = -dai - (evb - t2p.eo[j]);
+          const double tv = (2.0 * e1 - e2) / den;
+          trow[j] = tv;
+          fsum += tv * frow[j];
+        }
+      }
+      fsum = warp_sum(fsum);
+      if (lane == 0) t2p.OmP[(i64)tn * mslab + (i64)(a - t2p.a_begin) * o + i] = fsum;
+    }
+  }
+}
+
+}  // namespace mpccb

@@ -4,6 +4,7 @@
 // HBM-bound kernels on one stream.
 #include "../../include/mpcc_b200.h"
 #include "gemm_dmma.cuh"
+#include "gemm_tma.cuh"
 #include "kernels_elem.cuh"
 
 #include <algorithm>
@@ -425,7 +426,105 @@ extern "C" int mpccb_dress(mpccb_ctx* c, const double* t1_dev) {
 // ===========================================================================
 namespace {
 
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+// cuTensorMapEncodeTiled through the runtime's driver entry point: no link-time dependency on libcuda,
+// so the library still loads on a machine without a driver (symbol/ABI tests).
+EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+// rank-`rank` FP64 tensor, dims/box innermost first, strides in bytes for dims 1.., 128-byte swizzle
+int make_tensor_map(mpccb_ctx* c, CUtensorMap* map, const double* base, int rank, const cuuint64_t* dims,
+                    const cuuint64_t* strides_bytes, const cuuint32_t* box) {
+  EncodeTiledFn fn = encode_tiled_fn();
+  if (!fn) return fail(c, "cuTensorMapEncodeTiled is not available from this driver");
+  cuuint32_t ones[5] = {1, 1, 1, 1, 1};
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, (cuuint32_t)rank, const_cast<double*>(base), dims,
+                  strides_bytes, box, ones, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(c, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+  return 0;
+}
+
+int make_map_2d(mpccb_ctx* c, CUtensorMap* map, const double* base, i64 K, i64 rows, i64 ld, int box_rows) {
+  cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * 8};
+  cuuint32_t box[2] = {(cuuint32_t)TMA_TK, (cuuint32_t)box_rows};
+  return make_tensor_map(c, map, base, 2, dims, strides, box);
+}
+
+template <int EPI>
+int launch_tma(mpccb_ctx* c, const char* what, const CUtensorMap& mA, const CUtensorMap& mB,
+               const TmaGemmParams& p, const T2Params& t2p) {
+  const size_t smem = (EPI == 1 ? std::max<size_t>(sizeof(double) * TMA_TM * (TMA_TN + 1), TMA_RING_BYTES)
+                                : (size_t)TMA_RING_BYTES) + TMA_BAR_BYTES;
+  static bool attr_done = false;
+  if (!attr_done) {
+    CUDA_OK(c, cudaFuncSetAttribute(gemm_tma_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr_done = true;
+  }
+  gemm_tma_kernel<EPI><<<p.tiles_m * p.tiles_n, TMA_THREADS, smem, c->stream>>>(mA, mB, p, t2p);
+  LAUNCH_OK(c, what);
+  return 0;
+}
+
+int launch_eris_t2_tma(mpccb_ctx* c) {
+  const int o = c->o, v = c->v, L = c->L;
+  CUtensorMap mA, mB;
+  if (make_map_2d(c, &mA, c->JK + (i64)c->a_begin * o * c->ldk, L, (i64)c->na * o, c->ldk, TMA_TM)) return 1;
+  if (make_map_2d(c, &mB, c->JK, L, (i64)v * o, c->ldk, TMA_TN)) return 1;
+  T2Params t;
+  t.T = c->T; t.eo = c->eo; t.ev = c->ev; t.Fvo = c->Fvo; t.OmP = c->OmP;
+  t.o = o; t.v = v; t.a_begin = c->a_begin; t.a_end = c->a_end; t.n_a = c->t2_na; t.n_b = c->t2_nb;
+  TmaGemmParams p;
+  memset(&p, 0, sizeof(p));
+  p.M = c->na * o; p.N = v * o;
+  p.tm_eff = c->t2_na * o; p.tn_eff = c->t2_nb * o;
+  p.tiles_m = c->t2_tiles_m; p.tiles_n = c->t2_tiles_n;
+  p.nk = cdiv(L, TMA_TK);
+  p.a_mode = 0;
+  p.a_bytes = TMA_TM * TMA_TK * 8; p.b_bytes = TMA_TN * TMA_TK * 8;
+  return launch_tma<1>(c, "gemm_tma_kernel<t2>", mA, mB, p, t);
+}
+
+int launch_yvo_tma(mpccb_ctx* c) {
+  const int o = c->o, v = c->v, L = c->L;
+  const int n_a = 128 / o;
+  CUtensorMap mA, mB;
+  {  // T[a][b][i][j], box = (16 j, o i, 1 b, n_a a) -> smem rows (a,i) x 16 k
+    cuuint64_t dims[4] = {(cuuint64_t)o, (cuuint64_t)o, (cuuint64_t)v, (cuuint64_t)c->na};
+    cuuint64_t strides[3] = {(cuuint64_t)o * 8, (cuuint64_t)o * o * 8, (cuuint64_t)v * o * o * 8};
+    cuuint32_t box[4] = {(cuuint32_t)TMA_TK, (cuuint32_t)o, 1, (cuuint32_t)n_a};
+    if (make_tensor_map(c, &mA, c->T, 4, dims, strides, box)) return 1;
+  }
+  if (make_map_2d(c, &mB, c->Lvo, (i64)v * o, L, (i64)v * o, TMA_TN)) return 1;
+  TmaGemmParams p;
+  memset(&p, 0, sizeof(p));
+  p.M = c->na * o; p.N = L;
+  p.tm_eff = n_a * o; p.tn_eff = TMA_TN;
+  p.tiles_m = cdiv(c->na, n_a); p.tiles_n = cdiv(L, TMA_TN);
+  p.nk = v * (o / TMA_TK);
+  p.a_mode = 1; p.jsteps = o / TMA_TK; p.o = o; p.n_a = n_a;
+  p.a_bytes = (uint32_t)(TMA_TK * o * n_a * 8); p.b_bytes = TMA_TN * TMA_TK * 8;
+  p.C = c->Y + (i64)c->a_begin * o * L; p.ldc = L;
+  T2Params t;
+  memset(&t, 0, sizeof(t));
+  return launch_tma<0>(c, "gemm_tma_kernel<store>", mA, mB, p, t);
+}
+
 int launch_eris_t2(mpccb_ctx* c) {
+  if (c->use_tma) return launch_eris_t2_tma(c);
   typedef CfgBigKK Cfg;
   const int o = c->o, v = c->v, L = c->L;
   Operand A = flat_operand(c->JK + (i64)c->a_begin * o * c->ldk, c->na * o, c->ldk, 1);
@@ -451,6 +550,7 @@ int launch_eris_t2(mpccb_ctx* c) {
 
 int launch_yvo(mpccb_ctx* c) {
   const int o = c->o, v = c->v, L = c->L;
+  if (c->use_tma && o % TMA_TK == 0) return launch_yvo_tma(c);
   // :138  Y[(a,i)][L] = sum_{(b,j)} T[a][b][i][j] Lvo[L][(b,j)]
   Operand A;
   A.base = c->T; A.rows = c->na * o;
