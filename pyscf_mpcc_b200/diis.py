@@ -149,10 +149,16 @@ class AmplitudeVector:
         return out
 
     def numpy(self):
-        if self.solver.world_size > 1:
-            raise NotImplementedError("gather of a sharded amplitude vector")
+        """The reference's flat host vector. With several ranks this is a collective call
+        (the packed t2 segments are all-gathered; the t1 part is replicated)."""
+        ll = self.solver
         v = self.packed_device()
-        self.solver._sync()
+        if ll.world_size > 1:
+            from . import sharding
+            lens = [sharding.local_vector_length(ll.nocc, ll.nvir, *sharding.slab_bounds(ll.nvir, ll.world_size, r))
+                    - ll.nov for r in range(ll.world_size)]
+            v = torch.cat([v[:ll.nov], ll._gather_flat(v[ll.nov:], lens)])
+        ll._sync()
         return v.cpu().numpy()
 
     def __array__(self, dtype=None, copy=None):

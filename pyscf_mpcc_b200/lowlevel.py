@@ -52,24 +52,43 @@ class DeviceT2:
         self.ndim = 4
 
     def numpy(self):
+        """Full host tensor. With several ranks this is a collective call: every rank
+        contributes its slab (all-gather over the solver's process group)."""
         ll = self.solver
-        if ll.world_size > 1:
-            raise NotImplementedError("gather of sharded t2; read the local slab with local_numpy()")
-        return self.local_numpy()
+        if ll.world_size == 1:
+            return self.local_numpy()
+        o, v = ll.nocc, ll.nvir
+        if self.layout == "aibj":
+            slab = self._local_device()                      # (na, o, v, o)
+            return ll._gather_rows(slab.reshape(ll._na, -1), v).reshape(v, o, v, o).cpu().numpy()
+        seg = self.packed                                    # local packed rows of the lower triangle
+        full = ll._gather_flat(seg, [sharding.local_vector_length(o, v, *sharding.slab_bounds(v, ll.world_size, r))
+                                     - ll.nov for r in range(ll.world_size)])
+        out = torch.empty((o, o, v, v), dtype=torch.float64, device=ll.device)
+        ll._ctx.call("mpccb_unpack_oovv", full.data_ptr(), out.data_ptr())
+        ll._sync()
+        return out.cpu().numpy()
+
+    def _local_device(self):
+        ll = self.solver
+        o, v = ll.nocc, ll.nvir
+        if self.serial != ll._t2_serial:
+            raise RuntimeError("this t2 handle is stale: the device buffer was overwritten by a later updated_amps()")
+        out = torch.empty((ll._na, o, v, o), dtype=torch.float64, device=ll.device)
+        ll._ctx.call("mpccb_t2_to_aibj", out.data_ptr())
+        ll._sync()
+        return out
 
     def local_numpy(self):
+        """This rank's part: the (na,o,v,o) slab for "aibj"; the whole (o,o,v,v) tensor on one rank."""
         ll = self.solver
         o, v = ll.nocc, ll.nvir
         if self.layout == "aibj":
-            if self.serial != ll._t2_serial:
-                raise RuntimeError("this t2 handle is stale: the device buffer was overwritten by a later updated_amps()")
-            out = torch.empty((ll._na, o, v, o), dtype=torch.float64, device=ll.device)
-            ll._ctx.call("mpccb_t2_to_aibj", out.data_ptr())
-        else:
-            if ll.world_size > 1:
-                raise NotImplementedError("oovv unpack of a sharded vector")
-            out = torch.empty((o, o, v, v), dtype=torch.float64, device=ll.device)
-            ll._ctx.call("mpccb_unpack_oovv", self.packed.data_ptr(), out.data_ptr())
+            return self._local_device().cpu().numpy()
+        if ll.world_size > 1:
+            raise RuntimeError("the (o,o,v,v) form of a sharded vector needs the collective numpy()")
+        out = torch.empty((o, o, v, v), dtype=torch.float64, device=ll.device)
+        ll._ctx.call("mpccb_unpack_oovv", self.packed.data_ptr(), out.data_ptr())
         ll._sync()
         return out.cpu().numpy()
 
@@ -201,6 +220,25 @@ class MPCC_LL:
     def _host_attr(self, name):
         self._sync()
         return self._d[name].cpu().numpy()
+
+    def _gather_flat(self, seg, lengths):
+        """All-gather of per-rank 1-D device segments of unequal `lengths` (padded to the longest)."""
+        n = max(lengths)
+        pad = torch.zeros(n, dtype=torch.float64, device=self.device)
+        pad[:seg.numel()].copy_(seg.reshape(-1))
+        parts = [torch.empty_like(pad) for _ in range(self.world_size)]
+        self._sync()
+        torch.distributed.all_gather(parts, pad, group=self.group)
+        return torch.cat([p[:k] for p, k in zip(parts, lengths)])
+
+    def _gather_rows(self, slab, nvir):
+        """All-gather of the per-rank (na_r, width) row slabs into (nvir, width)."""
+        width = slab.shape[1]
+        lens = []
+        for r in range(self.world_size):
+            a0, a1 = sharding.slab_bounds(nvir, self.world_size, r)
+            lens.append((a1 - a0) * width)
+        return self._gather_flat(slab.reshape(-1), lens).reshape(nvir, width)
 
     # host-readable views of the device-resident tensors (reference attribute names, :66-69,:36-37)
     Loo = property(lambda self: self._host_attr("Loo"))
