@@ -58,6 +58,17 @@ def parse_args():
     return ap.parse_args()
 
 
+def ncu_traffic(o, v, L, world):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one launch of the dominant kernel from the committed
+    `ncu --set full` capture (profiles/ncu_traffic.json, written from the .ncu-rep); None for shapes not captured."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            tab = json.load(f)
+        return tab.get(f"{o},{v},{L},{world}", {}).get("eris_t2_bytes")
+    except Exception:
+        return None
+
+
 class ClockSampler:
     """nvidia-smi clocks/throttle reasons during the timed region (B200_PROFILING.md recipe)."""
 
@@ -241,7 +252,7 @@ def run_b200(args):
     if rank == 0:
         sampler.start()
     t1 = torch.zeros(nov, dtype=torch.float64, device=dev)
-    adiis = DIIS()
+    adiis = DIIS().reserve(ll)          # history buffers allocated before the timed region
     trace = []
     launches0 = ctx.launch_count()
     e0 = torch.cuda.Event(enable_timing=True)
@@ -262,7 +273,7 @@ def run_b200(args):
     # ---- e2e: the public API with host numpy amplitudes in and out each step ----
     ll.h2d_bytes = ll.d2h_bytes = 0
     ll.t1 = np.zeros((o, v))
-    adiis = DIIS()
+    adiis = DIIS().reserve(ll)
     barrier()
     e0.record()
     for _ in range(K):
@@ -285,9 +296,10 @@ def run_b200(args):
     er_tf = F.eris_flops(o, v, L, na) / (er_ms / max(er_n, 1) * 1e-3) * 1e-12
     yv_tf = F.yvo_flops(o, v, L, na) / (yv_ms / max(yv_n, 1) * 1e-3) * 1e-12
     roofline = {
-        "bound": "tensor", "kernel": "gemm_t2_kernel (fused eris -> t2, DMMA.8x8x4)",
+        "bound": "tensor", "kernel": ("gemm_tma_kernel<1>" if not args.no_tma else "gemm_t2_kernel")
+                                     + " (fused eris -> t2, TMA-fed DMMA.8x8x4)",
         "achieved": er_tf, "peak": FP64_PEAK_TFLOPS_MEASURED, "unit": "TFLOP/s",
-        "frac": er_tf / FP64_PEAK_TFLOPS_MEASURED, "traffic": None,
+        "frac": er_tf / FP64_PEAK_TFLOPS_MEASURED, "traffic": ncu_traffic(o, v, L, world),
         "peak_source": "cuBLAS DGEMM 32768x8192x1536 measured on this pool's B200 (FP64; MEASURED_PEAKS.json has "
                        "only bf16); nominal 37.2",
         "frac_of_nominal": er_tf / FP64_PEAK_TFLOPS_NOMINAL,

@@ -49,8 +49,13 @@ int mpccb_bind_integrals(mpccb_ctx* ctx, const double* Loo_dev, const double* Lo
 int mpccb_bind_t2(mpccb_ctx* ctx, double* t2_abij_dev);
 
 /* ---- one residual evaluation: MPCC_LL.updated_amps (dfrmpcc_lowlevel.py:103-152) --- */
-/* phase 1, :119-133 — T1 dressing, singles intermediates, Fov (rank-replicated work) */
+/* phase 1, :119-133 — T1 dressing and singles intermediates. Everything that carries a virtual index is
+ * computed for the context's slab only (rows [a_begin*o, a_end*o) of JK = Jvo in [(a,i)][ldk] order,
+ * ldk = naux rounded up to even). A whole-range context (one rank) also runs mpccb_dress_post itself. */
 int mpccb_dress(mpccb_ctx* ctx, const double* t1_dev);
+/* phase 1b — several ranks: after the caller has all-gathered the JK rows of all slabs (buffer "JK" of
+ * mpccb_get_buffer; slabs are contiguous row ranges), form w = Jvo.X and Fov for every (b,j) (:128,:133) */
+int mpccb_dress_post(mpccb_ctx* ctx);
 /* phase 2, :135-147 — eris/t2 (fused), Yvo, doubles->singles, energy, for the local slab.
  * Writes the slab's partial sums to red_dev[0..nov) = Omega part [a,i], red_dev[nov] = dE part;
  * with several ranks the caller all-reduces red_dev (nov+1 doubles) before phase 3. */
@@ -99,7 +104,10 @@ int mpccb_profile_stages(void);
 const char* mpccb_profile_stage_name(int stage);
 int mpccb_profile_read(mpccb_ctx* ctx, double* ms_out, long long* count_out);
 /* option by name: "tma" (0/1 use the TMA-fed kernels when shapes allow; default 1),
- * "profile" (0/1 record stage timings; default 0) */
+ * "profile" (0/1 record stage timings; default 0), "t2_wide_tiles" (1: 128x128 tiles / one CTA per SM for the
+ * fused eris->t2 GEMM, 0: 128x64 tiles / two CTAs per SM; default: the better-filled shape; set before bind_workspace), "t2_unfused" (1: GEMM into the t2 buffer + in-place
+ * t2 pass instead of the fused epilogue; default: only when whole (i,j) blocks fill the tile < 70 %, e.g. nocc = 80,
+ * or nocc > 128) */
 int mpccb_set_option(mpccb_ctx* ctx, const char* name, long long value);
 /* standalone C[m,n] = sum_k A[m,k] B[n,k] through the generic DMMA kernel (row-major, test hook) */
 int mpccb_gemm_nt(mpccb_ctx* ctx, const double* A_dev, const double* B_dev, double* C_dev,

@@ -33,6 +33,7 @@ SIGNATURES = {
     "mpccb_bind_integrals": (c_int, [c_void_p] + [c_void_p] * 7),
     "mpccb_bind_t2": (c_int, [c_void_p, c_void_p]),
     "mpccb_dress": (c_int, [c_void_p, c_void_p]),
+    "mpccb_dress_post": (c_int, [c_void_p]),
     "mpccb_doubles": (c_int, [c_void_p, c_void_p]),
     "mpccb_finish": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p]),
     "mpccb_updated_amps_host": (c_int, [c_void_p, c_void_p, c_void_p, c_double_p, c_double_p]),

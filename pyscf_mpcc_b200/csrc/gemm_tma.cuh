@@ -21,13 +21,23 @@
 
 namespace mpccb {
 
-constexpr int TMA_TM = 128, TMA_TN = 128, TMA_TK = 16;
+constexpr int TMA_TM = 128, TMA_TK = 16;
 constexpr int TMA_STAGES = 4;
-constexpr int TMA_CONSUMER_WARPS = 16;
-constexpr int TMA_THREADS = (TMA_CONSUMER_WARPS + 1) * 32;
-constexpr int TMA_STAGE_BYTES = (TMA_TM + TMA_TN) * TMA_TK * 8;   // 32 KB
-constexpr int TMA_RING_BYTES = TMA_STAGES * TMA_STAGE_BYTES;       // 128 KB
 constexpr int TMA_BAR_BYTES = 128;
+
+// WN = consumer warps along N (32 columns each): 4 -> 128 x 128 tile, 16 warps, one CTA per SM;
+// 2 -> 128 x 64 tile, 8 warps, two CTAs per SM (one CTA's epilogue overlaps the other's K loop).
+template <int WN>
+struct TmaCfg {
+  static constexpr int TN = 32 * WN;
+  static constexpr int WARPS = 4 * WN;
+  static constexpr int THREADS = WARPS * 32;
+  static constexpr int MIN_CTAS = (WN == 2) ? 2 : 1;
+  static constexpr int STAGE_BYTES = (TMA_TM + TN) * TMA_TK * 8;
+  static constexpr int RING_BYTES = TMA_STAGES * STAGE_BYTES;
+  static constexpr int STAGING_BYTES = 8 * TMA_TM * (TN + 1);      // fused-t2 epilogue staging (aliases the ring)
+  static constexpr int AREA_EPI1 = STAGING_BYTES > RING_BYTES ? STAGING_BYTES : RING_BYTES;
+};
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
@@ -87,16 +97,18 @@ struct TmaGemmParams {
   i64 ldc;
 };
 
-// EPI: 0 = plain row-major store (Yvo), 1 = fused eris -> t2 epilogue
-template <int EPI>
-__global__ void __launch_bounds__(TMA_THREADS, 1)
+// EPI: 0 = plain row-major store (Yvo), 1 = fused eris -> t2 epilogue.
+// Every warp is a consumer; lane 0 of warp 0 doubles as the TMA producer: at the top of K step kt it
+// refills the stage that all warps released at the end of step kt-1 with the operands of step
+// kt + STAGES-1. No 17th warp, so a sub-partition holds 4 (or 2 x 2) warps and ptxas gets 128 registers.
+template <int EPI, int WN>
+__global__ void __launch_bounds__(TmaCfg<WN>::THREADS, TmaCfg<WN>::MIN_CTAS)
 gemm_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
                 TmaGemmParams p, T2Params t2p) {
+  typedef TmaCfg<WN> Cfg;
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   double* ring = reinterpret_cast<double*>(smem_raw);
-  constexpr size_t STAGE_AREA = (EPI == 1 && sizeof(double) * TMA_TM * (TMA_TN + 1) > (size_t)TMA_RING_BYTES)
-                                    ? sizeof(double) * TMA_TM * (TMA_TN + 1)
-                                    : (size_t)TMA_RING_BYTES;
+  constexpr size_t STAGE_AREA = (EPI == 1) ? (size_t)Cfg::AREA_EPI1 : (size_t)Cfg::RING_BYTES;
   uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + STAGE_AREA);
   uint64_t* empty = full + TMA_STAGES;
 
@@ -104,71 +116,74 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
   int tm, tn;
   tile_coords(blockIdx.x, p.tiles_m, p.tiles_n, tm, tn);
   const int m0 = tm * p.tm_eff, n0 = tn * p.tn_eff;
+  const bool producer = (threadIdx.x == 0);
 
-  if (threadIdx.x == 0) {
+  auto issue = [&](int kt) {
+    const int s = kt % TMA_STAGES;
+    double* a_dst = ring + s * (Cfg::STAGE_BYTES / 8);
+    double* b_dst = a_dst + TMA_TM * TMA_TK;
+    mbar_expect_tx(&full[s], p.a_bytes + p.b_bytes);
+    if (p.a_mode == 0) {
+      tma_load_2d(a_dst, &mapA, &full[s], kt * TMA_TK, m0);
+    } else {
+      const int b = kt / p.jsteps, j0 = (kt - b * p.jsteps) * TMA_TK;
+      tma_load_4d(a_dst, &mapA, &full[s], j0, 0, b, tm * p.n_a);
+    }
+    tma_load_2d(b_dst, &mapB, &full[s], kt * TMA_TK, n0);
+  };
+
+  if (producer) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&mapA) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&mapB) : "memory");
     for (int s = 0; s < TMA_STAGES; ++s) {
       mbar_init(&full[s], 1);
-      mbar_init(&empty[s], TMA_CONSUMER_WARPS);
+      mbar_init(&empty[s], Cfg::WARPS);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    for (int kt = 0; kt < TMA_STAGES - 1 && kt < p.nk; ++kt) issue(kt);
   }
   __syncthreads();
 
-  if (warp == TMA_CONSUMER_WARPS) {
-    // ===== producer warp: one lane feeds the ring =====
-    if (lane == 0) {
-      asm volatile("prefetch.tensormap [%0];" ::"l"(&mapA) : "memory");
-      asm volatile("prefetch.tensormap [%0];" ::"l"(&mapB) : "memory");
-      for (int kt = 0; kt < p.nk; ++kt) {
-        const int s = kt % TMA_STAGES;
-        const uint32_t use = kt / TMA_STAGES;
-        if (use > 0) mbar_wait(&empty[s], (use - 1) & 1);
-        double* a_dst = ring + s * (TMA_STAGE_BYTES / 8);
-        double* b_dst = a_dst + TMA_TM * TMA_TK;
-        mbar_expect_tx(&full[s], p.a_bytes + p.b_bytes);
-        if (p.a_mode == 0) {
-          tma_load_2d(a_dst, &mapA, &full[s], kt * TMA_TK, m0);
-        } else {
-          const int b = kt / p.jsteps, j0 = (kt - b * p.jsteps) * TMA_TK;
-          tma_load_4d(a_dst, &mapA, &full[s], j0, 0, b, tm * p.n_a);
-        }
-        tma_load_2d(b_dst, &mapB, &full[s], kt * TMA_TK, n0);
+  double acc[4][4][2];
+  const int g = lane >> 2, tig = lane & 3;
+  const int wm = warp / WN, wn = warp % WN;     // 4 x WN warps, 32 x 32 each
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { acc[i][j][0] = 0.0; acc[i][j][1] = 0.0; }
+  const int rg = rho(g);
+  const int arow = (wm * 32 + rg) * 16, brow = (wn * 32 + rg) * 16;
+  for (int kt = 0; kt < p.nk; ++kt) {
+    if (producer) {
+      const int kp = kt + TMA_STAGES - 1;
+      if (kp < p.nk) {
+        if (kt > 0) mbar_wait(&empty[kp % TMA_STAGES], ((kp / TMA_STAGES) - 1) & 1);
+        issue(kp);
       }
     }
     __syncwarp();
-    if (EPI == 0) return;          // plain epilogue needs no block-wide sync afterwards
-  }
-
-  double acc[4][4][2];
-  const int g = lane >> 2, tig = lane & 3;
-  const int wm = warp >> 2, wn = warp & 3;     // 4 x 4 consumer warps, 32 x 32 each
-  if (warp < TMA_CONSUMER_WARPS) {
+    const int s = kt % TMA_STAGES;
+    mbar_wait(&full[s], (kt / TMA_STAGES) & 1);
+    const double* as = ring + s * (Cfg::STAGE_BYTES / 8) + arow;
+    const double* bs = ring + s * (Cfg::STAGE_BYTES / 8) + TMA_TM * TMA_TK + brow;
 #pragma unroll
-    for (int i = 0; i < 4; ++i)
+    for (int ks = 0; ks < TMA_TK / 4; ++ks) {
+      // swizzle-128B: 16-byte chunk (k/2) ^ (row % 8); row % 8 == rg for every fragment row of this lane
+      const int kk = ks * 4 + tig;
+      const int col = ((((kk >> 1) ^ rg) << 1) | (kk & 1));
+      double a[4], b[4];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) { acc[i][j][0] = 0.0; acc[i][j][1] = 0.0; }
-    const int rg = rho(g);
-    for (int kt = 0; kt < p.nk; ++kt) {
-      const int s = kt % TMA_STAGES;
-      mbar_wait(&full[s], (kt / TMA_STAGES) & 1);
-      const double* as = ring + s * (TMA_STAGE_BYTES / 8);
-      const double* bs = as + TMA_TM * TMA_TK;
+      for (int i = 0; i < 4; ++i) a[i] = as[i * 128 + col];
 #pragma unroll
-      for (int ks = 0; ks < TMA_TK / 4; ++ks) {
-        double a[4], b[4];
+      for (int j = 0; j < 4; ++j) b[j] = bs[j * 128 + col];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) a[i] = as[swz(wm * 32 + i * 8 + rg, ks * 4 + tig)];
+      for (int i = 0; i < 4; ++i)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) b[j] = bs[swz(wn * 32 + j * 8 + rg, ks * 4 + tig)];
-#pragma unroll
-        for (int i = 0; i < 4; ++i)
-#pragma unroll
-          for (int j = 0; j < 4; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
-      }
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&empty[s]);
+        for (int j = 0; j < 4; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
     }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&empty[s]);
   }
 
   if (EPI == 0) {
@@ -191,9 +206,9 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
     // all consumers have drained the ring (every full barrier was waited on) before the staging
     // buffer, which aliases it, is written
     __syncthreads();
-    constexpr int PITCH = TMA_TN + 1;
+    constexpr int PITCH = Cfg::TN + 1;
     double* S = reinterpret_cast<double*>(smem_raw);
-    if (warp < TMA_CONSUMER_WARPS) {
+    {
 #pragma unroll
       for (int i = 0; i < 4; ++i)
 #pragma unroll
@@ -204,7 +219,7 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
     }
     __syncthreads();
     const int o = t2p.o;
-    const int nwarps = TMA_THREADS / 32;
+    const int nwarps = Cfg::WARPS;
     const int mslab = (t2p.a_end - t2p.a_begin) * o;
     for (int r = warp; r < p.tm_eff; r += nwarps) {
       const int al = r / o, i = r - al * o;

@@ -48,16 +48,17 @@ k_dress_finalize(const double* __restrict__ Xov, const double* __restrict__ Lov,
                  const double* __restrict__ JT, const double* __restrict__ XT,
                  const double* __restrict__ X, const double* __restrict__ t1,
                  double* __restrict__ JK, double* __restrict__ E1K, double* __restrict__ Wov,
-                 int L, int o, int v, int ldk) {
+                 int L, int o, int v, int ldk, int a_lo, int a_hi) {
+  // only the virtual columns a in [a_lo, a_hi) (this rank's slab) are produced; grid.x covers the slab
   __shared__ double tj[32][33];
   __shared__ double te[32][33];
   const int i = blockIdx.z;
-  const int a0 = blockIdx.x * 32, l0 = blockIdx.y * 32;
+  const int a0 = a_lo + blockIdx.x * 32, l0 = blockIdx.y * 32;
   const int a = a0 + threadIdx.x;
-  const double t1ia = (a < v) ? t1[(i64)i * v + a] : 0.0;
+  const double t1ia = (a < a_hi) ? t1[(i64)i * v + a] : 0.0;
   for (int dy = threadIdx.y; dy < 32; dy += 8) {
     const int l = l0 + dy;
-    if (l < L && a < v) {
+    if (l < L && a < a_hi) {
       const i64 off = ((i64)l * o + i) * v + a;
       const double xov = Xov[off], xt = XT[off];
       const double j = xov + Lov[off] - JT[off];
@@ -69,7 +70,7 @@ k_dress_finalize(const double* __restrict__ Xov, const double* __restrict__ Lov,
   __syncthreads();
   for (int dy = threadIdx.y; dy < 32; dy += 8) {
     const int aa = a0 + dy, l = l0 + threadIdx.x;
-    if (aa < v && l < L) {
+    if (aa < a_hi && l < L) {
       const i64 off = ((i64)aa * o + i) * ldk + l;
       JK[off] = tj[threadIdx.x][dy];
       E1K[off] = te[threadIdx.x][dy];
@@ -151,7 +152,7 @@ k_final_sums(const double* __restrict__ partial, double* __restrict__ out, int n
 }
 
 // Singles residual assembly + T1 update (reference :128-131, :149-151).
-//   Om[a,i]  = OmRep[a,i] + w[(a,i)] + OmLoc[a,i] + sum_b t1[i,b] fvv[b,a] - sum_k t1[k,a] foo[i,k]
+//   Om[a,i]  = [OmRep[a,i] if given] + w[(a,i)] + OmLoc[a,i] + sum_b t1[i,b] fvv[b,a] - sum_k t1[k,a] foo[i,k]
 //   t1n[i,a] = -Om[a,i]/(ev[a]-eo[i]);  partial[block] = sum (t1[i,a] - t1n[i,a])^2
 __global__ void __launch_bounds__(256)
 k_t1_update(const double* __restrict__ OmRep, const double* __restrict__ w, const double* __restrict__ OmLoc,
@@ -164,7 +165,7 @@ k_t1_update(const double* __restrict__ OmRep, const double* __restrict__ w, cons
   if (idx < (i64)o * v) {
     const int i = (int)(idx / v), a = (int)(idx % v);   // lanes along a: t1/t1n/fvv coalesced
     const i64 ai = (i64)a * o + i;
-    double om = OmRep[ai] + w[ai] + OmLoc[ai];
+    double om = (OmRep ? OmRep[ai] : 0.0) + w[ai] + OmLoc[ai];
     double s = 0.0;
     for (int b = 0; b < v; ++b) s += t1[(i64)i * v + b] * fvv[(i64)b * v + a];
     om += s;
@@ -314,6 +315,44 @@ k_final_sums_strided(const double* __restrict__ partial, double* __restrict__ ou
     s = block_sum(s, scratch);
     if (threadIdx.x == 0) out[q] = s;
     __syncthreads();
+  }
+}
+}  // namespace mpccb
+
+namespace mpccb {
+// In-place t2 build for the unfused path (reference dfrmpcc_lowlevel.py:137,:139): the GEMM wrote
+// e[(a,i),(b,j)] into T[a][b][i][j]; one block per (a,b) turns its o x o block into
+//   t2[i][j] = (2 e[i][j] - e[j][i]) / (eo[i] + eo[j] - ev[a] - ev[b])
+// Each thread owns a pair {(i,j),(j,i)}, i <= j: both inputs are read before either output is
+// written, so no staging copy is needed. Then OmP[b][(a,i)] = sum_j t2[i][j] * Fvo[b][j] (row dots,
+// fixed order) from the block's own freshly written (L1/L2-hot) values.
+__global__ void __launch_bounds__(256)
+k_t2_finalize(double* __restrict__ T, const double* __restrict__ eo, const double* __restrict__ ev,
+              const double* __restrict__ Fvo, double* __restrict__ OmP, int o, int v, int a_begin, int na) {
+  const int b = blockIdx.x, al = blockIdx.y;
+  double* blk = T + ((i64)al * v + b) * o * o;
+  const double dab = ev[a_begin + al] + ev[b];
+  const int npair = o * (o + 1) / 2;
+  for (int p = threadIdx.x; p < npair; p += blockDim.x) {
+    // p -> (j, i) with i <= j: row j of the packed lower triangle
+    int j = (int)((sqrt(8.0 * p + 1.0) - 1.0) * 0.5);
+    while (j * (j + 1) / 2 > p) --j;
+    while ((j + 1) * (j + 2) / 2 <= p) ++j;
+    const int i = p - j * (j + 1) / 2;
+    const double eij = blk[i * o + j], eji = blk[j * o + i];
+    const double den = eo[i] + eo[j] - dab;
+    blk[i * o + j] = (2.0 * eij - eji) / den;
+    if (i != j) blk[j * o + i] = (2.0 * eji - eij) / den;
+  }
+  __threadfence_block();
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+  const double* f = Fvo + (i64)b * o;
+  for (int i = warp; i < o; i += nw) {
+    double s = 0.0;
+    for (int j = lane; j < o; j += 32) s += blk[i * o + j] * f[j];
+    s = warp_sum(s);
+    if (lane == 0) OmP[((i64)b * na + al) * o + i] = s;
   }
 }
 }  // namespace mpccb

@@ -45,15 +45,15 @@ struct mpccb_ctx {
   double *Lvo, *t1, *t1T, *t1n, *Xov, *Xoo, *Joo, *X, *XT, *JT, *JK, *E1K, *Wov, *w, *F2, *Fvo, *OmP, *Y,
       *P, *OmRep, *OmLoc, *OmTot, *Z, *scal, *red;
   i64 P_count, OmP_count;
-  int t2_na, t2_nb, t2_tiles_m, t2_tiles_n;
+  int t2_na, t2_nb, t2_tiles_m, t2_tiles_n, t2_wn, t2_unfused, force_unfused;
   // optional per-stage CUDA-event timing (mpccb_set_option("profile", 1))
   int profile;
   std::vector<cudaEvent_t>* prof_ev;   // [stage] -> start/stop pairs
   int prof_used[16];
 };
 
-enum Stage { ST_DRESS = 0, ST_ERIS_T2, ST_YVO, ST_SINGLES_FROM_Y, ST_FINISH, ST_DIIS_PUSH, ST_DIIS_COMBINE, ST_COUNT };
-static const char* kStageNames[ST_COUNT] = {"dress", "eris_t2", "yvo", "singles_from_y", "finish", "diis_push",
+enum Stage { ST_DRESS = 0, ST_DRESS_POST, ST_ERIS_T2, ST_YVO, ST_SINGLES_FROM_Y, ST_FINISH, ST_DIIS_PUSH, ST_DIIS_COMBINE, ST_COUNT };
+static const char* kStageNames[ST_COUNT] = {"dress", "dress_post", "eris_t2", "yvo", "singles_from_y", "finish", "diis_push",
                                             "diis_combine"};
 
 namespace {
@@ -253,6 +253,32 @@ i64 carve_workspace(mpccb_ctx* c, unsigned char* base) {
 
 }  // namespace
 
+namespace {
+// tile geometry of the fused eris -> t2 kernel: n_a x n_b whole (i,j) blocks per 128 x (32*wn) tile.
+// wn = 0 picks the better-filled of the two tile shapes. When whole blocks fill the tile badly
+// (e.g. nocc = 80: one 80 x 80 block in a 128 x 128 tile = 39 %) or nocc > 128, the path is unfused:
+// generic-tile GEMM scattering e into T[a][b][i][j], then the in-place k_t2_finalize pass.
+double t2_fill(int o, int wn) {
+  if (o > 128 || 32 * wn < o) return 0.0;
+  return (double)((128 / o) * o) / 128.0 * (double)(((32 * wn) / o) * o) / (32.0 * wn);
+}
+void set_t2_geometry(mpccb_ctx* c, int wn) {
+  if (wn == 0) wn = (t2_fill(c->o, 2) >= 0.95 * t2_fill(c->o, 4) && t2_fill(c->o, 2) > 0.0) ? 2 : 4;
+  if (t2_fill(c->o, wn) == 0.0) wn = 4;
+  const double fill = t2_fill(c->o, wn);
+  c->t2_unfused = (c->force_unfused || fill < 0.70) ? 1 : 0;
+  c->t2_wn = wn;
+  if (c->t2_unfused) {
+    c->t2_na = 1; c->t2_nb = 1;
+    c->t2_tiles_m = c->na; c->t2_tiles_n = c->v;     // OmP[b][(a,i)]
+  } else {
+    c->t2_na = 128 / c->o; c->t2_nb = (32 * wn) / c->o;
+    c->t2_tiles_m = cdiv(c->na, c->t2_na);
+    c->t2_tiles_n = cdiv(c->v, c->t2_nb);
+  }
+}
+}  // namespace
+
 extern "C" {
 
 const char* mpccb_version(void) { return "mpcc_b200 0.1 (sm_100a, DMMA.8x8x4)"; }
@@ -265,7 +291,6 @@ int mpccb_create(mpccb_ctx** out, int nocc, int nvir, int naux, int a_begin, int
   *out = c;   // returned even on failure so the caller can read the message
   if (nocc <= 0 || nvir <= 0 || naux <= 0) return fail(c, "sizes must be positive");
   if (a_begin < 0 || a_end > nvir || a_begin >= a_end) return fail(c, "bad slab [%d,%d) of %d", a_begin, a_end, nvir);
-  if (nocc > 128) return fail(c, "nocc=%d > 128: fused t2 epilogue needs a whole (i,j) block per tile", nocc);
   if ((i64)nocc * nvir * (i64)nocc * nvir / nocc > (i64)INT_MAX) return fail(c, "problem too large for 32-bit row indices");
   c->o = nocc; c->v = nvir; c->L = naux; c->device = device;
   c->a_begin = a_begin; c->a_end = a_end; c->na = a_end - a_begin;
@@ -274,9 +299,7 @@ int mpccb_create(mpccb_ctx** out, int nocc, int nvir, int naux, int a_begin, int
   c->use_tma = 1;
   c->profile = 0;
   c->prof_ev = new std::vector<cudaEvent_t>[ST_COUNT];
-  c->t2_na = 128 / nocc; c->t2_nb = 128 / nocc;
-  c->t2_tiles_m = cdiv(c->na, c->t2_na);
-  c->t2_tiles_n = cdiv(nvir, c->t2_nb);
+  set_t2_geometry(c, 0);
   CUDA_OK(c, cudaSetDevice(device));
   c->ws_bytes = 0;
   return 0;
@@ -321,8 +344,23 @@ int mpccb_synchronize(mpccb_ctx* c) { CUDA_OK(c, cudaStreamSynchronize(c->stream
 long long mpccb_launch_count(const mpccb_ctx* c) { return c->launches; }
 
 int mpccb_set_option(mpccb_ctx* c, const char* name, long long value) {
-  if (!strcmp(name, "tma")) { c->use_tma = value != 0; return 0; }
+  if (!strcmp(name, "tma")) {
+    c->use_tma = value != 0;
+    if (!c->ws) set_t2_geometry(c, c->use_tma ? 0 : 4);   // the generic fallback kernel has 128 x 128 tiles
+    return 0;
+  }
   if (!strcmp(name, "profile")) { c->profile = value != 0; return 0; }
+  if (!strcmp(name, "t2_unfused")) {      // 1: always GEMM -> T, then in-place k_t2_finalize (before bind_workspace)
+    if (c->ws) return fail(c, "set t2_unfused before binding the workspace");
+    c->force_unfused = value != 0;
+    set_t2_geometry(c, c->use_tma ? 0 : 4);
+    return 0;
+  }
+  if (!strcmp(name, "t2_wide_tiles")) {   // 1: 128x128 tiles, one CTA/SM; 0: 128x64, two CTAs/SM (before bind_workspace)
+    if (c->ws) return fail(c, "set t2_wide_tiles before binding the workspace");
+    set_t2_geometry(c, value ? 4 : 2);
+    return 0;
+  }
   return fail(c, "unknown option %s", name);
 }
 
@@ -362,11 +400,18 @@ int mpccb_bind_t2(mpccb_ctx* c, double* T) { c->T = T; return 0; }
 // ===========================================================================
 // phase 1: T1 dressing + singles intermediates (reference :119-133)
 // ===========================================================================
+extern "C" int mpccb_dress_post(mpccb_ctx* c);
+
+// Slab-local part: everything that carries the virtual index a is computed for a in [a_begin, a_end)
+// only (JK/E1K rows, W columns, the W.Joo singles term); Xoo/Joo/X/F2 have no virtual index and are
+// replicated (2 x 2 L o^2 v flop). With several ranks the caller all-gathers the JK rows and then
+// calls mpccb_dress_post; on one rank mpccb_dress runs the post part itself.
 extern "C" int mpccb_dress(mpccb_ctx* c, const double* t1_dev) {
   if (!c->ws || !c->Lov) return fail(c, "workspace/integrals not bound");
-  StageTimer timer(c, ST_DRESS);
-  const int o = c->o, v = c->v, L = c->L;
+  const int o = c->o, v = c->v, L = c->L, a0 = c->a_begin, na = c->na;
   const i64 nov = c->nov;
+  {
+  StageTimer timer(c, ST_DRESS);
   if (t1_dev != c->t1)
     CUDA_OK(c, cudaMemcpyAsync(c->t1, t1_dev, sizeof(double) * nov, cudaMemcpyDeviceToDevice, c->stream));
   {  // t1T[a][i] = t1[i][a]
@@ -374,14 +419,15 @@ extern "C" int mpccb_dress(mpccb_ctx* c, const double* t1_dev) {
     k_transpose_batched<<<grid, block, 0, c->stream>>>(c->t1, c->t1T, o, v);
     LAUNCH_OK(c, "k_transpose_batched(t1)");
   }
-  {  // :119  Xov[L][i][a] = sum_b Lvv[L][a][b] t1[i][b]      M=(L,a) N=i K=b
-    Operand A = flat_operand(c->Lvv, L * v, v, 1);
+  {  // :119  Xov[L][i][a] = sum_b Lvv[L][a][b] t1[i][b]      M=(L, a in slab) N=i K=b
+    Operand A = flat_operand(c->Lvv + (i64)a0 * v, L * na, v, 1);
+    A.rdiv = na; A.r_hi = (i64)v * v; A.r_lo = v;
     Operand B = flat_operand(c->t1, o, v, 1);
-    Output C = flat_output(c->Xov, 0, v);
-    C.mdiv = v; C.m_hi = (i64)o * v; C.m_lo = 1;
-    if (launch_gemm<CfgN64KK>(c, "Xvo", A, B, C, L * v, o, v, 1, nullptr)) return 1;
+    Output C = flat_output(c->Xov + a0, 0, v);
+    C.mdiv = na; C.m_hi = (i64)o * v; C.m_lo = 1;
+    if (launch_gemm<CfgN64KK>(c, "Xvo", A, B, C, L * na, o, v, 1, nullptr)) return 1;
   }
-  {  // :120,:123  Xoo[(L,i)][j] = sum_a Lov[(L,i)][a] t1[j][a];  Joo = Xoo + Loo
+  {  // :120,:123  Xoo[(L,i)][j] = sum_a Lov[(L,i)][a] t1[j][a];  Joo = Xoo + Loo      (replicated)
     Operand A = flat_operand(c->Lov, L * o, v, 1);
     Operand B = flat_operand(c->t1, o, v, 1);
     Output C = flat_output(c->Xoo, o, 1);
@@ -391,33 +437,44 @@ extern "C" int mpccb_dress(mpccb_ctx* c, const double* t1_dev) {
   // :121  X[L] = trace_i Xoo[L]
   k_trace<<<cdiv(L, 4), 128, 0, c->stream>>>(c->Xoo, c->X, L, o);
   LAUNCH_OK(c, "k_trace");
-  {  // [XT | JT][(L,i)][a] = sum_k [Xoo | Joo][(L,i)][k] t1[k][a]    (:124 last term, :127, :146)
+  {  // [XT | JT][(L,i)][a] = sum_k [Xoo | Joo][(L,i)][k] t1[k][a], a in slab    (:124 last term, :127, :146)
     Operand A = flat_operand(c->Xoo, 2 * L * o, o, 1);
-    Operand B = flat_operand(c->t1T, v, o, 1);
-    Output C = flat_output(c->XT, v, 1);
-    if (launch_gemm<CfgBigKK>(c, "XT|JT", A, B, C, 2 * L * o, v, o, 1, nullptr)) return 1;
+    Operand B = flat_operand(c->t1T + (i64)a0 * o, na, o, 1);
+    Output C = flat_output(c->XT + a0, v, 1);
+    if (na >= 96) { if (launch_gemm<CfgBigKK>(c, "XT|JT", A, B, C, 2 * L * o, na, o, 1, nullptr)) return 1; }
+    else          { if (launch_gemm<CfgN64KK>(c, "XT|JT", A, B, C, 2 * L * o, na, o, 1, nullptr)) return 1; }
   }
-  {  // :124, :146 integrand, W = XT - Xov
-    dim3 grid(cdiv(v, 32), cdiv(L, 32), o), block(32, 8);
+  {  // :124, :146 integrand, W = XT - Xov   (columns a of the slab -> JK/E1K rows of the slab)
+    dim3 grid(cdiv(na, 32), cdiv(L, 32), o), block(32, 8);
     k_dress_finalize<<<grid, block, 0, c->stream>>>(c->Xov, c->Lov, c->JT, c->XT, c->X, c->t1, c->JK, c->E1K,
-                                                    c->Wov, L, o, v, c->ldk);
+                                                    c->Wov, L, o, v, c->ldk, a0, a0 + na);
     LAUNCH_OK(c, "k_dress_finalize");
   }
-  {  // :126-127  OmRep[a][i] = sum_{(L,j)} W[(L,j)][a] Joo[(L,j)][i]
-    Operand A = flat_operand(c->Wov, v, 1, v);
+  {  // :126-127  OmRep[a][i] = sum_{(L,j)} W[(L,j)][a] Joo[(L,j)][i],  a in slab
+    Operand A = flat_operand(c->Wov + a0, na, 1, v);
     Operand B = flat_operand(c->Joo, o, 1, o);
-    if (splitk_gemm<CfgN64RR>(c, "W.Joo", A, B, c->OmRep, v, o, L * o, 1.0, 0.0)) return 1;
+    if (splitk_gemm<CfgN64RR>(c, "W.Joo", A, B, c->OmRep + (i64)a0 * o, na, o, L * o, 1.0, 0.0)) return 1;
   }
-  // :128 and first half of :133   w[(a,i)] = sum_L J[(a,i)][L] X[L]
-  k_gemv_rows<<<cdiv(nov, 8), 256, 0, c->stream>>>(c->JK, c->X, c->w, (int)nov, L, c->ldk);
-  LAUNCH_OK(c, "k_gemv_rows");
-  {  // :133 second half   F2[b][j] = sum_{(L,i)} Lov[(L,i)][b] Xoo[(L,i)][j];  Fvo = w - F2
+  {  // :133 second half   F2[b][j] = sum_{(L,i)} Lov[(L,i)][b] Xoo[(L,i)][j]      (replicated)
     Operand A = flat_operand(c->Lov, v, 1, v);
     Operand B = flat_operand(c->Xoo, o, 1, o);
     if (splitk_gemm<CfgN64RR>(c, "Xoo.Lov", A, B, c->F2, v, o, L * o, 1.0, 0.0)) return 1;
-    k_make_fvo<<<cdiv(nov, 256), 256, 0, c->stream>>>(c->w, c->F2, c->Fvo, nov);
-    LAUNCH_OK(c, "k_make_fvo");
   }
+  }
+  if (na == v) return mpccb_dress_post(c);
+  return 0;
+}
+
+// Needs every row of JK (all-gathered over the ranks): w = Jvo.X for all (b,j), Fvo = w - F2.
+extern "C" int mpccb_dress_post(mpccb_ctx* c) {
+  if (!c->ws || !c->Lov) return fail(c, "workspace/integrals not bound");
+  StageTimer timer(c, ST_DRESS_POST);
+  const i64 nov = c->nov;
+  // :128 and first half of :133   w[(a,i)] = sum_L J[(a,i)][L] X[L]
+  k_gemv_rows<<<cdiv(nov, 8), 256, 0, c->stream>>>(c->JK, c->X, c->w, (int)nov, c->L, c->ldk);
+  LAUNCH_OK(c, "k_gemv_rows");
+  k_make_fvo<<<cdiv(nov, 256), 256, 0, c->stream>>>(c->w, c->F2, c->Fvo, nov);
+  LAUNCH_OK(c, "k_make_fvo");
   return 0;
 }
 
@@ -464,26 +521,31 @@ int make_map_2d(mpccb_ctx* c, CUtensorMap* map, const double* base, i64 K, i64 r
   return make_tensor_map(c, map, base, 2, dims, strides, box);
 }
 
-template <int EPI>
+template <int EPI, int WN>
 int launch_tma(mpccb_ctx* c, const char* what, const CUtensorMap& mA, const CUtensorMap& mB,
                const TmaGemmParams& p, const T2Params& t2p) {
-  const size_t smem = (EPI == 1 ? std::max<size_t>(sizeof(double) * TMA_TM * (TMA_TN + 1), TMA_RING_BYTES)
-                                : (size_t)TMA_RING_BYTES) + TMA_BAR_BYTES;
+  typedef TmaCfg<WN> Cfg;
+  const size_t smem = (EPI == 1 ? (size_t)Cfg::AREA_EPI1 : (size_t)Cfg::RING_BYTES) + TMA_BAR_BYTES;
   static bool attr_done = false;
   if (!attr_done) {
-    CUDA_OK(c, cudaFuncSetAttribute(gemm_tma_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CUDA_OK(c, cudaFuncSetAttribute(gemm_tma_kernel<EPI, WN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CUDA_OK(c, cudaFuncSetAttribute(gemm_tma_kernel<EPI, WN>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
     attr_done = true;
   }
-  gemm_tma_kernel<EPI><<<p.tiles_m * p.tiles_n, TMA_THREADS, smem, c->stream>>>(mA, mB, p, t2p);
+  gemm_tma_kernel<EPI, WN><<<p.tiles_m * p.tiles_n, Cfg::THREADS, smem, c->stream>>>(mA, mB, p, t2p);
   LAUNCH_OK(c, what);
   return 0;
 }
 
-int launch_eris_t2_tma(mpccb_ctx* c) {
+// fused eris -> t2: 128 x (32*WN) tiles; WN = 2 runs two CTAs per SM so that one CTA's epilogue
+// overlaps the other's K loop (needs n_b = 64 / o >= 1)
+template <int WN>
+int launch_eris_t2_tma_wn(mpccb_ctx* c) {
+  typedef TmaCfg<WN> Cfg;
   const int o = c->o, v = c->v, L = c->L;
   CUtensorMap mA, mB;
   if (make_map_2d(c, &mA, c->JK + (i64)c->a_begin * o * c->ldk, L, (i64)c->na * o, c->ldk, TMA_TM)) return 1;
-  if (make_map_2d(c, &mB, c->JK, L, (i64)v * o, c->ldk, TMA_TN)) return 1;
+  if (make_map_2d(c, &mB, c->JK, L, (i64)v * o, c->ldk, Cfg::TN)) return 1;
   T2Params t;
   t.T = c->T; t.eo = c->eo; t.ev = c->ev; t.Fvo = c->Fvo; t.OmP = c->OmP;
   t.o = o; t.v = v; t.a_begin = c->a_begin; t.a_end = c->a_end; t.n_a = c->t2_na; t.n_b = c->t2_nb;
@@ -494,11 +556,16 @@ int launch_eris_t2_tma(mpccb_ctx* c) {
   p.tiles_m = c->t2_tiles_m; p.tiles_n = c->t2_tiles_n;
   p.nk = cdiv(L, TMA_TK);
   p.a_mode = 0;
-  p.a_bytes = TMA_TM * TMA_TK * 8; p.b_bytes = TMA_TN * TMA_TK * 8;
-  return launch_tma<1>(c, "gemm_tma_kernel<t2>", mA, mB, p, t);
+  p.a_bytes = TMA_TM * TMA_TK * 8; p.b_bytes = Cfg::TN * TMA_TK * 8;
+  return launch_tma<1, WN>(c, "gemm_tma_kernel<t2>", mA, mB, p, t);
+}
+
+int launch_eris_t2_tma(mpccb_ctx* c) {
+  return c->t2_wn == 2 ? launch_eris_t2_tma_wn<2>(c) : launch_eris_t2_tma_wn<4>(c);
 }
 
 int launch_yvo_tma(mpccb_ctx* c) {
+  constexpr int TN = TmaCfg<4>::TN;
   const int o = c->o, v = c->v, L = c->L;
   const int n_a = 128 / o;
   CUtensorMap mA, mB;
@@ -508,22 +575,39 @@ int launch_yvo_tma(mpccb_ctx* c) {
     cuuint32_t box[4] = {(cuuint32_t)TMA_TK, (cuuint32_t)o, 1, (cuuint32_t)n_a};
     if (make_tensor_map(c, &mA, c->T, 4, dims, strides, box)) return 1;
   }
-  if (make_map_2d(c, &mB, c->Lvo, (i64)v * o, L, (i64)v * o, TMA_TN)) return 1;
+  if (make_map_2d(c, &mB, c->Lvo, (i64)v * o, L, (i64)v * o, TN)) return 1;
   TmaGemmParams p;
   memset(&p, 0, sizeof(p));
   p.M = c->na * o; p.N = L;
-  p.tm_eff = n_a * o; p.tn_eff = TMA_TN;
-  p.tiles_m = cdiv(c->na, n_a); p.tiles_n = cdiv(L, TMA_TN);
+  p.tm_eff = n_a * o; p.tn_eff = TN;
+  p.tiles_m = cdiv(c->na, n_a); p.tiles_n = cdiv(L, TN);
   p.nk = v * (o / TMA_TK);
   p.a_mode = 1; p.jsteps = o / TMA_TK; p.o = o; p.n_a = n_a;
-  p.a_bytes = (uint32_t)(TMA_TK * o * n_a * 8); p.b_bytes = TMA_TN * TMA_TK * 8;
+  p.a_bytes = (uint32_t)(TMA_TK * o * n_a * 8); p.b_bytes = TN * TMA_TK * 8;
   p.C = c->Y + (i64)c->a_begin * o * L; p.ldc = L;
   T2Params t;
   memset(&t, 0, sizeof(t));
-  return launch_tma<0>(c, "gemm_tma_kernel<store>", mA, mB, p, t);
+  return launch_tma<0, 4>(c, "gemm_tma_kernel<store>", mA, mB, p, t);
+}
+
+// unfused form of :135-137,:139 for occupied counts that tile badly: e -> T[a][b][i][j] with the
+// generic DMMA GEMM (any tile alignment), then t2 = (2e - e^T)/D in place per (a,b) block
+int launch_eris_t2_unfused(mpccb_ctx* c) {
+  const int o = c->o, v = c->v, L = c->L;
+  Operand A = flat_operand(c->JK + (i64)c->a_begin * o * c->ldk, c->na * o, c->ldk, 1);
+  Operand B = flat_operand(c->JK, v * o, c->ldk, 1);
+  Output C = flat_output(c->T, 0, 0);
+  C.mdiv = o; C.m_hi = (i64)v * o * o; C.m_lo = o;      // m = (a_l, i)
+  C.ndiv = o; C.n_hi = (i64)o * o;     C.n_lo = 1;      // n = (b, j)
+  if (launch_gemm<CfgBigKK>(c, "eris(unfused)", A, B, C, c->na * o, v * o, L, 1, nullptr)) return 1;
+  dim3 grid(v, c->na);
+  k_t2_finalize<<<grid, 256, 0, c->stream>>>(c->T, c->eo, c->ev, c->Fvo, c->OmP, o, v, c->a_begin, c->na);
+  LAUNCH_OK(c, "k_t2_finalize");
+  return 0;
 }
 
 int launch_eris_t2(mpccb_ctx* c) {
+  if (c->t2_unfused) return launch_eris_t2_unfused(c);
   if (c->use_tma) return launch_eris_t2_tma(c);
   typedef CfgBigKK Cfg;
   const int o = c->o, v = c->v, L = c->L;
@@ -550,7 +634,7 @@ int launch_eris_t2(mpccb_ctx* c) {
 
 int launch_yvo(mpccb_ctx* c) {
   const int o = c->o, v = c->v, L = c->L;
-  if (c->use_tma && o % TMA_TK == 0) return launch_yvo_tma(c);
+  if (c->use_tma && o % TMA_TK == 0 && o <= 128 && (128 / o) * o >= 96) return launch_yvo_tma(c);
   // :138  Y[(a,i)][L] = sum_{(b,j)} T[a][b][i][j] Lvo[L][(b,j)]
   Operand A;
   A.base = c->T; A.rows = c->na * o;
@@ -569,12 +653,15 @@ extern "C" int mpccb_doubles(mpccb_ctx* c, double* red_dev) {
   const i64 nov = c->nov;
   double* Om = red_dev;   // [a][i] partial over the local slab
   CUDA_OK(c, cudaMemsetAsync(red_dev, 0, sizeof(double) * (nov + 1), c->stream));
+  // the slab's W.Joo singles term from mpccb_dress (:126-127) joins the partial sums
+  CUDA_OK(c, cudaMemcpyAsync(Om + (i64)c->a_begin * o, c->OmRep + (i64)c->a_begin * o, sizeof(double) * na * o,
+                             cudaMemcpyDeviceToDevice, c->stream));
   {
     StageTimer timer(c, ST_ERIS_T2);
     if (launch_eris_t2(c)) return 1;                                 // :135-137 (+ :139 partials)
   }
-  // :139  Om[a_loc][i] = sum_tiles OmP
-  if (reduce_splits(c, Om + (i64)c->a_begin * o, c->OmP, c->t2_tiles_n, (i64)na * o, (i64)na * o, 1.0, 0.0))
+  // :139  Om[a_loc][i] += sum_tiles OmP
+  if (reduce_splits(c, Om + (i64)c->a_begin * o, c->OmP, c->t2_tiles_n, (i64)na * o, (i64)na * o, 1.0, 1.0))
     return 1;
   {
     StageTimer timer(c, ST_YVO);
@@ -625,7 +712,7 @@ extern "C" int mpccb_finish(mpccb_ctx* c, const double* red_dev, double* t1_new_
   const i64 nov = c->nov;
   const int nb = cdiv(nov, 256);
   if (nb > 8000) return fail(c, "nov too large for the residual scratch");
-  k_t1_update<<<nb, 256, 0, c->stream>>>(c->OmRep, c->w, red_dev, c->t1, c->fvv, c->foo, c->eo, c->ev, t1_new_dev,
+  k_t1_update<<<nb, 256, 0, c->stream>>>(nullptr, c->w, red_dev, c->t1, c->fvv, c->foo, c->eo, c->ev, t1_new_dev,
                                          c->OmTot, c->scal, c->o, c->v);
   LAUNCH_OK(c, "k_t1_update");
   k_final_sums<<<1, 256, 0, c->stream>>>(c->scal, scal_dev, nb, 1);
@@ -638,6 +725,7 @@ extern "C" int mpccb_updated_amps_host(mpccb_ctx* c, const double* t1_host, doub
                                        double* res_host, double* dE_host) {
   const i64 nov = c->nov;
   CUDA_OK(c, cudaMemcpyAsync(c->t1, t1_host, sizeof(double) * nov, cudaMemcpyHostToDevice, c->stream));
+  if (c->na != c->v) return fail(c, "mpccb_updated_amps_host works on a whole-range context (one rank)");
   if (mpccb_dress(c, c->t1)) return 1;
   if (mpccb_doubles(c, c->red)) return 1;
   double* sc = c->scal + 8000;

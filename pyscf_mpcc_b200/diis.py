@@ -53,6 +53,7 @@ class DIIS:
         self._x = {}
         self._e = {}
         self.last_coeff = None
+        self._pool = []
 
     def get_num_vec(self):
         return len(self._bookkeep)
@@ -65,7 +66,18 @@ class DIIS:
 
     # -- device plumbing ----------------------------------------------------
     def _alloc(self, like_len, device):
+        if self._pool:
+            return self._pool.pop()
         return torch.empty(like_len, dtype=torch.float64, device=device)
+
+    def reserve(self, solver):
+        """Allocate the whole history (xprev + ``space`` x/e pairs) up front, so that no cudaMalloc —
+        slow once NCCL has mapped peer memory — lands inside the iteration loop. Optional: without it
+        the vectors are allocated on first use, as the reference's ``push_vec`` does (diis.py:148-185)."""
+        need = 1 + 2 * self.space - (0 if self._xprev is None else 1) - 2 * len(self._x) - len(self._pool)
+        for _ in range(max(need, 0)):
+            self._pool.append(torch.empty(solver._vec_len_local, dtype=torch.float64, device=solver.device))
+        return self
 
     def update(self, amps):
         """Push the amplitudes the solver just produced and return the extrapolated

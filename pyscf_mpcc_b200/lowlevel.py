@@ -23,6 +23,7 @@ energy lagging the amplitudes by one update, convergence tested on T1 only.
 """
 from __future__ import annotations
 
+import os
 import sys
 
 import numpy as np
@@ -100,7 +101,7 @@ class DeviceT2:
 class MPCC_LL:
     """GPU-resident equivalent of ``pyscf.mpcc.dfrmpcc_lowlevel.MPCC_LL``."""
 
-    def __init__(self, mf=None, *, blocks=None, device=None, group=None, use_tma=True):
+    def __init__(self, mf=None, *, blocks=None, device=None, group=None, use_tma=True, t2_wide_tiles=None, t2_unfused=None):
         """``MPCC_LL(mf)`` as in the reference (:7-43). Extensions (keyword only):
 
         blocks : (Loo, Lov, Lvv, foo, fvv, mo_energy) numpy arrays or CUDA tensors
@@ -161,11 +162,27 @@ class MPCC_LL:
         self._vec_len_local = sharding.local_vector_length(o, v, self._a_begin, self._a_end)
         self._ctx = _cabi.Context(o, v, L, self._a_begin, self._a_end, self.device.index)
         self._ctx.call("mpccb_set_option", b"tma", int(bool(use_tma)))
+        if t2_wide_tiles is None and os.environ.get("MPCC_T2_WIDE_TILES"):
+            t2_wide_tiles = os.environ["MPCC_T2_WIDE_TILES"] != "0"
+        if t2_unfused is not None:
+            self._ctx.call("mpccb_set_option", b"t2_unfused", int(bool(t2_unfused)))
+        if t2_wide_tiles is not None:      # tuning knob: 128x128 tiles (1 CTA/SM) vs 128x64 (2 CTAs/SM) for eris->t2
+            self._ctx.call("mpccb_set_option", b"t2_wide_tiles", int(bool(t2_wide_tiles)))
         self._bind_stream()
         f64 = dict(dtype=torch.float64, device=self.device)
         self._ws = torch.empty(self._ctx.workspace_bytes() + 256, dtype=torch.uint8, device=self.device)
         ws_ptr = (self._ws.data_ptr() + 255) // 256 * 256
         self._ctx.call("mpccb_bind_workspace", ws_ptr, self._ctx.workspace_bytes())
+        if self.world_size > 1:
+            ptr, count = self._ctx.buffer("JK")
+            off = ptr - self._ws.data_ptr()
+            ldk = count // self.nov
+            self._jk_view = self._ws[off:off + count * 8].view(torch.float64)
+            self._jk_rows = []
+            for r in range(self.world_size):
+                b0, b1 = sharding.slab_bounds(v, self.world_size, r)
+                self._jk_rows.append((b0 * o * ldk, b1 * o * ldk))
+            self._equal_slabs = len({hi - lo for lo, hi in self._jk_rows}) == 1
         self._T = torch.empty(self._na * v * o * o, **f64)
         self._ctx.call("mpccb_bind_t2", self._T.data_ptr())
         self._t2_serial = 0
@@ -297,6 +314,23 @@ class MPCC_LL:
             Lvv[p0:p1] = torch.from_numpy(np.ascontiguousarray(full[:, o:, o:]))
         self._d = {"Loo": Loo, "Lov": Lov, "Lvv": Lvv}
 
+    def _dress(self, t1_dev):
+        """T1 dressing (:119-133). One rank: a single native call. Several ranks: each dresses its own
+        virtual slab, the dressed integrals Jvo (rows of the K-major JK buffer; a slab is a contiguous
+        row range) are all-gathered over NVLink, then the terms that need every row are formed."""
+        ctx = self._ctx
+        ctx.call("mpccb_dress", t1_dev.data_ptr())
+        if self.world_size == 1:
+            return
+        jk, rows = self._jk_view, self._jk_rows
+        if self._equal_slabs:
+            torch.distributed.all_gather_into_tensor(jk, jk[rows[self.rank][0]:rows[self.rank][1]], group=self.group)
+        else:
+            for r, (lo, hi) in enumerate(rows):
+                torch.distributed.broadcast(jk[lo:hi], src=torch.distributed.get_global_rank(self.group, r),
+                                            group=self.group)
+        ctx.call("mpccb_dress_post")
+
     # ------------------------------------------------------------------ :103-152
     def updated_amps(self):
         """One residual evaluation from ``self.t1``; returns (res, dE, t1_new, t2) with
@@ -310,7 +344,7 @@ class MPCC_LL:
             self._t1_dev.copy_(self._t1_host, non_blocking=True)
             self.h2d_bytes += self.nov * 8
         ctx = self._ctx
-        ctx.call("mpccb_dress", self._t1_dev.data_ptr())
+        self._dress(self._t1_dev)
         ctx.call("mpccb_doubles", self._red.data_ptr())
         self._t2_serial += 1
         if self.world_size > 1:
@@ -334,7 +368,7 @@ class MPCC_LL:
         the <= 6 DIIS dot products cross PCIe. Returns (res, dE, t1_next_dev)."""
         self._bind_stream()
         ctx = self._ctx
-        ctx.call("mpccb_dress", t1_dev.data_ptr())
+        self._dress(t1_dev)
         ctx.call("mpccb_doubles", self._red.data_ptr())
         self._t2_serial += 1
         if self.world_size > 1:

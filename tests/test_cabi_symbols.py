@@ -29,7 +29,7 @@ def test_binding_covers_header():
     assert sorted(_cabi.SIGNATURES) == declared_symbols()
     lib = _cabi.load()
     assert b"sm_100a" in lib.mpccb_version()
-    assert lib.mpccb_profile_stages() == 7
+    assert lib.mpccb_profile_stages() == 8
 
 
 def test_library_is_sm100a_dmma_code():

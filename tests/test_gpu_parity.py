@@ -72,11 +72,24 @@ def test_updated_amps_known_answers(path, tag):
     assert ll.update_amps.__func__ is ll.updated_amps.__func__
 
 
+@pytest.mark.parametrize("variant", ["default", "wide", "unfused", "no_tma"])
+def test_t2_kernel_variants_agree_with_fixture(variant):
+    """All forms of the eris -> t2 step (128x64 two-CTA tiles, 128x128 tiles, unfused GEMM + in-place pass,
+    generic non-TMA kernel) reproduce the reference fixture."""
+    g, o, v, L, scale = _load([p for p in golden_cases() if "12_64_192" in p][0])
+    kw = {"default": {}, "wide": {"t2_wide_tiles": True}, "unfused": {"t2_unfused": True}, "no_tma": {"use_tma": False}}[variant]
+    mf, ll = _solver(o, v, L, scale, **kw)
+    e = ll.kernel()
+    assert ll.iterations == int(g["iterations"]) and abs(e - g["trace_dE"][-1]) <= E_TOL
+    assert np.abs(ll.t1 - g["final_t1"]).max() <= AMP_TOL
+    assert np.abs(np.asarray(ll.t2).reshape(-1)[::STRIDE] - g["final_t2_samples"]).max() <= AMP_TOL
+
+
 @pytest.mark.parametrize("shape", [(5, 19, 116, 0.1), (7, 33, 65, 0.15), (16, 48, 150, 0.1), (33, 70, 129, 0.05),
-                                   (64, 66, 130, 0.05), (128, 130, 64, 0.03)])
+                                   (64, 66, 130, 0.05), (80, 90, 100, 0.04), (128, 130, 64, 0.03), (131, 140, 48, 0.03)])
 def test_intermediates_against_oracle(shape):
-    """Every stage of updated_amps vs the oracle on the same seeded inputs (odd sizes, o up to the
-    128 limit of the fused epilogue, naux not a multiple of the K tile)."""
+    """Every stage of updated_amps vs the oracle on the same seeded inputs (odd sizes, occupied counts on
+    both sides of the fused-epilogue limit of 128, badly tiling nocc = 80 (unfused path), naux not a multiple of the K tile)."""
     from oracle.mpcc_oracle import LowLevelOracle
     o, v, L, scale = shape
     mf, ll = _solver(o, v, L, scale, seed=3)
