@@ -45,6 +45,13 @@ int mpccb_bind_workspace(mpccb_ctx* ctx, void* ws_dev, size_t bytes);
 int mpccb_bind_integrals(mpccb_ctx* ctx, const double* Loo_dev, const double* Lov_dev,
                          const double* Lvv_dev, const double* foo_dev, const double* fvv_dev,
                          const double* eps_o_dev, const double* eps_v_dev);
+/* AO -> MO transform of one block of Cholesky rows on the device: MPCC_LL.compute_three_center_ints
+ * (dfrmpcc_lowlevel.py:46-69: lib.unpack_tril + lib.einsum("Lab,ap,bq->Lpq") + slicing). packed_dev holds nb rows
+ * of nao(nao+1)/2 doubles as with_df.loop() yields them; C_dev is mo_coeff (nao x nao row-major). Writes rows
+ * [l0, l0+nb) of Loo (L,o,o), Lov (L,o,v), Lvv (L,v,v). scratch_dev: mpccb_ao2mo_scratch_bytes(ctx, nb) bytes. */
+size_t mpccb_ao2mo_scratch_bytes(const mpccb_ctx* ctx, int nb);
+int mpccb_ao2mo_block(mpccb_ctx* ctx, const double* packed_dev, int nb, int l0, const double* C_dev,
+                      double* Loo_dev, double* Lov_dev, double* Lvv_dev, void* scratch_dev, size_t scratch_bytes);
 /* t2 buffer in [a - a_begin, b, i, j] order: (a_end-a_begin)*v*o*o doubles */
 int mpccb_bind_t2(mpccb_ctx* ctx, double* t2_abij_dev);
 
@@ -107,7 +114,8 @@ int mpccb_profile_read(mpccb_ctx* ctx, double* ms_out, long long* count_out);
  * "profile" (0/1 record stage timings; default 0), "t2_wide_tiles" (1: 128x128 tiles / one CTA per SM for the
  * fused eris->t2 GEMM, 0: 128x64 tiles / two CTAs per SM; default: the better-filled shape; set before bind_workspace), "t2_unfused" (1: GEMM into the t2 buffer + in-place
  * t2 pass instead of the fused epilogue; default: only when whole (i,j) blocks fill the tile < 70 %, e.g. nocc = 80,
- * or nocc > 128) */
+ * or nocc > 128), "yvo_split" (force the split-K factor of the Yvo GEMM; default 0 = chosen from the tile count so that
+ * the last wave of CTAs is not mostly idle when the slab is small) */
 int mpccb_set_option(mpccb_ctx* ctx, const char* name, long long value);
 /* standalone C[m,n] = sum_k A[m,k] B[n,k] through the generic DMMA kernel (row-major, test hook) */
 int mpccb_gemm_nt(mpccb_ctx* ctx, const double* A_dev, const double* B_dev, double* C_dev,

@@ -31,6 +31,9 @@ SIGNATURES = {
     "mpccb_workspace_bytes": (ctypes.c_size_t, [c_void_p]),
     "mpccb_bind_workspace": (c_int, [c_void_p, c_void_p, ctypes.c_size_t]),
     "mpccb_bind_integrals": (c_int, [c_void_p] + [c_void_p] * 7),
+    "mpccb_ao2mo_scratch_bytes": (ctypes.c_size_t, [c_void_p, c_int]),
+    "mpccb_ao2mo_block": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
+                                  c_void_p, ctypes.c_size_t]),
     "mpccb_bind_t2": (c_int, [c_void_p, c_void_p]),
     "mpccb_dress": (c_int, [c_void_p, c_void_p]),
     "mpccb_dress_post": (c_int, [c_void_p]),

@@ -95,6 +95,10 @@ struct TmaGemmParams {
   // plain store epilogue
   double* C;
   i64 ldc;
+  // split-K (EPI 0 only): blockIdx.x = split * tiles + tile; split s covers K steps [s*nk_split, ...) and
+  // stores to C + s*split_stride (partials reduced afterwards in fixed order). ksplit == 1: none.
+  int ksplit, nk_split, tiles_total;
+  i64 split_stride;
 };
 
 // EPI: 0 = plain row-major store (Yvo), 1 = fused eris -> t2 epilogue.
@@ -114,12 +118,17 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   int tm, tn;
-  tile_coords(blockIdx.x, p.tiles_m, p.tiles_n, tm, tn);
+  const int ntiles = p.tiles_m * p.tiles_n;
+  const int split = (EPI == 0 && p.ksplit > 1) ? blockIdx.x / ntiles : 0;
+  tile_coords(blockIdx.x - split * ntiles, p.tiles_m, p.tiles_n, tm, tn);
   const int m0 = tm * p.tm_eff, n0 = tn * p.tn_eff;
   const bool producer = (threadIdx.x == 0);
+  const int k_first = split * p.nk_split;                        // first K step of this CTA
+  const int nk = (EPI == 0 && p.ksplit > 1) ? min(p.nk_split, p.nk - k_first) : p.nk;
 
-  auto issue = [&](int kt) {
-    const int s = kt % TMA_STAGES;
+  auto issue = [&](int kl) {                                     // kl: K step local to this CTA
+    const int s = kl % TMA_STAGES;
+    const int kt = k_first + kl;
     double* a_dst = ring + s * (Cfg::STAGE_BYTES / 8);
     double* b_dst = a_dst + TMA_TM * TMA_TK;
     mbar_expect_tx(&full[s], p.a_bytes + p.b_bytes);
@@ -141,7 +150,7 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    for (int kt = 0; kt < TMA_STAGES - 1 && kt < p.nk; ++kt) issue(kt);
+    for (int kt = 0; kt < TMA_STAGES - 1 && kt < nk; ++kt) issue(kt);
   }
   __syncthreads();
 
@@ -154,10 +163,10 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
     for (int j = 0; j < 4; ++j) { acc[i][j][0] = 0.0; acc[i][j][1] = 0.0; }
   const int rg = rho(g);
   const int arow = (wm * 32 + rg) * 16, brow = (wn * 32 + rg) * 16;
-  for (int kt = 0; kt < p.nk; ++kt) {
+  for (int kt = 0; kt < nk; ++kt) {
     if (producer) {
       const int kp = kt + TMA_STAGES - 1;
-      if (kp < p.nk) {
+      if (kp < nk) {
         if (kt > 0) mbar_wait(&empty[kp % TMA_STAGES], ((kp / TMA_STAGES) - 1) & 1);
         issue(kp);
       }
@@ -199,7 +208,7 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
         for (int c = 0; c < 2; ++c) {
           const int nl = wn * 32 + j * 8 + rho(2 * tig + c);
           const int n = n0 + nl;
-          if (nl < p.tn_eff && n < p.N) p.C[(i64)m * p.ldc + n] = acc[i][j][c];
+          if (nl < p.tn_eff && n < p.N) p.C[split * p.split_stride + (i64)m * p.ldc + n] = acc[i][j][c];
         }
     }
   } else {

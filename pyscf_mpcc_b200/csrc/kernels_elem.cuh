@@ -356,3 +356,18 @@ k_t2_finalize(double* __restrict__ T, const double* __restrict__ eo, const doubl
   }
 }
 }  // namespace mpccb
+
+namespace mpccb {
+// full[l][r][c] = packed[l][max(r,c)*(max(r,c)+1)/2 + min(r,c)]: lib.unpack_tril of the Cholesky rows
+// with_df.loop() yields (reference dfrmpcc_lowlevel.py:55-57; NPdunpack_tril + NPdsymm_triu,
+// pyscf/lib/np_helper/pack_tril.c:24-37,58-69). One block row per (l, r).
+__global__ void __launch_bounds__(256)
+k_unpack_tril_sym(const double* __restrict__ packed, double* __restrict__ full, int nao, i64 npair) {
+  const int r = blockIdx.x, l = blockIdx.y;
+  const double* src = packed + (i64)l * npair;
+  double* dst = full + ((i64)l * nao + r) * nao;
+  const i64 rbase = (i64)r * (r + 1) / 2;
+  for (int c = threadIdx.x; c < nao; c += blockDim.x)
+    dst[c] = (c <= r) ? src[rbase + c] : src[(i64)c * (c + 1) / 2 + r];
+}
+}  // namespace mpccb

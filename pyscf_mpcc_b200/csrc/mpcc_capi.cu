@@ -27,6 +27,9 @@ typedef GemmCfg<4, 2, 4, 4, true, true> CfgN64KK;     // 128 x 64
 typedef GemmCfg<4, 2, 4, 4, false, false> CfgN64RR;
 typedef GemmCfg<4, 2, 4, 4, true, false> CfgN64KR;
 typedef GemmCfg<4, 2, 4, 4, false, true> CfgN64RK;
+typedef GemmCfg<2, 4, 8, 4, true, false> CfgBigKR;    // 128 x 128, B row-major
+typedef GemmCfg<2, 4, 8, 4, false, false> CfgBigRR;   // 128 x 128, both row-major
+typedef GemmCfg<2, 4, 4, 4, false, false> CfgM64RR;   // 64 x 128
 }  // namespace
 
 struct mpccb_ctx {
@@ -43,7 +46,8 @@ struct mpccb_ctx {
   size_t ws_bytes;
   // workspace carve-up (doubles)
   double *Lvo, *t1, *t1T, *t1n, *Xov, *Xoo, *Joo, *X, *XT, *JT, *JK, *E1K, *Wov, *w, *F2, *Fvo, *OmP, *Y,
-      *P, *OmRep, *OmLoc, *OmTot, *Z, *scal, *red;
+      *P, *OmRep, *OmLoc, *OmTot, *Z, *scal, *red, *YP;
+  int yvo_split, yvo_split_force;
   i64 P_count, OmP_count;
   int t2_na, t2_nb, t2_tiles_m, t2_tiles_n, t2_wn, t2_unfused, force_unfused;
   // optional per-stage CUDA-event timing (mpccb_set_option("profile", 1))
@@ -210,6 +214,25 @@ struct Carve {
   }
 };
 
+// Split-K factor of the TMA Yvo GEMM: with few output tiles per SM (a-slab sharding) the last wave is
+// mostly idle; s K-slices turn T tiles into T*s shorter CTAs. Pick s <= 8 minimising ceil(T*s/148)/s.
+int choose_yvo_splits(const mpccb_ctx* c) {
+  const int o = c->o;
+  if (!c->use_tma || o % TMA_TK != 0 || o > 128 || (128 / o) * o < 96) return 1;
+  const int n_a = 128 / o;
+  const i64 T = (i64)cdiv(c->na, n_a) * cdiv(c->L, 128);
+  const i64 nk = (i64)c->v * (o / TMA_TK);
+  if (c->yvo_split_force > 0) return (int)std::min<i64>(c->yvo_split_force, nk);
+  double best = (double)cdiv(T, NSM);
+  int best_s = 1;
+  for (int s = 2; s <= 8; ++s) {
+    if (nk / s < 64) break;
+    const double w = (double)cdiv(T * s, NSM) / s + 0.01 * s;      // small bias against needless splitting
+    if (w < best * 0.98) { best = w; best_s = s; }
+  }
+  return best_s;
+}
+
 // lays the scratch tensors out in the workspace; with base == nullptr only sizes it
 i64 carve_workspace(mpccb_ctx* c, unsigned char* base) {
   const i64 o = c->o, v = c->v, L = c->L, nov = c->nov, ldk = c->ldk, na = c->na;
@@ -233,6 +256,8 @@ i64 carve_workspace(mpccb_ctx* c, unsigned char* base) {
   c->OmP_count = (i64)c->t2_tiles_n * na * o;
   c->OmP = w.take(c->OmP_count);
   c->Y = w.take(nov * L);
+  c->yvo_split = choose_yvo_splits(c);
+  c->YP = w.take(c->yvo_split > 1 ? (i64)c->yvo_split * na * o * L : 0);
   i64 p = 0;
   auto mx = [&](i64 x) { if (x > p) p = x; };
   mx(splitk_scratch((int)v, (int)o, (int)(L * o), 128, 64));   // S5, S6
@@ -350,6 +375,11 @@ int mpccb_set_option(mpccb_ctx* c, const char* name, long long value) {
     return 0;
   }
   if (!strcmp(name, "profile")) { c->profile = value != 0; return 0; }
+  if (!strcmp(name, "yvo_split")) {       // force the split-K factor of the TMA Yvo GEMM (0 = automatic; before bind_workspace)
+    if (c->ws) return fail(c, "set yvo_split before binding the workspace");
+    c->yvo_split_force = (int)value;
+    return 0;
+  }
   if (!strcmp(name, "t2_unfused")) {      // 1: always GEMM -> T, then in-place k_t2_finalize (before bind_workspace)
     if (c->ws) return fail(c, "set t2_unfused before binding the workspace");
     c->force_unfused = value != 0;
@@ -532,7 +562,7 @@ int launch_tma(mpccb_ctx* c, const char* what, const CUtensorMap& mA, const CUte
     CUDA_OK(c, cudaFuncSetAttribute(gemm_tma_kernel<EPI, WN>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
     attr_done = true;
   }
-  gemm_tma_kernel<EPI, WN><<<p.tiles_m * p.tiles_n, Cfg::THREADS, smem, c->stream>>>(mA, mB, p, t2p);
+  gemm_tma_kernel<EPI, WN><<<p.tiles_total > 0 ? p.tiles_total : p.tiles_m * p.tiles_n, Cfg::THREADS, smem, c->stream>>>(mA, mB, p, t2p);
   LAUNCH_OK(c, what);
   return 0;
 }
@@ -584,10 +614,23 @@ int launch_yvo_tma(mpccb_ctx* c) {
   p.nk = v * (o / TMA_TK);
   p.a_mode = 1; p.jsteps = o / TMA_TK; p.o = o; p.n_a = n_a;
   p.a_bytes = (uint32_t)(TMA_TK * o * n_a * 8); p.b_bytes = TN * TMA_TK * 8;
-  p.C = c->Y + (i64)c->a_begin * o * L; p.ldc = L;
+  double* Yslab = c->Y + (i64)c->a_begin * o * L;
+  p.C = Yslab; p.ldc = L;
+  p.ksplit = 1;
+  const int splits = c->yvo_split;
+  if (splits > 1) {
+    p.ksplit = splits; p.nk_split = cdiv(p.nk, splits);
+    p.ksplit = cdiv(p.nk, p.nk_split);
+    p.C = c->YP; p.split_stride = (i64)c->na * o * L;
+  }
   T2Params t;
   memset(&t, 0, sizeof(t));
-  return launch_tma<0, 4>(c, "gemm_tma_kernel<store>", mA, mB, p, t);
+  const int ntiles = p.tiles_m * p.tiles_n;
+  p.tiles_total = ntiles * p.ksplit;
+  if (launch_tma<0, 4>(c, "gemm_tma_kernel<store>", mA, mB, p, t)) return 1;
+  if (p.ksplit > 1)
+    return reduce_splits(c, Yslab, c->YP, p.ksplit, (i64)c->na * o * L, p.split_stride, 1.0, 0.0);
+  return 0;
 }
 
 // unfused form of :135-137,:139 for occupied counts that tile badly: e -> T[a][b][i][j] with the
@@ -801,6 +844,52 @@ extern "C" int mpccb_diis_combine(mpccb_ctx* c, const double* const* x_list_dev,
   const int nb = (int)std::min<i64>(cdiv(n, 256), 148 * 16);
   k_diis_combine<<<nb, 256, 0, c->stream>>>(cb, nd, xnew_dev, n);
   LAUNCH_OK(c, "k_diis_combine");
+  return 0;
+}
+
+// ===========================================================================
+// AO -> MO transform of the Cholesky tensor (reference compute_three_center_ints, :46-69)
+// ===========================================================================
+extern "C" size_t mpccb_ao2mo_scratch_bytes(const mpccb_ctx* c, int nb) {
+  const i64 nao = c->o + c->v;
+  return (size_t)(2 * (i64)nb * nao * nao * sizeof(double));
+}
+
+// packed_dev: nb rows of nao(nao+1)/2 (lower triangle, row-major) = one block of with_df.loop();
+// C_dev: mo_coeff (nao x nao, row-major, columns = MOs). Writes Loo/Lov/Lvv[l0 : l0+nb].
+//   full = unpack_tril(packed);  half[(l,mu)][q] = sum_nu full[(l,mu)][nu] C[nu][q];
+//   Lxy[l][p][q] = sum_mu C[mu][p] half[l][mu][q]   for the oo, ov and vv blocks (the vo block is skipped)
+extern "C" int mpccb_ao2mo_block(mpccb_ctx* c, const double* packed_dev, int nb, int l0, const double* C_dev,
+                                 double* Loo_dev, double* Lov_dev, double* Lvv_dev, void* scratch_dev,
+                                 size_t scratch_bytes) {
+  const int o = c->o, v = c->v, nao = o + v;
+  if (nb <= 0 || l0 < 0 || l0 + nb > c->L) return fail(c, "bad auxiliary block [%d,%d)", l0, l0 + nb);
+  if (scratch_bytes < mpccb_ao2mo_scratch_bytes(c, nb)) return fail(c, "ao2mo scratch too small");
+  if ((i64)nb * nao > (i64)INT_MAX) return fail(c, "auxiliary block too large");
+  double* full = static_cast<double*>(scratch_dev);
+  double* half = full + (i64)nb * nao * nao;
+  k_unpack_tril_sym<<<dim3(nao, nb), 256, 0, c->stream>>>(packed_dev, full, nao, (i64)nao * (nao + 1) / 2);
+  LAUNCH_OK(c, "k_unpack_tril_sym");
+  {
+    Operand A = flat_operand(full, nb * nao, nao, 1);
+    Operand B = flat_operand(C_dev, nao, 1, nao);
+    Output C = flat_output(half, nao, 1);
+    if (launch_gemm<CfgBigKR>(c, "ao2mo.half", A, B, C, nb * nao, nao, nao, 1, nullptr)) return 1;
+  }
+  struct Blk { int p0, np, q0, nq; double* out; };
+  const Blk blks[3] = {{0, o, 0, o, Loo_dev + (i64)l0 * o * o}, {0, o, o, v, Lov_dev + (i64)l0 * o * v},
+                       {o, v, o, v, Lvv_dev + (i64)l0 * v * v}};
+  for (const Blk& b : blks) {
+    Operand A = flat_operand(C_dev + b.p0, b.np, 1, nao);              // (p, mu) -> C[mu][p0 + p]
+    Operand B;                                                        // ((l,q), mu) -> half[l][mu][q0 + q]
+    B.base = half + b.q0; B.rows = nb * b.nq;
+    B.rdiv = b.nq; B.r_hi = (i64)nao * nao; B.r_lo = 1;
+    B.kdiv = BIG; B.k_hi = 0; B.k_lo = nao;
+    Output C = flat_output(b.out, b.nq, 0);                           // out[l][p][q]
+    C.ndiv = b.nq; C.n_hi = (i64)b.np * b.nq; C.n_lo = 1;
+    if (b.np > 64) { if (launch_gemm<CfgBigRR>(c, "ao2mo.full", A, B, C, b.np, nb * b.nq, nao, 1, nullptr)) return 1; }
+    else           { if (launch_gemm<CfgM64RR>(c, "ao2mo.full", A, B, C, b.np, nb * b.nq, nao, 1, nullptr)) return 1; }
+  }
   return 0;
 }
 

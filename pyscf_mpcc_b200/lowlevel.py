@@ -101,7 +101,7 @@ class DeviceT2:
 class MPCC_LL:
     """GPU-resident equivalent of ``pyscf.mpcc.dfrmpcc_lowlevel.MPCC_LL``."""
 
-    def __init__(self, mf=None, *, blocks=None, device=None, group=None, use_tma=True, t2_wide_tiles=None, t2_unfused=None):
+    def __init__(self, mf=None, *, blocks=None, device=None, group=None, use_tma=True, t2_wide_tiles=None, t2_unfused=None, yvo_split=None):
         """``MPCC_LL(mf)`` as in the reference (:7-43). Extensions (keyword only):
 
         blocks : (Loo, Lov, Lvv, foo, fvv, mo_energy) numpy arrays or CUDA tensors
@@ -164,6 +164,8 @@ class MPCC_LL:
         self._ctx.call("mpccb_set_option", b"tma", int(bool(use_tma)))
         if t2_wide_tiles is None and os.environ.get("MPCC_T2_WIDE_TILES"):
             t2_wide_tiles = os.environ["MPCC_T2_WIDE_TILES"] != "0"
+        if yvo_split is not None:
+            self._ctx.call("mpccb_set_option", b"yvo_split", int(yvo_split))
         if t2_unfused is not None:
             self._ctx.call("mpccb_set_option", b"t2_unfused", int(bool(t2_unfused)))
         if t2_wide_tiles is not None:      # tuning knob: 128x128 tiles (1 CTA/SM) vs 128x64 (2 CTAs/SM) for eris->t2
@@ -289,31 +291,34 @@ class MPCC_LL:
 
     # ------------------------------------------------------------------ :46-69
     def compute_three_center_ints(self):
-        """AO->MO transform of the Cholesky tensor, block by block as ``with_df.loop()``
-        yields it, then upload. Host BLAS; T1-independent, once per solve (device
-        version is SURVEY.md §8f row f3)."""
-        nao, o = self.nao, self.nocc
-        C = self.mo_coeff
-        r, c = np.tril_indices(nao)
-        Loo = torch.empty((self.naux, o, o), dtype=torch.float64, device=self.device)
-        Lov = torch.empty((self.naux, o, nao - o), dtype=torch.float64, device=self.device)
-        Lvv = torch.empty((self.naux, nao - o, nao - o), dtype=torch.float64, device=self.device)
-        identity = C.shape == (nao, nao) and np.array_equal(C, np.eye(nao))
-        p1 = 0
+        """AO->MO transform of the Cholesky tensor (:46-69), block by block as ``with_df.loop()``
+        yields it: the packed rows are uploaded and unpacked, transformed (two DMMA GEMM passes) and
+        sliced into Loo/Lov/Lvv on the device (``mpccb_ao2mo_block``). T1-independent, once per solve."""
+        nao, o, L = self.nao, self.nocc, self.naux
+        f64 = dict(dtype=torch.float64, device=self.device)
+        Loo = torch.empty((L, o, o), **f64)
+        Lov = torch.empty((L, o, nao - o), **f64)
+        Lvv = torch.empty((L, nao - o, nao - o), **f64)
+        C = self._to_dev(self.mo_coeff)
+        if tuple(C.shape) != (nao, nao):
+            raise ValueError("mo_coeff must be (nao, nao): no frozen orbitals on this path (:23-25)")
+        scratch, p1 = None, 0
         for packed in self.with_df.loop():
-            nb = packed.shape[0]
-            full = np.empty((nb, nao, nao))
-            full[:, r, c] = packed
-            full[:, c, r] = packed
-            if not identity:
-                half = (full.reshape(nb * nao, nao) @ C).reshape(nb, nao, nao)        # [L, mu, q]
-                full = np.matmul(C.T[None, :, :], half)                                # [L, p, q]
-            p0, p1 = p1, p1 + nb
-            Loo[p0:p1] = torch.from_numpy(np.ascontiguousarray(full[:, :o, :o]))
-            Lov[p0:p1] = torch.from_numpy(np.ascontiguousarray(full[:, :o, o:]))
-            Lvv[p0:p1] = torch.from_numpy(np.ascontiguousarray(full[:, o:, o:]))
+            nb = int(packed.shape[0])
+            blk = self._to_dev(packed)
+            need = int(self._ctx.lib.mpccb_ao2mo_scratch_bytes(self._ctx.h, nb))
+            if scratch is None or scratch.numel() < need:
+                scratch = torch.empty(need, dtype=torch.uint8, device=self.device)
+            self._ctx.call("mpccb_ao2mo_block", blk.data_ptr(), nb, p1, C.data_ptr(), Loo.data_ptr(),
+                           Lov.data_ptr(), Lvv.data_ptr(), scratch.data_ptr(), need)
+            self.h2d_bytes = getattr(self, "h2d_bytes", 0) + blk.numel() * 8
+            p1 += nb
+        if p1 != L:
+            raise ValueError(f"with_df.loop() yielded {p1} auxiliary rows, get_naoaux() says {L}")
+        self._sync()
         self._d = {"Loo": Loo, "Lov": Lov, "Lvv": Lvv}
 
+    # ------------------------------------------------------------------ :103-152
     def _dress(self, t1_dev):
         """T1 dressing (:119-133). One rank: a single native call. Several ranks: each dresses its own
         virtual slab, the dressed integrals Jvo (rows of the K-major JK buffer; a slab is a contiguous

@@ -72,6 +72,22 @@ def test_updated_amps_known_answers(path, tag):
     assert ll.update_amps.__func__ is ll.updated_amps.__func__
 
 
+@pytest.mark.parametrize("split", [2, 3, 5])
+def test_yvo_split_k_matches_oracle(split):
+    """Split-K form of the TMA Yvo GEMM (used when a rank's slab has few tiles) against the oracle."""
+    from oracle.mpcc_oracle import LowLevelOracle
+    o, v, L = 32, 70, 129
+    mf, ll = _solver(o, v, L, 0.05, seed=4, yvo_split=split)
+    orc = LowLevelOracle(mf, mode="blas")
+    t1 = 0.03 * np.random.default_rng(12).standard_normal((o, v))
+    ll.t1 = t1
+    res, dE, t1n, t2 = ll.updated_amps()
+    res_o, dE_o, t1n_o, t2_o = orc.updated_amps(t1)
+    Y = np.einsum("aibj,Ljb->aiL", t2_o, orc.Lov, optimize=True).reshape(v * o, L)
+    assert np.abs(ll.debug_buffer("Y").reshape(v * o, L) - Y).max() <= 1e-12 * max(1.0, np.abs(Y).max())
+    assert abs(dE - dE_o) <= E_TOL and np.abs(t1n - t1n_o).max() <= AMP_TOL
+
+
 @pytest.mark.parametrize("variant", ["default", "wide", "unfused", "no_tma"])
 def test_t2_kernel_variants_agree_with_fixture(variant):
     """All forms of the eris -> t2 step (128x64 two-CTA tiles, 128x128 tiles, unfused GEMM + in-place pass,
@@ -203,3 +219,28 @@ def test_dmma_gemm_against_fp64_matmul(mnk):
     ref = a @ b.T
     assert torch.isfinite(c).all()
     assert (c - ref).abs().max().item() <= 1e-12 * max(1.0, ref.abs().max().item()) * max(1, k) ** 0.5
+
+
+@pytest.mark.parametrize("shape", [(5, 19, 116), (16, 48, 150), (70, 90, 250)])
+def test_device_ao2mo_with_rotated_orbitals(shape):
+    """compute_three_center_ints on the device (unpack_tril + two GEMM passes + slicing, :46-69) with a
+    non-trivial mo_coeff, several with_df.loop() blocks (naux > 240) and a ragged last block."""
+    from oracle.mpcc_oracle import LowLevelOracle
+    from pyscf_mpcc_b200.lowlevel import MPCC_LL
+    from pyscf_mpcc_b200.synthetic import SyntheticMF
+    o, v, L = shape
+    mf = SyntheticMF(o, v, L, seed=5, scale=0.1)
+    q, _ = np.linalg.qr(np.random.default_rng(9).standard_normal((o + v, o + v)))
+    mf.mo_coeff = q
+    mf.get_fock = lambda: q @ np.diag(mf.mo_energy) @ q.T
+    ll = MPCC_LL(mf)
+    ll.verbose_print = False
+    orc = LowLevelOracle(mf, mode="blas")
+    for name in ("Loo", "Lov", "Lvv"):
+        ref = getattr(orc, name)
+        assert np.abs(getattr(ll, name) - ref).max() <= 1e-12 * max(1.0, np.abs(ref).max()), name
+    assert np.abs(ll.foo - orc.foo).max() <= 1e-12 and np.abs(ll.fvv - orc.fvv).max() <= 1e-12
+    e = ll.kernel()
+    e_o = orc.kernel()
+    assert ll.iterations == orc.iterations and abs(e - e_o) <= E_TOL
+    assert np.abs(ll.t1 - orc.t1).max() <= AMP_TOL
