@@ -320,7 +320,7 @@ def run_b200(args):
         "config": {"workload": f"synthetic DF-MPCC nocc={o} nvir={v} naux={L} (BASELINE.json configs[2])",
                    "step": "updated_amps + run_diis (first K iterations of a solve from t1=0, DIIS on)",
                    "l2": "inputs_exceed_l2 (t2 buffer 8.6 GB, DIIS vectors 4.3 GB each at the default shape)",
-                   "parallelism": f"a-slab x{world}", "flop_per_iteration": flop_it},
+                   "parallelism": f"a-slab x{world}", "jk_exchange": ll._jk_mode, "flop_per_iteration": flop_it},
         "e2e": {"value": tflops_e2e, "unit": "TFLOP/s", "ms_per_step": ms_e2e / K,
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "note": "integrals are uploaded once per solve at construction, as the reference builds them once"},

@@ -55,6 +55,15 @@ int mpccb_ao2mo_block(mpccb_ctx* ctx, const double* packed_dev, int nb, int l0, 
 /* t2 buffer in [a - a_begin, b, i, j] order: (a_end-a_begin)*v*o*o doubles */
 int mpccb_bind_t2(mpccb_ctx* ctx, double* t2_abij_dev);
 
+/* Several ranks, fused all-gather of the dressed integrals: every rank allocates its JK buffer
+ * (nov * ldk doubles, ldk = naux rounded up to even, zero-filled) in peer-mapped symmetric memory and binds
+ * (a) its own buffer, (b) either the device pointers of all ranks' buffers (npeers of them, own rank included)
+ * or the NVSwitch multicast address of the allocation. mpccb_dress then stores the slab's JK rows directly into
+ * every rank's buffer over NVLink (no separate all-gather); the caller only has to run a cross-rank barrier on
+ * the stream before mpccb_dress_post. Optional: without it the caller all-gathers the "JK" buffer itself. */
+int mpccb_bind_jk_exchange(mpccb_ctx* ctx, double* jk_local_dev, double* const* peer_jk_dev, int npeers,
+                           double* jk_multicast_dev);
+
 /* ---- one residual evaluation: MPCC_LL.updated_amps (dfrmpcc_lowlevel.py:103-152) --- */
 /* phase 1, :119-133 — T1 dressing and singles intermediates. Everything that carries a virtual index is
  * computed for the context's slab only (rows [a_begin*o, a_end*o) of JK = Jvo in [(a,i)][ldk] order,

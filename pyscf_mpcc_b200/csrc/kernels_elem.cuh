@@ -43,11 +43,20 @@ k_trace(const double* __restrict__ Xoo, double* __restrict__ X, int L, int o) {
 //   e1 = XT + X[L]*t1[i,a] + J               -> E1K[(a,i)][ldk]
 //   W  = XT - Xov                            -> Wov[L][i][a]
 // grid (ceil(v/32), ceil(L/32), o), block (32, 8)
+// Where the dressed integrals go. One rank: the local JK buffer. Several ranks, fused all-gather: every
+// rank's JK buffer lives in symmetric (peer-mapped) memory and the kernel stores its slab's rows straight
+// into all of them over NVLink — either one store per peer pointer, or a single store to the NVSwitch
+// multicast address that the switch replicates to every rank (n == 1, p[0] = multicast pointer).
+struct JkTargets {
+  double* p[16];
+  int n;
+};
+
 __global__ void __launch_bounds__(256)
 k_dress_finalize(const double* __restrict__ Xov, const double* __restrict__ Lov,
                  const double* __restrict__ JT, const double* __restrict__ XT,
                  const double* __restrict__ X, const double* __restrict__ t1,
-                 double* __restrict__ JK, double* __restrict__ E1K, double* __restrict__ Wov,
+                 JkTargets jk, double* __restrict__ E1K, double* __restrict__ Wov,
                  int L, int o, int v, int ldk, int a_lo, int a_hi) {
   // only the virtual columns a in [a_lo, a_hi) (this rank's slab) are produced; grid.x covers the slab
   __shared__ double tj[32][33];
@@ -72,7 +81,8 @@ k_dress_finalize(const double* __restrict__ Xov, const double* __restrict__ Lov,
     const int aa = a0 + dy, l = l0 + threadIdx.x;
     if (aa < a_hi && l < L) {
       const i64 off = ((i64)aa * o + i) * ldk + l;
-      JK[off] = tj[threadIdx.x][dy];
+      const double jv = tj[threadIdx.x][dy];
+      for (int t = 0; t < jk.n; ++t) jk.p[t][off] = jv;      // local, peer (NVLink) or multicast store
       E1K[off] = te[threadIdx.x][dy];
     }
   }

@@ -48,6 +48,7 @@ struct mpccb_ctx {
   double *Lvo, *t1, *t1T, *t1n, *Xov, *Xoo, *Joo, *X, *XT, *JT, *JK, *E1K, *Wov, *w, *F2, *Fvo, *OmP, *Y,
       *P, *OmRep, *OmLoc, *OmTot, *Z, *scal, *red, *YP;
   int yvo_split, yvo_split_force;
+  JkTargets jk_targets;      // n == 0: plain local JK
   i64 P_count, OmP_count;
   int t2_na, t2_nb, t2_tiles_m, t2_tiles_n, t2_wn, t2_unfused, force_unfused;
   // optional per-stage CUDA-event timing (mpccb_set_option("profile", 1))
@@ -425,6 +426,23 @@ int mpccb_bind_integrals(mpccb_ctx* c, const double* Loo, const double* Lov, con
 
 int mpccb_bind_t2(mpccb_ctx* c, double* T) { c->T = T; return 0; }
 
+int mpccb_bind_jk_exchange(mpccb_ctx* c, double* jk_local_dev, double* const* peer_jk_dev, int npeers,
+                           double* jk_multicast_dev) {
+  if (!c->ws) return fail(c, "bind the workspace first");
+  if (!jk_local_dev) return fail(c, "null JK buffer");
+  if (npeers < 0 || npeers > 16) return fail(c, "at most 16 peers");
+  c->JK = jk_local_dev;
+  if (jk_multicast_dev) {
+    c->jk_targets.n = 1;
+    c->jk_targets.p[0] = jk_multicast_dev;
+  } else {
+    c->jk_targets.n = npeers;
+    for (int r = 0; r < npeers; ++r) c->jk_targets.p[r] = peer_jk_dev[r];
+    if (npeers == 0) { c->jk_targets.n = 1; c->jk_targets.p[0] = jk_local_dev; }
+  }
+  return 0;
+}
+
 }  // extern "C"
 
 // ===========================================================================
@@ -476,7 +494,9 @@ extern "C" int mpccb_dress(mpccb_ctx* c, const double* t1_dev) {
   }
   {  // :124, :146 integrand, W = XT - Xov   (columns a of the slab -> JK/E1K rows of the slab)
     dim3 grid(cdiv(na, 32), cdiv(L, 32), o), block(32, 8);
-    k_dress_finalize<<<grid, block, 0, c->stream>>>(c->Xov, c->Lov, c->JT, c->XT, c->X, c->t1, c->JK, c->E1K,
+    JkTargets jk = c->jk_targets;
+    if (jk.n == 0) { jk.n = 1; jk.p[0] = c->JK; }
+    k_dress_finalize<<<grid, block, 0, c->stream>>>(c->Xov, c->Lov, c->JT, c->XT, c->X, c->t1, jk, c->E1K,
                                                     c->Wov, L, o, v, c->ldk, a0, a0 + na);
     LAUNCH_OK(c, "k_dress_finalize");
   }

@@ -23,6 +23,7 @@ energy lagging the amplitudes by one update, convergence tested on T1 only.
 """
 from __future__ import annotations
 
+import ctypes
 import os
 import sys
 
@@ -101,7 +102,8 @@ class DeviceT2:
 class MPCC_LL:
     """GPU-resident equivalent of ``pyscf.mpcc.dfrmpcc_lowlevel.MPCC_LL``."""
 
-    def __init__(self, mf=None, *, blocks=None, device=None, group=None, use_tma=True, t2_wide_tiles=None, t2_unfused=None, yvo_split=None):
+    def __init__(self, mf=None, *, blocks=None, device=None, group=None, use_tma=True, t2_wide_tiles=None, t2_unfused=None, yvo_split=None,
+                 jk_exchange=None):
         """``MPCC_LL(mf)`` as in the reference (:7-43). Extensions (keyword only):
 
         blocks : (Loo, Lov, Lvv, foo, fvv, mo_energy) numpy arrays or CUDA tensors
@@ -175,16 +177,9 @@ class MPCC_LL:
         self._ws = torch.empty(self._ctx.workspace_bytes() + 256, dtype=torch.uint8, device=self.device)
         ws_ptr = (self._ws.data_ptr() + 255) // 256 * 256
         self._ctx.call("mpccb_bind_workspace", ws_ptr, self._ctx.workspace_bytes())
+        self._jk_mode = "local"
         if self.world_size > 1:
-            ptr, count = self._ctx.buffer("JK")
-            off = ptr - self._ws.data_ptr()
-            ldk = count // self.nov
-            self._jk_view = self._ws[off:off + count * 8].view(torch.float64)
-            self._jk_rows = []
-            for r in range(self.world_size):
-                b0, b1 = sharding.slab_bounds(v, self.world_size, r)
-                self._jk_rows.append((b0 * o * ldk, b1 * o * ldk))
-            self._equal_slabs = len({hi - lo for lo, hi in self._jk_rows}) == 1
+            self._setup_jk_exchange(jk_exchange or os.environ.get("MPCC_JK_EXCHANGE", "auto"))
         self._T = torch.empty(self._na * v * o * o, **f64)
         self._ctx.call("mpccb_bind_t2", self._T.data_ptr())
         self._t2_serial = 0
@@ -319,6 +314,52 @@ class MPCC_LL:
         self._d = {"Loo": Loo, "Lov": Lov, "Lvv": Lvv}
 
     # ------------------------------------------------------------------ :103-152
+    def _setup_jk_exchange(self, mode):
+        """How the slab-dressed integrals Jvo reach every rank.
+
+        "multicast" / "p2p": the JK buffers live in symmetric (peer-mapped) memory and the dressing kernel
+        stores its rows into every rank's buffer itself — through the NVSwitch multicast address when the
+        allocation has one, else one NVLink store per peer; only a stream barrier follows.
+        "nccl": slab-local store + ``all_gather_into_tensor``. "auto" tries the fused forms first; all ranks
+        agree on the outcome (a failed rendezvous on any rank sends everyone to "nccl")."""
+        dist = torch.distributed
+        o, v = self.nocc, self.nvir
+        ptr, count = self._ctx.buffer("JK")
+        ldk = count // self.nov
+        if mode not in ("auto", "multicast", "p2p", "nccl"):
+            raise ValueError(f"jk_exchange={mode!r}")
+        ok, hdl, buf = 0, None, None
+        if mode != "nccl":
+            try:
+                import torch.distributed._symmetric_memory as symm
+                buf = symm.empty(count, dtype=torch.float64, device=self.device)
+                hdl = symm.rendezvous(buf, self.group)
+                ok = 1
+            except Exception as e:                      # no peer mapping on this system: use NCCL
+                self._jk_exchange_error = repr(e)
+        flag = torch.tensor([ok], device=self.device)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=self.group)
+        if int(flag.item()) == 1:
+            buf.zero_()                                  # K padding columns must read as zero
+            self._sync()
+            torch.cuda.current_stream(self.device).synchronize()
+            hdl.barrier(channel=0)                       # nobody stores into a buffer that is still being cleared
+            mc = int(getattr(hdl, "multicast_ptr", 0) or 0)
+            use_mc = mc != 0 and mode in ("auto", "multicast")
+            peers = (ctypes.c_void_p * self.world_size)(*[int(p) for p in hdl.buffer_ptrs])
+            self._ctx.call("mpccb_bind_jk_exchange", buf.data_ptr(), peers, self.world_size, mc if use_mc else None)
+            self._jk_buf, self._jk_hdl = buf, hdl
+            self._jk_mode = "multicast" if use_mc else "p2p"
+            return
+        off = ptr - self._ws.data_ptr()
+        self._jk_view = self._ws[off:off + count * 8].view(torch.float64)
+        self._jk_rows = []
+        for r in range(self.world_size):
+            b0, b1 = sharding.slab_bounds(v, self.world_size, r)
+            self._jk_rows.append((b0 * o * ldk, b1 * o * ldk))
+        self._equal_slabs = len({hi - lo for lo, hi in self._jk_rows}) == 1
+        self._jk_mode = "nccl"
+
     def _dress(self, t1_dev):
         """T1 dressing (:119-133). One rank: a single native call. Several ranks: each dresses its own
         virtual slab, the dressed integrals Jvo (rows of the K-major JK buffer; a slab is a contiguous
@@ -327,13 +368,17 @@ class MPCC_LL:
         ctx.call("mpccb_dress", t1_dev.data_ptr())
         if self.world_size == 1:
             return
-        jk, rows = self._jk_view, self._jk_rows
-        if self._equal_slabs:
-            torch.distributed.all_gather_into_tensor(jk, jk[rows[self.rank][0]:rows[self.rank][1]], group=self.group)
+        if self._jk_mode in ("multicast", "p2p"):
+            self._jk_hdl.barrier(channel=0)              # every rank's rows have landed in every buffer
         else:
-            for r, (lo, hi) in enumerate(rows):
-                torch.distributed.broadcast(jk[lo:hi], src=torch.distributed.get_global_rank(self.group, r),
-                                            group=self.group)
+            jk, rows = self._jk_view, self._jk_rows
+            if self._equal_slabs:
+                torch.distributed.all_gather_into_tensor(jk, jk[rows[self.rank][0]:rows[self.rank][1]],
+                                                         group=self.group)
+            else:
+                for r, (lo, hi) in enumerate(rows):
+                    torch.distributed.broadcast(jk[lo:hi], src=torch.distributed.get_global_rank(self.group, r),
+                                                group=self.group)
         ctx.call("mpccb_dress_post")
 
     # ------------------------------------------------------------------ :103-152

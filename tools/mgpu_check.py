@@ -55,7 +55,7 @@ def main():
         flag = torch.tensor([0 if ok else 1], device=dev)
         dist.all_reduce(flag)
         if rank == 0:
-            print(f"{os.path.basename(path)} world={world} its={ll.iterations} E={e:.12e} "
+            print(f"{os.path.basename(path)} world={world} jk={ll._jk_mode} its={ll.iterations} E={e:.12e} "
                   f"{'OK' if flag.item() == 0 else 'MISMATCH'}", flush=True)
         bad += int(flag.item())
         del ll
