@@ -244,3 +244,48 @@ def test_device_ao2mo_with_rotated_orbitals(shape):
     e_o = orc.kernel()
     assert ll.iterations == orc.iterations and abs(e - e_o) <= E_TOL
     assert np.abs(ll.t1 - orc.t1).max() <= AMP_TOL
+
+
+@pytest.mark.parametrize("shape", [(1, 1, 1, 0.3), (1, 3, 4, 0.3), (2, 1, 3, 0.3), (3, 2, 1, 0.3), (1, 40, 17, 0.2),
+                                   (6, 300, 20, 0.05), (40, 41, 33, 0.05)])
+def test_degenerate_and_ragged_shapes(shape):
+    """Smallest possible problems (one occupied / one virtual / one auxiliary function), shapes far from
+    any tile multiple: full kernel() against the oracle (iteration count, energy, amplitudes)."""
+    from oracle.mpcc_oracle import LowLevelOracle
+    o, v, L, scale = shape
+    mf, ll = _solver(o, v, L, scale, seed=7)
+    ll.max_its = 12
+    e = ll.kernel()
+    orc = LowLevelOracle(mf, mode="blas")
+    orc.max_its = 12
+    e_o = orc.kernel()
+    assert ll.iterations == orc.iterations
+    assert abs(e - e_o) <= E_TOL and np.abs(ll.t1 - orc.t1).max() <= AMP_TOL
+    assert np.abs(np.asarray(ll.t2) - orc.t2).max() <= AMP_TOL
+    for (k, de, r), (k2, de2, r2) in zip(ll.history, orc.history):
+        assert abs(de - de2) <= E_TOL and abs(r - r2) <= 1e-9 * max(1.0, r2)
+
+
+def test_errors_are_loud():
+    """Bad arguments raise (int status + message through the C ABI), nothing falls back silently."""
+    from pyscf_mpcc_b200 import _cabi
+    with pytest.raises(_cabi.MpccError):
+        _cabi.Context(0, 4, 4, 0, 4, 0)                      # nocc must be positive
+    with pytest.raises(_cabi.MpccError):
+        _cabi.Context(2, 4, 4, 3, 2, 0)                      # empty slab
+    ctx = _cabi.Context(2, 4, 4, 0, 4, 0)
+    with pytest.raises(_cabi.MpccError):
+        ctx.call("mpccb_dress", None)                        # workspace/integrals not bound
+    with pytest.raises(_cabi.MpccError):
+        ctx.call("mpccb_set_option", b"no_such_option", 1)
+    import pyscf_mpcc_b200
+
+    class UHF:                                               # the factory rejects unrestricted mean fields
+        pass
+    with pytest.raises(RuntimeError, match="UMPCC"):
+        pyscf_mpcc_b200.MPCC(UHF())
+    from pyscf_mpcc_b200.synthetic import SyntheticMF
+    mf = SyntheticMF(2, 3, 4)
+    mf.with_df = None
+    with pytest.raises(RuntimeError):
+        pyscf_mpcc_b200.MPCC(mf)
