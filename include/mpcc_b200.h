@@ -130,6 +130,24 @@ int mpccb_set_option(mpccb_ctx* ctx, const char* name, long long value);
 int mpccb_gemm_nt(mpccb_ctx* ctx, const double* A_dev, const double* B_dev, double* C_dev,
                   int M, int N, int K);
 
+/* ---- tensor engine for the CCSD-type residual terms: the reference evaluates
+ *      pyscf/cc/rmpccsd_slow.py:73-180 and pyscf/cc/rintermediates.py:29-130 as a list of lib.einsum calls
+ *      (-> lib.dot -> NPdgemm, pyscf/lib/numpy_helper.py:101-252, pyscf/lib/np_helper/npdot.c:32-139); here every
+ *      einsum is permute -> mpccb_gemm_nt (DMMA) -> permute/accumulate on the device. ------------------------ */
+/* out = alpha * transpose(in, perm) + beta * out; numpy semantics (out axis d = in axis perm[d]); rank <= 6 */
+int mpccb_permute_axpby(mpccb_ctx* ctx, const double* in_dev, double* out_dev, int rank, const int* in_dims,
+                        const int* perm, double alpha, double beta);
+/* t1[i,a] /= eps_o[i]-eps_v[a] (rank 2) or t2[i,j,a,b] /= eps_o[i]+eps_o[j]-eps_v[a]-eps_v[b] (rank 4)
+ * (rmpccsd_slow.py:164-169) */
+int mpccb_div_denominators(mpccb_ctx* ctx, double* t_dev, int rank);
+/* active-space overwrite tnew[idx] = told[idx] (rmpccsd_slow.py:171-178, index classes of get_index_tuples :39-71):
+ * bit (2*act_h[i] + act_p[a]) of class_mask for singles, bit (8*act_h[i] + 4*act_h[j] + 2*act_p[a] + act_p[b]) for
+ * doubles; act_h_dev / act_p_dev are 0/1 int flags per occupied / virtual orbital */
+int mpccb_class_overwrite(mpccb_ctx* ctx, double* tnew_dev, const double* told_dev, int rank,
+                          const int* act_h_dev, const int* act_p_dev, unsigned class_mask);
+/* out_dev[0] = x . y (deterministic two-pass reduction) */
+int mpccb_dot(mpccb_ctx* ctx, const double* x_dev, const double* y_dev, long long n, double* out_dev);
+
 #ifdef __cplusplus
 }
 #endif

@@ -55,6 +55,11 @@ SIGNATURES = {
     "mpccb_profile_stage_name": (ctypes.c_char_p, [c_int]),
     "mpccb_profile_read": (c_int, [c_void_p, c_double_p, ctypes.POINTER(c_ll)]),
     "mpccb_set_option": (c_int, [c_void_p, ctypes.c_char_p, c_ll]),
+    "mpccb_permute_axpby": (c_int, [c_void_p, c_void_p, c_void_p, c_int, ctypes.POINTER(c_int), ctypes.POINTER(c_int),
+                                    ctypes.c_double, ctypes.c_double]),
+    "mpccb_div_denominators": (c_int, [c_void_p, c_void_p, c_int]),
+    "mpccb_class_overwrite": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, ctypes.c_uint]),
+    "mpccb_dot": (c_int, [c_void_p, c_void_p, c_void_p, c_ll, c_void_p]),
     "mpccb_gemm_nt": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int]),
 }
 

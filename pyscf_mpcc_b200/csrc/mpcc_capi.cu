@@ -6,6 +6,7 @@
 #include "gemm_dmma.cuh"
 #include "gemm_tma.cuh"
 #include "kernels_elem.cuh"
+#include "kernels_tensor.cuh"
 
 #include <algorithm>
 #include <climits>
@@ -945,10 +946,116 @@ extern "C" int mpccb_copy_to_device(mpccb_ctx* c, const double* src, double* dst
   return 0;
 }
 
+// C[m][n] = sum_k A[m][k] B[n][k], all row-major contiguous. Large products whose rows are 16-byte aligned go
+// through the TMA-fed kernel (same code as the Yvo GEMM), everything else through the generic DMMA kernel.
 extern "C" int mpccb_gemm_nt(mpccb_ctx* c, const double* A_dev, const double* B_dev, double* C_dev,
                              int M, int N, int K) {
+  if (M <= 0 || N <= 0 || K <= 0) return fail(c, "gemm_nt: empty product");
+  const bool aligned = (K % 2 == 0) && ((reinterpret_cast<uintptr_t>(A_dev) | reinterpret_cast<uintptr_t>(B_dev)) & 15) == 0;
+  if (c->use_tma && aligned && K >= 64 && (double)M * N * K >= 5e8 && M >= 64 && N >= 64) {
+    constexpr int TN = TmaCfg<4>::TN;
+    CUtensorMap mA, mB;
+    if (make_map_2d(c, &mA, A_dev, K, M, K, TMA_TM)) return 1;
+    if (make_map_2d(c, &mB, B_dev, K, N, K, TN)) return 1;
+    TmaGemmParams p;
+    memset(&p, 0, sizeof(p));
+    p.M = M; p.N = N;
+    p.tm_eff = TMA_TM; p.tn_eff = TN;
+    p.tiles_m = cdiv(M, TMA_TM); p.tiles_n = cdiv(N, TN);
+    p.nk = cdiv(K, TMA_TK);
+    p.a_mode = 0;
+    p.a_bytes = TMA_TM * TMA_TK * 8; p.b_bytes = TN * TMA_TK * 8;
+    p.C = C_dev; p.ldc = N; p.ksplit = 1;
+    T2Params t;
+    memset(&t, 0, sizeof(t));
+    return launch_tma<0, 4>(c, "gemm_tma_kernel<nt>", mA, mB, p, t);
+  }
   Operand A = flat_operand(A_dev, M, K, 1);
   Operand B = flat_operand(B_dev, N, K, 1);
   Output C = flat_output(C_dev, N, 1);
+  if (N <= 64) return launch_gemm<CfgN64KK>(c, "gemm_nt", A, B, C, M, N, K, 1, nullptr);
   return launch_gemm<CfgBigKK>(c, "gemm_nt", A, B, C, M, N, K, 1, nullptr);
+}
+
+// ===========================================================================
+// tensor engine (rows f1/f2): permute/accumulate, denominators, active-space overwrite, dot
+// ===========================================================================
+// out = alpha * transpose(in, perm) + beta * out   (numpy semantics: out axis d = in axis perm[d])
+extern "C" int mpccb_permute_axpby(mpccb_ctx* c, const double* in_dev, double* out_dev, int rank,
+                                   const int* in_dims, const int* perm, double alpha, double beta) {
+  if (rank < 1 || rank > MAX_RANK) return fail(c, "permute: rank must be 1..%d", MAX_RANK);
+  i64 istr[MAX_RANK], total = 1;
+  int seen = 0;
+  for (int d = rank - 1; d >= 0; --d) { istr[d] = total; total *= in_dims[d]; }
+  for (int d = 0; d < rank; ++d) {
+    if (perm[d] < 0 || perm[d] >= rank || (seen >> perm[d]) & 1) return fail(c, "permute: bad permutation");
+    seen |= 1 << perm[d];
+  }
+  if (total == 0) return 0;
+  int rpos = -1;                                 // output axis that is the input's unit-stride axis
+  for (int d = 0; d < rank; ++d) if (perm[d] == rank - 1) rpos = d;
+  const int nblk_max = NSM * 8;
+  if (rpos == rank - 1 || in_dims[rank - 1] < 8 || in_dims[perm[rank - 1]] < 8) {
+    PermuteDesc d;
+    memset(&d, 0, sizeof(d));
+    d.rank = rank; d.total = total;
+    for (int k = 0; k < rank; ++k) { d.out_dim[k] = in_dims[perm[k]]; d.in_stride[k] = istr[perm[k]]; }
+    const int nb = (int)std::min<i64>(cdiv(total, 256), nblk_max);
+    k_permute_axpby<<<nb, 256, 0, c->stream>>>(in_dev, out_dev, d, alpha, beta);
+    LAUNCH_OK(c, "k_permute_axpby");
+    return 0;
+  }
+  PermuteTiled d;
+  memset(&d, 0, sizeof(d));
+  i64 ostr[MAX_RANK], acc = 1;
+  for (int k = rank - 1; k >= 0; --k) { ostr[k] = acc; acc *= in_dims[perm[k]]; }
+  d.R = in_dims[rank - 1]; d.C = in_dims[perm[rank - 1]];
+  d.r_out_stride = ostr[rpos]; d.c_in_stride = istr[perm[rank - 1]];
+  d.n_outer = 1;
+  for (int k = 0; k < rank - 1; ++k) {
+    if (k == rpos) continue;
+    d.outer_dim[d.rank] = in_dims[perm[k]];
+    d.outer_in_stride[d.rank] = istr[perm[k]];
+    d.outer_out_stride[d.rank] = ostr[k];
+    d.n_outer *= in_dims[perm[k]];
+    d.rank++;
+  }
+  const i64 tiles = d.n_outer * cdiv(d.R, 32) * cdiv(d.C, 32);
+  const int nb = (int)std::min<i64>(tiles, nblk_max);
+  k_permute_tiled<<<nb, 256, 0, c->stream>>>(in_dev, out_dev, d, alpha, beta);
+  LAUNCH_OK(c, "k_permute_tiled");
+  return 0;
+}
+
+// rank 2: t1[i,a] /= eo[i]-ev[a];  rank 4: t2[i,j,a,b] /= eo[i]+eo[j]-ev[a]-ev[b]   (the context's eps_o / eps_v)
+extern "C" int mpccb_div_denominators(mpccb_ctx* c, double* t_dev, int rank) {
+  if (!c->eo || !c->ev) return fail(c, "orbital energies not bound");
+  if (rank != 2 && rank != 4) return fail(c, "div_denominators: rank 2 or 4");
+  const i64 total = rank == 2 ? c->nov : c->nov * c->nov;
+  const int nb = (int)std::min<i64>(cdiv(total, 256), NSM * 16);
+  k_div_denominators<<<nb, 256, 0, c->stream>>>(t_dev, c->eo, c->ev, c->o, c->v, rank);
+  LAUNCH_OK(c, "k_div_denominators");
+  return 0;
+}
+
+// tnew[idx] = told[idx] for the active/inactive index classes in class_mask (see k_class_overwrite)
+extern "C" int mpccb_class_overwrite(mpccb_ctx* c, double* tnew_dev, const double* told_dev, int rank,
+                                     const int* act_h_dev, const int* act_p_dev, unsigned class_mask) {
+  if (rank != 2 && rank != 4) return fail(c, "class_overwrite: rank 2 or 4");
+  const i64 total = rank == 2 ? c->nov : c->nov * c->nov;
+  const int nb = (int)std::min<i64>(cdiv(total, 256), NSM * 16);
+  k_class_overwrite<<<nb, 256, 0, c->stream>>>(tnew_dev, told_dev, act_h_dev, act_p_dev, class_mask, c->o, c->v, rank);
+  LAUNCH_OK(c, "k_class_overwrite");
+  return 0;
+}
+
+// out_dev[0] = sum_i x[i] y[i]  (deterministic two-pass reduction; needs the bound workspace)
+extern "C" int mpccb_dot(mpccb_ctx* c, const double* x_dev, const double* y_dev, long long n, double* out_dev) {
+  if (!c->ws) return fail(c, "bind the workspace first");
+  const int nb = (int)std::min<i64>(std::max<i64>(cdiv(n, 1024), 1), 592);
+  k_dot_partial<<<nb, 256, 0, c->stream>>>(x_dev, y_dev, c->scal, n);
+  LAUNCH_OK(c, "k_dot_partial");
+  k_final_sums<<<1, 256, 0, c->stream>>>(c->scal, out_dev, nb, 1);
+  LAUNCH_OK(c, "k_final_sums");
+  return 0;
 }
