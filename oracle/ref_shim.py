@@ -85,6 +85,24 @@ class _MemFile(dict):
 
 
 _loaded = None
+_loaded_cc = None
+
+
+def _direct_sum_general(spec, *ops):
+    """lib.direct_sum for the strings the reference uses (numpy_helper.py:1060-1127): the two MPCC_LL ones
+    plus 'ia,jb->ijab' of the CCSD denominators (rmpccsd_slow.py:168)."""
+    if spec == "ia,jb->ijab":
+        a, b = ops
+        return a[:, None, :, None] + b[None, :, None, :]
+    return _direct_sum(spec, *ops)
+
+
+def load_reference_cc():
+    """(rmpccsd_slow module, rintermediates module) executed from the reference tree."""
+    load_reference()
+    if isinstance(_loaded_cc, Exception):
+        raise _loaded_cc
+    return _loaded_cc
 
 
 def load_reference():
@@ -135,6 +153,26 @@ def load_reference():
     diis = run("pyscf.lib.diis", "lib/diis.py")
     lib.diis = diis
     lowlevel = run("pyscf.mpcc.dfrmpcc_lowlevel", "mpcc/dfrmpcc_lowlevel.py")
+    # CCSD-type residual of the high-level stage (rows f1/f2): rintermediates.py and rmpccsd_slow.py, unmodified.
+    # Everything they import besides numpy is faked: lib.einsum/direct_sum/dot, an empty ao2mo, a stub ccsd.CCSD.
+    global _loaded_cc
+    try:
+        lib.dot = lambda a, b, *r, **k: np.dot(a, b)
+        lib.direct_sum = nh.direct_sum = _direct_sum_general
+        lib.linalg_helper = mod("pyscf.lib.linalg_helper")
+        logger.info = logger.note = logger.timer = lambda *a, **k: None
+        logger.Logger = type("Logger", (), {"__init__": lambda self, *a, **k: None})
+        ao2mo = mod("pyscf.ao2mo"); pyscf.ao2mo = ao2mo
+        ao2mo.outcore = types.SimpleNamespace(general_iofree=None)     # default argument of _ChemistsERIs (:992)
+        cc = mod("pyscf.cc"); cc.__path__ = []; pyscf.cc = cc
+        ccsd = mod("pyscf.cc.ccsd"); cc.ccsd = ccsd
+        ccsd.CCSD = type("CCSD", (StreamObject,), {"_keys": set(), "__init__": lambda self, *a, **k: None})
+        imd = run("pyscf.cc.rintermediates", "cc/rintermediates.py")
+        cc.rintermediates = imd
+        slow = run("pyscf.cc.rmpccsd_slow", "cc/rmpccsd_slow.py")
+        _loaded_cc = (slow, imd)
+    except Exception as exc:                     # keep the low-level oracle usable even if this part fails
+        _loaded_cc = exc
     # leave the fake package installed only under private aliases
     for k in [k for k in sys.modules if k == "pyscf" or k.startswith("pyscf.")]:
         sys.modules["_mpcc_refshim_" + k] = sys.modules.pop(k)

@@ -973,6 +973,22 @@ extern "C" int mpccb_gemm_nt(mpccb_ctx* c, const double* A_dev, const double* B_
   Operand A = flat_operand(A_dev, M, K, 1);
   Operand B = flat_operand(B_dev, N, K, 1);
   Output C = flat_output(C_dev, N, 1);
+  // few output tiles but a long contraction index (the "->ia", "->ki", "->ac" terms: K = o*v*v): split K over
+  // the machine into the context's partial buffer, then a fixed-order reduction
+  const int tiles = cdiv(M, 128) * cdiv(N, N <= 64 ? 64 : 128);
+  if (c->P && tiles * 2 <= NSM && K >= 2048) {
+    int splits = std::min(cdiv(2 * NSM, tiles), K / 256);
+    const i64 cap = c->P_count / ((i64)M * N);
+    if (splits > cap) splits = (int)cap;
+    if (splits >= 2) {
+      const int kchunk = (int)align_up(cdiv(K, splits), TK);
+      splits = cdiv(K, kchunk);
+      int rc = (N <= 64) ? launch_gemm<CfgN64KK>(c, "gemm_nt(split-K)", A, B, C, M, N, K, splits, c->P)
+                         : launch_gemm<CfgBigKK>(c, "gemm_nt(split-K)", A, B, C, M, N, K, splits, c->P);
+      if (rc) return rc;
+      return reduce_splits(c, C_dev, c->P, splits, (i64)M * N, (i64)M * N, 1.0, 0.0);
+    }
+  }
   if (N <= 64) return launch_gemm<CfgN64KK>(c, "gemm_nt", A, B, C, M, N, K, 1, nullptr);
   return launch_gemm<CfgBigKK>(c, "gemm_nt", A, B, C, M, N, K, 1, nullptr);
 }

@@ -196,6 +196,7 @@ class MPCC_LL:
         if mf is not None:
             self.compute_three_center_ints()
             fock_mo = self.mo_coeff.T @ np.asarray(mf.get_fock()) @ self.mo_coeff
+            self._fock_mo = fock_mo
             foo = np.ascontiguousarray(fock_mo[:o, :o])
             fvv = np.ascontiguousarray(fock_mo[o:, o:])
         else:
@@ -443,6 +444,33 @@ class MPCC_LL:
             return self.updated_amps()[1]
         finally:
             self.t1 = keep
+
+    # ------------------------------------------------------------------ high-level stage (rows f1/f2)
+    def tensor_engine(self):
+        """Device contraction engine bound to this solver's native context (stream, workspace, orbital energies)."""
+        from .tensor_engine import CudaBackend, Engine
+        self._bind_stream()
+        return Engine(CudaBackend(self._ctx, self.device))
+
+    def high_level_eris(self, fock=None):
+        """Four-index integrals for the CCSD-type stage (``pyscf_mpcc_b200.rmpccsd``), built on the device from
+        this solver's DF tensors. ``fock``: full MO Fock matrix (default: the one of the mean field, or
+        blockdiag(foo, fvv) when the solver was built from MO blocks)."""
+        from . import rmpccsd
+        from .tensor_engine import DTensor
+        if self.world_size > 1:
+            raise NotImplementedError("the CCSD-type stage runs on one rank")
+        o, v, L = self.nocc, self.nvir, self.naux
+        if fock is None:
+            fock = getattr(self, "_fock_mo", None)
+        if fock is None:
+            fock = np.zeros((o + v, o + v))
+            fock[:o, :o] = self.foo
+            fock[o:, o:] = self.fvv
+        eng = self.tensor_engine()
+        d = self._d
+        return rmpccsd.DFERIs(eng, DTensor(d["Loo"].reshape(-1), (L, o, o)), DTensor(d["Lov"].reshape(-1), (L, o, v)),
+                              DTensor(d["Lvv"].reshape(-1), (L, v, v)), fock)
 
     # ------------------------------------------------------------------ :155-176
     def amplitudes_to_vector(self, t1, t2, out=None):

@@ -1,0 +1,305 @@
+"""CCSD-type doubles/singles residual of the multi-level solver on the GPU (SURVEY.md §8f rows f1 + f2).
+
+Counterpart of ``pyscf/cc/rmpccsd_slow.py`` — the "high-level" MPCC stage the DF low-level solver is meant
+to be embedded in (``pyscf/mpcc/mpcc.py:22-23``): the full RCCSD amplitude equations (Hirata et al., JCP 120,
+2581 (2004), Eqs. 35-36) followed by the active-space overwrite that keeps the inactive ("environment")
+amplitude classes at their input values.
+
+    update_amps(cc, t1, t2, eris, act_hole, act_particle, idx_singles, idx_doubles) -> (t1new, t2new)   (:73-180)
+    energy(cc, t1, t2, eris)                                                                            (:183-194)
+    get_index_tuples(act_hole, act_particle, nocc, nvir)                                                (:39-71)
+    init_amps(eris)                                                                                     (:206-219)
+
+The four-index integrals come from the three-index DF tensors of the low-level solver
+(``(pq|rs) = sum_L Lpq Lrs``): :class:`DFERIs` builds the oooo ... ovvv blocks as DMMA GEMMs on the device; the
+particle-particle ladder ``sum_cd W_abcd tau_ijcd`` (:138, ``cc_Wvvvv`` rintermediates.py:92-99) is evaluated
+**DF-direct in slabs of the first virtual index** so that v^4 integrals never exist in memory (the same blocking
+idea as ``pyscf/cc/dfccsd.py:54-117``). The hole-hole ladder (``cc_Woooo``), the ring/exchange terms
+(``cc_Wvoov``, ``cc_Wvovo``) and all singles terms follow the reference einsum by einsum through
+:class:`pyscf_mpcc_b200.tensor_engine.Engine` (permute -> FP64 tensor-core GEMM -> permute/accumulate).
+
+Amplitude layouts are the reference's: t1 (o,v), t2 (o,o,v,v); integrals in chemists' notation.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from .tensor_engine import DTensor, Engine
+
+
+def get_index_tuples(act_hole, act_particle, nocc, nvir):
+    """Index blocks of the singles (4) and doubles (16) amplitude classes, in the reference's order
+    (rmpccsd_slow.py:39-71). Host-side helper; the device path uses :func:`class_masks`."""
+    inact_particle = np.delete(np.arange(nvir), act_particle)
+    inact_hole = np.delete(np.arange(nocc), act_hole)
+    ah, ih, ap, ip = act_hole, inact_hole, act_particle, inact_particle
+    singles = [np.ix_(ah, ip), np.ix_(ih, ap), np.ix_(ih, ip), np.ix_(ah, ap)]
+    doubles = []
+    for pa, pb in ((ip, ap), (ap, ip), (ip, ip), (ap, ap)):
+        for hi, hj in ((ah, ah), (ih, ah), (ah, ih), (ih, ih)):
+            doubles.append(np.ix_(hi, hj, pa, pb))
+    # the reference lists the all-active block last and (inact,inact,act,act) before it (:65-68)
+    doubles[12:16] = [doubles[13], doubles[14], doubles[15], doubles[12]]
+    return singles, doubles
+
+
+# class bit used by mpccb_class_overwrite: singles 2*act_h[i] + act_p[a]; doubles 8*act_h[i] + 4*act_h[j] + 2*act_p[a] + act_p[b]
+_SINGLES_BITS = [0b10, 0b01, 0b00, 0b11]          # order of get_index_tuples()[0]
+
+
+def _doubles_bits():
+    bits = []
+    for pa, pb in ((0, 1), (1, 0), (0, 0), (1, 1)):
+        for hi, hj in ((1, 1), (0, 1), (1, 0), (0, 0)):
+            bits.append(8 * hi + 4 * hj + 2 * pa + pb)
+    bits[12:16] = [bits[13], bits[14], bits[15], bits[12]]
+    return bits
+
+
+_DOUBLES_BITS = _doubles_bits()
+
+
+def class_masks(idx_singles, idx_doubles):
+    """Bit masks over the active/inactive classes for the reference's class numbers (list positions)."""
+    ms = 0
+    for s in idx_singles:
+        ms |= 1 << _SINGLES_BITS[s]
+    md = 0
+    for d in idx_doubles:
+        md |= 1 << _DOUBLES_BITS[d]
+    return ms, md
+
+
+class DFERIs:
+    """Four-index MO integrals from the DF tensors, on the device (chemists' notation, reference attribute
+    names of ``ccsd._ChemistsERIs``): fock (host), oooo, ovoo, ooov, oovv, ovov, ovvo, ovvv; ``vvvv`` stays
+    implicit — ``Lvv`` is kept for the DF-direct ladder."""
+
+    def __init__(self, eng: Engine, Loo, Lov, Lvv, fock):
+        self.eng = eng
+        self.fock = np.asarray(fock, dtype=np.float64)
+        L, o, v = Lov.shape
+        self.nocc, self.nvir, self.naux = o, v, L
+        E = eng.einsum
+        self.Loo, self.Lov, self.Lvv = Loo, Lov, Lvv
+        self.oooo = E("Lij,Lkl->ijkl", Loo, Loo)
+        self.ovoo = E("Lia,Ljk->iajk", Lov, Loo)
+        self.ooov = eng.transpose(self.ovoo, (2, 3, 0, 1))
+        self.oovv = E("Lij,Lab->ijab", Loo, Lvv)
+        self.ovov = E("Lia,Ljb->iajb", Lov, Lov)
+        self.ovvo = eng.transpose(self.ovov, (0, 1, 3, 2))
+        self.ovvv = E("Lia,Lbc->iabc", Lov, Lvv)
+        self.vvvv = None
+
+    @classmethod
+    def from_numpy(cls, eng, Loo, Lov, Lvv, fock):
+        return cls(eng, eng.tensor(Loo), eng.tensor(Lov), eng.tensor(Lvv), fock)
+
+    def get_ovvv(self):
+        return self.ovvv
+
+
+def _sym_add(eng, t2new, tmp, alpha):
+    """t2new += alpha * (tmp + tmp.transpose(1,0,3,2))   — the P(ia,jb) symmetrisation of :142-155."""
+    eng.add(t2new, tmp, alpha)
+    eng.add(t2new, tmp, alpha, (1, 0, 3, 2))
+
+
+def _rows(t, lo, hi):
+    """Zero-copy view of t[lo:hi] (leading axis) of a contiguous tensor."""
+    inner = t.size // t.shape[0] if t.shape[0] else 0
+    return DTensor(t.buf[lo * inner:hi * inner], (hi - lo,) + t.shape[1:])
+
+
+def _pp_ladder(eng, eris, t1, tau, t2new, slab_bytes=4 << 30):
+    """t2new[i,j,a,b] += sum_cd W[a,b,c,d] tau[i,j,c,d]  (:138), W = cc_Wvvvv (rintermediates.py:92-99):
+        W[a,b,c,d] = (ac|bd) - sum_k (kd|ac) t1[k,b] - sum_k (kc|bd) t1[k,a]
+    evaluated for slabs of the first virtual index a; (ac|bd) = sum_L Lvv[L,a,c] Lvv[L,b,d] is formed per
+    slab from the DF tensor, so no v^4 array is ever stored. The last term is folded into the DF tensor:
+        sum_k t1[k,a] (kc|bd) = sum_L (sum_k t1[k,a] Lov[L,k,c]) Lvv[L,b,d]."""
+    E = eng.einsum
+    v = eris.nvir
+    na = max(1, min(v, int(slab_bytes // (8 * v * v * v))))
+    Lt = E("ka,Lkc->Lac", t1, eris.Lov)
+    Leff = eng.copy(eris.Lvv)
+    eng.add(Leff, Lt, -1.0)                                       # (Lvv - t1^T Lov)[L,a,c]
+    LA = eng.transpose(Leff, (1, 2, 0))                           # [a, c, L]   rows of a slab are contiguous
+    LB = eng.transpose(eris.Lvv, (1, 2, 0))                       # [b, d, L]
+    OA = eng.transpose(eris.ovvv, (2, 3, 1, 0))                   # ovvv[k,d,a,c] -> [a, c, d, k]
+    R = eng.zeros((v, v) + tau.shape[:2])                         # [a, b, i, j]
+    for a0 in range(0, v, na):
+        a1 = min(v, a0 + na)
+        W = E("acL,bdL->acbd", _rows(LA, a0, a1), LB)             # (ac|bd) - sum_k t1[k,a](kc|bd)
+        E("acdk,kb->acbd", _rows(OA, a0, a1), t1, alpha=-1.0, out=W, beta=1.0)   # - sum_k (kd|ac) t1[k,b]
+        E("acbd,ijcd->abij", W, tau, out=_rows(R, a0, a1))
+        del W
+    eng.add(t2new, R, 1.0, (2, 3, 0, 1))
+    return t2new
+
+
+def _intermediates(eng, t1, t2, tau, eris, f):
+    """Foo, Fvv, Fov (rintermediates.py:29-59), Loo, Lvv (:63-79), Woooo, Wvoov, Wvovo (:83-126).
+    `f` holds the fock blocks as device tensors (fov, foo, fvv)."""
+    E = eng.einsum
+    ovov, ovoo, ovvv = eris.ovov, eris.ovoo, eris.ovvv
+    # 2 (kc|ld) - (kd|lc): every "2*X - X'" pair of the kappa intermediates contracts this combination
+    lov = eng.scale(ovov, 2.0)
+    eng.add(lov, ovov, -1.0, (0, 3, 2, 1))
+    dFov = E("kcld,ld->kc", lov, t1)                              # Fov - fov                      (:55-57)
+    Fov = eng.copy(dFov)
+    eng.add(Fov, f["fov"])
+    Foo = E("kcld,ilcd->ki", lov, t2)                             # (:33-34)
+    E("kc,ic->ki", dFov, t1, out=Foo, beta=1.0)                   # (:35-36)
+    eng.add(Foo, f["foo"])
+    Fvv = E("kcld,klad->ac", lov, t2, alpha=-1.0)                 # (:44-45)
+    E("kc,ka->ac", dFov, t1, alpha=-1.0, out=Fvv, beta=1.0)       # (:46-47)
+    eng.add(Fvv, f["fvv"])
+    Loo = eng.copy(Foo)                                           # (:63-70)
+    E("kc,ic->ki", f["fov"], t1, out=Loo, beta=1.0)
+    E("lcki,lc->ki", ovoo, t1, alpha=2.0, out=Loo, beta=1.0)
+    E("kcli,lc->ki", ovoo, t1, alpha=-1.0, out=Loo, beta=1.0)
+    Lvv = eng.copy(Fvv)                                           # (:72-79)
+    E("kc,ka->ac", f["fov"], t1, alpha=-1.0, out=Lvv, beta=1.0)
+    E("kdac,kd->ac", ovvv, t1, alpha=2.0, out=Lvv, beta=1.0)
+    E("kcad,kd->ac", ovvv, t1, alpha=-1.0, out=Lvv, beta=1.0)
+    # hole-hole ladder intermediate (:83-91); the t2 and t1*t1 terms contract the same integrals -> tau
+    Woooo = eng.transpose(eris.oooo, (0, 2, 1, 3))
+    E("lcki,jc->klij", ovoo, t1, out=Woooo, beta=1.0)
+    E("kclj,ic->klij", ovoo, t1, out=Woooo, beta=1.0)
+    E("kcld,ijcd->klij", ovov, tau, out=Woooo, beta=1.0)
+    # ring / exchange intermediates (:101-126)
+    Wvoov = eng.transpose(eris.ovvo, (2, 0, 3, 1))
+    E("kcad,id->akic", ovvv, t1, out=Wvoov, beta=1.0)
+    E("kcli,la->akic", ovoo, t1, alpha=-1.0, out=Wvoov, beta=1.0)
+    E("ldkc,ilda->akic", ovov, t2, alpha=-0.5, out=Wvoov, beta=1.0)
+    E("lckd,ilad->akic", ovov, t2, alpha=-0.5, out=Wvoov, beta=1.0)
+    y = E("ldkc,id->lkci", ovov, t1)
+    E("lkci,la->akic", y, t1, alpha=-1.0, out=Wvoov, beta=1.0)
+    E("ldkc,ilad->akic", ovov, t2, out=Wvoov, beta=1.0)
+    Wvovo = eng.transpose(eris.oovv, (2, 0, 3, 1))
+    E("kdac,id->akci", ovvv, t1, out=Wvovo, beta=1.0)
+    E("lcki,la->akci", ovoo, t1, alpha=-1.0, out=Wvovo, beta=1.0)
+    E("lckd,ilda->akci", ovov, t2, alpha=-0.5, out=Wvovo, beta=1.0)
+    y = E("lckd,id->lcki", ovov, t1)
+    E("lcki,la->akci", y, t1, alpha=-1.0, out=Wvovo, beta=1.0)
+    return dict(Foo=Foo, Fvv=Fvv, Fov=Fov, Loo=Loo, Lvv=Lvv, Woooo=Woooo, Wvoov=Wvoov, Wvovo=Wvovo)
+
+
+def _fock_blocks(eng, eris, remove_diag=False):
+    o = eris.nocc
+    fock = eris.fock
+    foo, fvv, fov = fock[:o, :o].copy(), fock[o:, o:].copy(), fock[:o, o:].copy()
+    f = {"fov": eng.tensor(fov), "foo": eng.tensor(foo), "fvv": eng.tensor(fvv)}
+    f["foo_diag"] = eng.tensor(np.diag(np.diag(foo)))
+    f["fvv_diag"] = eng.tensor(np.diag(np.diag(fvv)))
+    return f
+
+
+def make_tau(eng, t1, t2):
+    """tau[i,j,a,b] = t2[i,j,a,b] + t1[i,a] t1[j,b]   (:136)."""
+    tau = eng.copy(t2)
+    eng.einsum("ia,jb->ijab", t1, t1, out=tau, beta=1.0)
+    return tau
+
+
+def update_amps(cc, t1, t2, eris, act_hole=(), act_particle=(), idx_singles=(), idx_doubles=()):
+    """One RCCSD amplitude update with active-space overwrite — ``rmpccsd_slow.update_amps`` (:73-180, the
+    ``cc.cc2 == False`` branch). ``t1``/``t2`` are :class:`DTensor` (o,v)/(o,o,v,v) or numpy arrays (uploaded;
+    the result then comes back as numpy). ``eris`` is a :class:`DFERIs`."""
+    if getattr(cc, "cc2", False):
+        raise NotImplementedError("the cc2 branch (:122-133) is not built")
+    eng = eris.eng
+    as_numpy = not isinstance(t1, DTensor)
+    if as_numpy:
+        t1, t2 = eng.tensor(t1), eng.tensor(t2)
+    E = eng.einsum
+    o, v = eris.nocc, eris.nvir
+    f = _fock_blocks(eng, eris)
+    ovvv, ooov, ovvo, oovv, ovov = eris.ovvv, eris.ooov, eris.ovvo, eris.oovv, eris.ovov
+    tau = make_tau(eng, t1, t2)
+    im = _intermediates(eng, t1, t2, tau, eris, f)
+    Foo, Fvv, Fov = im["Foo"], im["Fvv"], im["Fov"]
+    # move energy terms to the other side (:90-91, :135)
+    for x, d in ((Foo, "foo_diag"), (Fvv, "fvv_diag"), (im["Loo"], "foo_diag"), (im["Lvv"], "fvv_diag")):
+        eng.add(x, f[d], -1.0)
+
+    # ---- T1 equation (:93-111) ----
+    t1new = eng.copy(f["fov"])
+    z = E("kc,ic->ki", f["fov"], t1)
+    E("ki,ka->ia", z, t1, alpha=-2.0, out=t1new, beta=1.0)
+    E("ac,ic->ia", Fvv, t1, out=t1new, beta=1.0)
+    E("ki,ka->ia", Foo, t1, alpha=-1.0, out=t1new, beta=1.0)
+    E("kc,kica->ia", Fov, t2, alpha=2.0, out=t1new, beta=1.0)
+    E("kc,ikca->ia", Fov, t2, alpha=-1.0, out=t1new, beta=1.0)
+    z = E("kc,ic->ki", Fov, t1)
+    E("ki,ka->ia", z, t1, out=t1new, beta=1.0)
+    E("kcai,kc->ia", ovvo, t1, alpha=2.0, out=t1new, beta=1.0)
+    E("kiac,kc->ia", oovv, t1, alpha=-1.0, out=t1new, beta=1.0)
+    E("kdac,ikcd->ia", ovvv, t2, alpha=2.0, out=t1new, beta=1.0)
+    E("kcad,ikcd->ia", ovvv, t2, alpha=-1.0, out=t1new, beta=1.0)
+    w = E("kdac,kd->ac", ovvv, t1)
+    E("ac,ic->ia", w, t1, alpha=2.0, out=t1new, beta=1.0)
+    w = E("kcad,kd->ca", ovvv, t1)
+    E("ca,ic->ia", w, t1, alpha=-1.0, out=t1new, beta=1.0)
+    E("kilc,klac->ia", ooov, t2, alpha=-2.0, out=t1new, beta=1.0)
+    E("likc,klac->ia", ooov, t2, out=t1new, beta=1.0)
+    u = E("kilc,lc->ki", ooov, t1)
+    E("ki,ka->ia", u, t1, alpha=-2.0, out=t1new, beta=1.0)
+    u = E("likc,lc->ik", ooov, t1)
+    E("ik,ka->ia", u, t1, out=t1new, beta=1.0)
+
+    # ---- T2 equation (:114-162) ----
+    t2new = eng.transpose(ovov, (0, 2, 1, 3))
+    E("klij,klab->ijab", im["Woooo"], tau, out=t2new, beta=1.0)          # hole-hole ladder (:137)
+    _pp_ladder(eng, eris, t1, tau, t2new)                                 # particle-particle ladder (:138)
+    _sym_add(eng, t2new, E("ac,ijcb->ijab", im["Lvv"], t2), 1.0)          # (:139-140)
+    _sym_add(eng, t2new, E("ki,kjab->ijab", im["Loo"], t2), -1.0)         # (:141-142)
+    tmp = E("akic,kjcb->ijab", im["Wvoov"], t2, alpha=2.0)                # ring (:143-145)
+    E("akci,kjcb->ijab", im["Wvovo"], t2, alpha=-1.0, out=tmp, beta=1.0)
+    _sym_add(eng, t2new, tmp, 1.0)
+    _sym_add(eng, t2new, E("akic,kjbc->ijab", im["Wvoov"], t2), -1.0)     # exchange (:146-149)
+    _sym_add(eng, t2new, E("bkci,kjac->ijab", im["Wvovo"], t2), -1.0)
+    tmp2 = eng.transpose(ovvv, (1, 3, 0, 2))                              # (:151-154)
+    E("kibc,ka->abic", oovv, t1, alpha=-1.0, out=tmp2, beta=1.0)
+    _sym_add(eng, t2new, E("abic,jc->ijab", tmp2, t1), 1.0)
+    tmp2 = eng.transpose(ooov, (3, 1, 2, 0))                              # (:155-158)
+    E("kcai,jc->akij", ovvo, t1, out=tmp2, beta=1.0)
+    _sym_add(eng, t2new, E("akij,kb->ijab", tmp2, t1), -1.0)
+
+    eng.div_denominators(t1new)                                           # (:160-164)
+    eng.div_denominators(t2new)
+
+    # ---- active-space overwrite (:166-178) ----
+    ms, md = class_masks(idx_singles, idx_doubles)
+    if ms or md:
+        ah = np.zeros(o, dtype=np.int32); ah[np.asarray(act_hole, dtype=int)] = 1
+        ap = np.zeros(v, dtype=np.int32); ap[np.asarray(act_particle, dtype=int)] = 1
+        ah_d, ap_d = eng.be.upload_int(ah), eng.be.upload_int(ap)
+        eng.class_overwrite(t1new, t1, ah_d, ap_d, ms)
+        eng.class_overwrite(t2new, t2, ah_d, ap_d, md)
+    if as_numpy:
+        return eng.numpy(t1new), eng.numpy(t2new)
+    return t1new, t2new
+
+
+def energy(cc, t1, t2, eris):
+    """``rmpccsd_slow.energy`` (:183-194): 2 f_ia t1_ia + sum tau_ijab (2 (ia|jb) - (ib|ja))."""
+    eng = eris.eng
+    if not isinstance(t1, DTensor):
+        t1, t2 = eng.tensor(t1), eng.tensor(t2)
+    o = eris.nocc
+    e = 2.0 * eng.dot(eng.tensor(eris.fock[:o, o:]), t1)
+    tau = make_tau(eng, t1, t2)
+    e += 2.0 * eng.dot(tau, eng.transpose(eris.ovov, (0, 2, 1, 3)))
+    e -= eng.dot(tau, eng.transpose(eris.ovov, (0, 2, 3, 1)))
+    return e
+
+
+def init_amps(cc, eris):
+    """MP2 start (:206-219): t1 = f_ia / e_ia, t2 = (ia|jb) / e_ijab; returns (emp2, t1, t2) on the device."""
+    eng = eris.eng
+    o = eris.nocc
+    t1 = eng.div_denominators(eng.tensor(eris.fock[:o, o:]))
+    t2 = eng.div_denominators(eng.transpose(eris.ovov, (0, 2, 1, 3)))
+    emp2 = 2.0 * eng.dot(t2, eng.transpose(eris.ovov, (0, 2, 1, 3))) - eng.dot(t2, eng.transpose(eris.ovov, (0, 2, 3, 1)))
+    return emp2, t1, t2

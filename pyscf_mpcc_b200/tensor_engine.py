@@ -1,0 +1,219 @@
+"""Device tensor-contraction engine for the CCSD-type residual terms.
+
+The reference writes those terms as a list of ``lib.einsum`` calls
+(``pyscf/cc/rmpccsd_slow.py:73-180``, ``pyscf/cc/rintermediates.py:29-130``); ``lib.einsum`` itself
+turns each pairwise contraction into transpose -> ``lib.dot`` (BLAS dgemm) -> transpose
+(``pyscf/lib/numpy_helper.py:101-252``). This engine does the same on the GPU:
+
+    permute A to [M.., K..]  ->  permute B to [N.., K..]  ->  C[m,n] = sum_k A[m,k] B[n,k]  (FP64 DMMA GEMM)
+    ->  out = alpha * permute(C) + beta * out
+
+with hand-written kernels behind the C ABI (``mpccb_permute_axpby``, ``mpccb_gemm_nt`` — TMA-fed for the
+large products —, ``mpccb_div_denominators``, ``mpccb_class_overwrite``, ``mpccb_dot``). PyTorch only owns the
+buffers. The numerical primitives live in a *backend* object; the product backend is :class:`CudaBackend`
+and there is no CPU backend in this package (tests inject a NumPy stand-in to check the formula
+transcription without a GPU).
+"""
+from __future__ import annotations
+
+import ctypes
+
+import numpy as np
+
+
+class DTensor:
+    """Shape + flat device buffer (a torch float64 CUDA tensor for the product backend)."""
+    __slots__ = ("buf", "shape")
+
+    def __init__(self, buf, shape):
+        self.buf = buf
+        self.shape = tuple(int(s) for s in shape)
+
+    @property
+    def size(self):
+        n = 1
+        for s in self.shape:
+            n *= s
+        return n
+
+    @property
+    def ndim(self):
+        return len(self.shape)
+
+
+class CudaBackend:
+    """Primitives on the GPU through ``libmpcc_b200.so``. ``ctx`` is a ``_cabi.Context`` with its workspace,
+    stream and orbital energies bound (``MPCC_LL`` does that)."""
+
+    def __init__(self, ctx, device):
+        import torch
+        if not torch.cuda.is_available():
+            raise RuntimeError("the tensor engine needs a CUDA device; there is no CPU path")
+        self.torch = torch
+        self.ctx = ctx
+        self.device = device
+
+    def empty(self, n):
+        return self.torch.empty(int(n), dtype=self.torch.float64, device=self.device)
+
+    def zeros(self, n):
+        return self.torch.zeros(int(n), dtype=self.torch.float64, device=self.device)
+
+    def upload(self, array):
+        a = np.ascontiguousarray(array, dtype=np.float64).reshape(-1)
+        return self.torch.from_numpy(a).to(self.device)
+
+    def upload_int(self, array):
+        a = np.ascontiguousarray(array, dtype=np.int32).reshape(-1)
+        return self.torch.from_numpy(a).to(self.device)
+
+    def download(self, buf):
+        self.torch.cuda.current_stream(self.device).synchronize()
+        return buf.cpu().numpy()
+
+    def copy(self, buf):
+        return buf.clone()
+
+    def permute_axpby(self, src, dst, dims, perm, alpha, beta):
+        r = len(dims)
+        self.ctx.call("mpccb_permute_axpby", src.data_ptr(), dst.data_ptr(), r,
+                      (ctypes.c_int * r)(*dims), (ctypes.c_int * r)(*perm), float(alpha), float(beta))
+
+    def gemm_nt(self, a, b, c, m, n, k):
+        self.ctx.call("mpccb_gemm_nt", a.data_ptr(), b.data_ptr(), c.data_ptr(), int(m), int(n), int(k))
+
+    def div_denominators(self, buf, rank):
+        self.ctx.call("mpccb_div_denominators", buf.data_ptr(), int(rank))
+
+    def class_overwrite(self, new, old, rank, act_h, act_p, mask):
+        self.ctx.call("mpccb_class_overwrite", new.data_ptr(), old.data_ptr(), int(rank), act_h.data_ptr(),
+                      act_p.data_ptr(), int(mask))
+
+    def dot(self, x, y, n):
+        out = self.empty(1)
+        self.ctx.call("mpccb_dot", x.data_ptr(), y.data_ptr(), int(n), out.data_ptr())
+        return float(self.download(out)[0])
+
+
+def _prod(xs):
+    n = 1
+    for x in xs:
+        n *= x
+    return n
+
+
+class Engine:
+    """Pairwise einsum / transpose / axpy on :class:`DTensor` objects. ``flops`` accumulates 2*M*N*K of
+    every GEMM issued (the algorithmic count used for throughput reports)."""
+
+    def __init__(self, backend):
+        self.be = backend
+        self.flops = 0.0
+        self.gemms = 0
+
+    # -- construction ------------------------------------------------------------------------------
+    def tensor(self, array):
+        a = np.asarray(array, dtype=np.float64)
+        return DTensor(self.be.upload(a), a.shape)
+
+    def zeros(self, shape):
+        return DTensor(self.be.zeros(_prod(shape)), shape)
+
+    def numpy(self, t):
+        return self.be.download(t.buf).reshape(t.shape)
+
+    def copy(self, t):
+        return DTensor(self.be.copy(t.buf), t.shape)
+
+    # -- layout ------------------------------------------------------------------------------------
+    def transpose(self, t, perm, alpha=1.0):
+        """alpha * t.transpose(perm) as a new contiguous tensor."""
+        perm = tuple(perm)
+        shape = tuple(t.shape[p] for p in perm)
+        out = DTensor(self.be.empty(t.size), shape)
+        if t.size:
+            self.be.permute_axpby(t.buf, out.buf, t.shape, perm, alpha, 0.0)
+        return out
+
+    def add(self, out, x, alpha=1.0, perm=None):
+        """out += alpha * x.transpose(perm)   (perm None = identity)."""
+        perm = tuple(range(x.ndim)) if perm is None else tuple(perm)
+        if tuple(x.shape[p] for p in perm) != out.shape:
+            raise ValueError(f"add: shape {x.shape} permuted by {perm} does not match {out.shape}")
+        if out.size:
+            self.be.permute_axpby(x.buf, out.buf, x.shape, perm, alpha, 1.0)
+        return out
+
+    def scale(self, t, alpha):
+        return self.transpose(t, range(t.ndim), alpha)
+
+    # -- contraction -------------------------------------------------------------------------------
+    def einsum(self, spec, a, b, alpha=1.0, out=None, beta=0.0):
+        """``out = alpha * einsum(spec, a, b) + beta * out`` for two operands without batch indices."""
+        lhs, io = spec.replace(" ", "").split("->")
+        ia, ib = lhs.split(",")
+        if len(ia) != a.ndim or len(ib) != b.ndim:
+            raise ValueError(f"einsum {spec}: operand ranks {a.ndim},{b.ndim}")
+        if len(set(ia)) != len(ia) or len(set(ib)) != len(ib) or len(set(io)) != len(io):
+            raise NotImplementedError(f"einsum {spec}: repeated index inside one operand")
+        ext = {}
+        for idx, t in ((ia, a), (ib, b)):
+            for ch, n in zip(idx, t.shape):
+                if ext.setdefault(ch, n) != n:
+                    raise ValueError(f"einsum {spec}: extent of '{ch}' differs ({ext[ch]} vs {n})")
+        ksum = [ch for ch in ia if ch in ib and ch not in io]
+        if any(ch in ia and ch in ib for ch in io):
+            raise NotImplementedError(f"einsum {spec}: batch index (present in both operands and the output)")
+        if any((ch not in ib and ch not in io) for ch in ia) or any((ch not in ia and ch not in io) for ch in ib):
+            raise NotImplementedError(f"einsum {spec}: index summed inside a single operand")
+        mi = [ch for ch in io if ch in ia]
+        ni = [ch for ch in io if ch in ib]
+        if len(mi) + len(ni) != len(io):
+            raise ValueError(f"einsum {spec}: output index not found in the operands")
+        M, N, K = _prod(ext[c] for c in mi), _prod(ext[c] for c in ni), _prod(ext[c] for c in ksum)
+        oshape = tuple(ext[c] for c in io)
+        if out is not None and out.shape != oshape:
+            raise ValueError(f"einsum {spec}: out has shape {out.shape}, expected {oshape}")
+        if out is None:
+            if beta != 0.0:
+                raise ValueError("beta without out")
+            out = DTensor(self.be.empty(_prod(oshape)), oshape)
+        if M * N == 0:
+            return out
+        if K == 0:
+            raise NotImplementedError("empty contraction index")
+        am = self._to_matrix(a, ia, mi + ksum)
+        bm = self._to_matrix(b, ib, ni + ksum)
+        cm_idx = mi + ni
+        perm = tuple(cm_idx.index(ch) for ch in io)
+        direct = perm == tuple(range(len(io))) and alpha == 1.0 and beta == 0.0
+        cbuf = out.buf if direct else self.be.empty(M * N)
+        self.be.gemm_nt(am, bm, cbuf, M, N, K)
+        self.flops += 2.0 * M * N * K
+        self.gemms += 1
+        if not direct:
+            self.be.permute_axpby(cbuf, out.buf, tuple(ext[c] for c in cm_idx), perm, alpha, beta)
+        return out
+
+    def _to_matrix(self, t, idx, order):
+        perm = tuple(idx.index(ch) for ch in order)
+        if perm == tuple(range(len(idx))):
+            return t.buf
+        tmp = self.be.empty(t.size)
+        self.be.permute_axpby(t.buf, tmp, t.shape, perm, 1.0, 0.0)
+        return tmp
+
+    # -- reductions / elementwise ------------------------------------------------------------------
+    def dot(self, x, y):
+        if x.shape != y.shape:
+            raise ValueError("dot: shapes differ")
+        return self.be.dot(x.buf, y.buf, x.size) if x.size else 0.0
+
+    def div_denominators(self, t):
+        self.be.div_denominators(t.buf, t.ndim)
+        return t
+
+    def class_overwrite(self, tnew, told, act_h, act_p, mask):
+        if mask:
+            self.be.class_overwrite(tnew.buf, told.buf, tnew.ndim, act_h, act_p, mask)
+        return tnew

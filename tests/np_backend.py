@@ -1,0 +1,60 @@
+"""TEST INFRASTRUCTURE — NumPy stand-in for the tensor engine's backend (tests only; the product backend is
+``pyscf_mpcc_b200.tensor_engine.CudaBackend``). It lets the CPU suite check the *transcription* of the reference
+formulas in ``pyscf_mpcc_b200/rmpccsd.py`` (index strings, signs, permutations, class masks) without a GPU; the
+CUDA kernels themselves are checked by the ``-m gpu`` tests against the same reference numbers."""
+import numpy as np
+
+
+class NumpyBackend:
+    def __init__(self, eps_o, eps_v):
+        self.eo = np.asarray(eps_o, dtype=float)
+        self.ev = np.asarray(eps_v, dtype=float)
+
+    def empty(self, n):
+        return np.full(int(n), np.nan)
+
+    def zeros(self, n):
+        return np.zeros(int(n))
+
+    def upload(self, a):
+        return np.array(a, dtype=float).reshape(-1)
+
+    def upload_int(self, a):
+        return np.array(a, dtype=np.int32).reshape(-1)
+
+    def download(self, buf):
+        return np.array(buf)
+
+    def copy(self, buf):
+        return np.array(buf)
+
+    def permute_axpby(self, src, dst, dims, perm, alpha, beta):
+        val = alpha * src[:int(np.prod(dims))].reshape(dims).transpose(perm).reshape(-1)
+        if beta == 0.0:
+            dst[:val.size] = val
+        else:
+            dst[:val.size] = val + beta * dst[:val.size]
+
+    def gemm_nt(self, a, b, c, m, n, k):
+        c[:m * n] = (a[:m * k].reshape(m, k) @ b[:n * k].reshape(n, k).T).reshape(-1)
+
+    def div_denominators(self, buf, rank):
+        o, v = self.eo.size, self.ev.size
+        eia = self.eo[:, None] - self.ev[None, :]
+        if rank == 2:
+            buf[:] = (buf.reshape(o, v) / eia).reshape(-1)
+        else:
+            buf[:] = (buf.reshape(o, o, v, v) / (eia[:, None, :, None] + eia[None, :, None, :])).reshape(-1)
+
+    def class_overwrite(self, new, old, rank, act_h, act_p, mask):
+        o, v = self.eo.size, self.ev.size
+        if rank == 2:
+            cls = 2 * act_h[:, None] + act_p[None, :]
+        else:
+            cls = (8 * act_h[:, None, None, None] + 4 * act_h[None, :, None, None]
+                   + 2 * act_p[None, None, :, None] + act_p[None, None, None, :])
+        sel = ((mask >> cls.reshape(-1)) & 1).astype(bool)
+        new[sel] = old[sel]
+
+    def dot(self, x, y, n):
+        return float(np.dot(x[:n], y[:n]))

@@ -1,0 +1,86 @@
+"""CPU checks of the CCSD-residual transcription (rows f1/f2): pyscf_mpcc_b200/rmpccsd.py driven through a
+NumPy stand-in backend against the REFERENCE's own rmpccsd_slow.update_amps / energy executed unmodified
+through oracle/ref_shim.py (build container), and against the committed fixture tests/golden/rmpccsd_*.npz."""
+import glob
+import os
+import types
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN
+from cc_problem import make_problem, reference_eris
+from np_backend import NumpyBackend
+from oracle import ref_shim
+from pyscf_mpcc_b200 import rmpccsd
+from pyscf_mpcc_b200.tensor_engine import Engine
+
+needs_ref = pytest.mark.skipif(not ref_shim.reference_available(), reason="reference tree not present")
+
+
+def _ours(p, act_h, act_p, idx_s, idx_d):
+    eng = Engine(NumpyBackend(p["eo"], p["ev"]))
+    eris = rmpccsd.DFERIs.from_numpy(eng, p["Loo"], p["Lov"], p["Lvv"], p["fock"])
+    cc = types.SimpleNamespace(cc2=False)
+    t1n, t2n = rmpccsd.update_amps(cc, p["t1"], p["t2"], eris, act_h, act_p, idx_s, idx_d)
+    return t1n, t2n, rmpccsd.energy(cc, p["t1"], p["t2"], eris), eng
+
+
+@needs_ref
+@pytest.mark.parametrize("case", [(3, 5, 11, [0, 2], [1, 3], [0, 2], [1, 5, 10, 12]),
+                                  (4, 7, 13, [1], [0, 2, 6], [], []),
+                                  (2, 6, 9, [0, 1], [0, 1, 2, 3, 4, 5], [1], list(range(15)))])
+def test_update_amps_against_reference_code(case):
+    o, v, L, act_h, act_p, idx_s, idx_d = case
+    p = make_problem(o, v, L, seed=o * 10 + v)
+    slow, _ = ref_shim.load_reference_cc()
+    cc = types.SimpleNamespace(cc2=False)
+    er = reference_eris(p)
+    t1r, t2r = slow.update_amps(cc, p["t1"], p["t2"], er, act_h, act_p, idx_s, idx_d)
+    e_r = slow.energy(cc, p["t1"], p["t2"], er)
+    t1n, t2n, e, eng = _ours(p, act_h, act_p, idx_s, idx_d)
+    assert np.abs(t1n - t1r).max() <= 1e-12
+    assert np.abs(t2n - t2r).max() <= 1e-12
+    assert abs(e - e_r) <= 1e-12
+    assert eng.gemms > 50
+
+
+def test_class_numbering_matches_get_index_tuples():
+    o, v = 5, 7
+    act_h, act_p = [1, 3], [0, 2, 5]
+    singles, doubles = rmpccsd.get_index_tuples(act_h, act_p, o, v)
+    ah = np.zeros(o, int); ah[act_h] = 1
+    ap = np.zeros(v, int); ap[act_p] = 1
+    for s, ix in enumerate(singles):
+        m = np.zeros((o, v), bool); m[ix] = True
+        cls = 2 * ah[:, None] + ap[None, :]
+        assert np.array_equal(m, cls == rmpccsd._SINGLES_BITS[s])
+    cls = (8 * ah[:, None, None, None] + 4 * ah[None, :, None, None] + 2 * ap[None, None, :, None] + ap[None, None, None, :])
+    seen = set()
+    for d, ix in enumerate(doubles):
+        m = np.zeros((o, o, v, v), bool); m[ix] = True
+        assert np.array_equal(m, cls == rmpccsd._DOUBLES_BITS[d]), d
+        seen.add(rmpccsd._DOUBLES_BITS[d])
+    assert seen == set(range(16))
+
+
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(GOLDEN, "rmpccsd_*.npz"))), ids=os.path.basename)
+def test_update_amps_against_fixture(path):
+    g = np.load(path)
+    o, v, L = (int(x) for x in g["shape"])
+    p = make_problem(o, v, L, seed=int(g["seed"]))
+    t1n, t2n, e, _ = _ours(p, list(g["act_hole"]), list(g["act_particle"]), list(g["idx_singles"]), list(g["idx_doubles"]))
+    assert np.abs(t1n - g["t1new"]).max() <= 1e-12
+    assert np.abs(t2n.reshape(-1)[::int(g["stride"])] - g["t2new_samples"]).max() <= 1e-12
+    assert abs(np.linalg.norm(t2n) - float(g["t2new_norm"])) <= 1e-11 and abs(e - float(g["energy"])) <= 1e-12
+
+
+def test_engine_rejects_what_it_cannot_do():
+    eng = Engine(NumpyBackend([0.0], [1.0]))
+    a = eng.tensor(np.ones((2, 3)))
+    with pytest.raises(NotImplementedError):
+        eng.einsum("ij,ij->ij", a, a)            # batch indices
+    with pytest.raises(NotImplementedError):
+        eng.einsum("ij,k->k", a, eng.tensor(np.ones(4)))   # index summed inside one operand
+    with pytest.raises(ValueError):
+        eng.einsum("ij,jk->ik", a, a)            # extent mismatch
