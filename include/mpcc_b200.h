@@ -140,6 +140,10 @@ int mpccb_permute_axpby(mpccb_ctx* ctx, const double* in_dev, double* out_dev, i
 /* t1[i,a] /= eps_o[i]-eps_v[a] (rank 2) or t2[i,j,a,b] /= eps_o[i]+eps_o[j]-eps_v[a]-eps_v[b] (rank 4)
  * (rmpccsd_slow.py:164-169) */
 int mpccb_div_denominators(mpccb_ctx* ctx, double* t_dev, int rank);
+/* t[x0..x_{r-1}] /= sum_d signs[d] * e_dev[d][x_d], rank <= 4: denominators in any index order / spin combination
+ * (pyscf/cc/umpcc_lowlevel.py:468-476 D_aa, D_ab, D_bb in [a,i,b,j] order; :350-354 the singles denominators) */
+int mpccb_div_general(mpccb_ctx* ctx, double* t_dev, int rank, const int* dims, const double* const* e_dev,
+                      const double* signs);
 /* active-space overwrite tnew[idx] = told[idx] (rmpccsd_slow.py:171-178, index classes of get_index_tuples :39-71):
  * bit (2*act_h[i] + act_p[a]) of class_mask for singles, bit (8*act_h[i] + 4*act_h[j] + 2*act_p[a] + act_p[b]) for
  * doubles; act_h_dev / act_p_dev are 0/1 int flags per occupied / virtual orbital */

@@ -97,6 +97,17 @@ def _direct_sum_general(spec, *ops):
     return _direct_sum(spec, *ops)
 
 
+_loaded_u = None
+
+
+def load_reference_unrestricted():
+    """pyscf/cc/umpcc_lowlevel.py executed from the reference tree (its ``updated_amp`` is the oracle of row f4)."""
+    load_reference()
+    if isinstance(_loaded_u, Exception) or _loaded_u is None:
+        raise _loaded_u if _loaded_u is not None else RuntimeError("unrestricted reference not loaded")
+    return _loaded_u
+
+
 def load_reference_cc():
     """(rmpccsd_slow module, rintermediates module) executed from the reference tree."""
     load_reference()
@@ -171,6 +182,22 @@ def load_reference():
         cc.rintermediates = imd
         slow = run("pyscf.cc.rmpccsd_slow", "cc/rmpccsd_slow.py")
         _loaded_cc = (slow, imd)
+        # unrestricted low-level prototype (row f4): only the module-level function updated_amp is used
+        global _loaded_u
+        try:
+            ao2mo._ao2mo = types.SimpleNamespace()
+            mod("pyscf.ao2mo._ao2mo")
+            pyscf.df = mod("pyscf.df")
+            mp = mod("pyscf.mp"); mp.__path__ = []; pyscf.mp = mp
+            ump2 = mod("pyscf.mp.ump2"); mp.ump2 = ump2
+            ump2.MP2 = type("MP2", (StreamObject,), {"_keys": set(), "__init__": lambda self, *a, **k: None})
+            ump2.make_rdm1 = ump2.make_rdm2 = None
+            dfn = mod("pyscf.mp.dfump2_native"); mp.dfump2_native = dfn
+            dfn.DFMP2 = type("DFMP2", (), {})
+            pyscf.scf = mod("pyscf.scf")                      # `from pyscf import scf, cc` at module level (:631)
+            _loaded_u = run("pyscf.cc.umpcc_lowlevel", "cc/umpcc_lowlevel.py")
+        except Exception as exc:
+            _loaded_u = exc
     except Exception as exc:                     # keep the low-level oracle usable even if this part fails
         _loaded_cc = exc
     # leave the fake package installed only under private aliases

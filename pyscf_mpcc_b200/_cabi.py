@@ -58,6 +58,8 @@ SIGNATURES = {
     "mpccb_permute_axpby": (c_int, [c_void_p, c_void_p, c_void_p, c_int, ctypes.POINTER(c_int), ctypes.POINTER(c_int),
                                     ctypes.c_double, ctypes.c_double]),
     "mpccb_div_denominators": (c_int, [c_void_p, c_void_p, c_int]),
+    "mpccb_div_general": (c_int, [c_void_p, c_void_p, c_int, ctypes.POINTER(c_int), ctypes.POINTER(c_void_p),
+                                  c_double_p]),
     "mpccb_class_overwrite": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, ctypes.c_uint]),
     "mpccb_dot": (c_int, [c_void_p, c_void_p, c_void_p, c_ll, c_void_p]),
     "mpccb_gemm_nt": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int]),

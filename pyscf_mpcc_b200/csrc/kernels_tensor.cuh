@@ -146,3 +146,32 @@ k_dot_partial(const double* __restrict__ x, const double* __restrict__ y, double
 }
 
 }  // namespace mpccb
+
+namespace mpccb {
+// t[x0,..,x_{r-1}] /= sum_d sign[d] * e[d][x_d]   — orbital-energy denominators in any index order and spin
+// combination (reference pyscf/cc/umpcc_lowlevel.py:468-476 D_aa/D_ab/D_bb in [a,i,b,j] order, :350-354 fock[0/1])
+struct DenomDesc {
+  int rank;
+  int dim[4];
+  const double* e[4];
+  double sign[4];
+  i64 total;
+};
+__global__ void __launch_bounds__(256)
+k_div_general(double* __restrict__ t, DenomDesc d) {
+  const i64 stride = (i64)gridDim.x * blockDim.x;
+  for (i64 idx = (i64)blockIdx.x * blockDim.x + threadIdx.x; idx < d.total; idx += stride) {
+    i64 rem = idx;
+    double den = 0.0;
+#pragma unroll
+    for (int k = 3; k >= 0; --k) {
+      if (k < d.rank) {
+        const i64 q = rem / d.dim[k];
+        den += d.sign[k] * d.e[k][rem - q * d.dim[k]];
+        rem = q;
+      }
+    }
+    t[idx] /= den;
+  }
+}
+}  // namespace mpccb

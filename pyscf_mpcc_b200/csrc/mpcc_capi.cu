@@ -1054,6 +1054,21 @@ extern "C" int mpccb_div_denominators(mpccb_ctx* c, double* t_dev, int rank) {
   return 0;
 }
 
+// t[x0..] /= sum_d sign[d] * e_dev[d][x_d]  (rank <= 4; e_dev[d] has dims[d] entries)
+extern "C" int mpccb_div_general(mpccb_ctx* c, double* t_dev, int rank, const int* dims,
+                                 const double* const* e_dev, const double* signs) {
+  if (rank < 1 || rank > 4) return fail(c, "div_general: rank 1..4");
+  DenomDesc d;
+  memset(&d, 0, sizeof(d));
+  d.rank = rank; d.total = 1;
+  for (int k = 0; k < rank; ++k) { d.dim[k] = dims[k]; d.e[k] = e_dev[k]; d.sign[k] = signs[k]; d.total *= dims[k]; }
+  if (d.total == 0) return 0;
+  const int nb = (int)std::min<i64>(cdiv(d.total, 256), NSM * 16);
+  k_div_general<<<nb, 256, 0, c->stream>>>(t_dev, d);
+  LAUNCH_OK(c, "k_div_general");
+  return 0;
+}
+
 // tnew[idx] = told[idx] for the active/inactive index classes in class_mask (see k_class_overwrite)
 extern "C" int mpccb_class_overwrite(mpccb_ctx* c, double* tnew_dev, const double* told_dev, int rank,
                                      const int* act_h_dev, const int* act_p_dev, unsigned class_mask) {

@@ -85,6 +85,11 @@ class CudaBackend:
     def div_denominators(self, buf, rank):
         self.ctx.call("mpccb_div_denominators", buf.data_ptr(), int(rank))
 
+    def div_general(self, buf, dims, evecs, signs):
+        r = len(dims)
+        self.ctx.call("mpccb_div_general", buf.data_ptr(), r, (ctypes.c_int * r)(*dims),
+                      (ctypes.c_void_p * r)(*[e.data_ptr() for e in evecs]), (ctypes.c_double * r)(*signs))
+
     def class_overwrite(self, new, old, rank, act_h, act_p, mask):
         self.ctx.call("mpccb_class_overwrite", new.data_ptr(), old.data_ptr(), int(rank), act_h.data_ptr(),
                       act_p.data_ptr(), int(mask))
@@ -213,7 +218,32 @@ class Engine:
         self.be.div_denominators(t.buf, t.ndim)
         return t
 
+    def div_general(self, t, evecs, signs):
+        """t[x0,..] /= sum_d signs[d] * evecs[d][x_d]; evecs are 1-D device tensors."""
+        if t.size:
+            self.be.div_general(t.buf, t.shape, [e.buf for e in evecs], signs)
+        return t
+
     def class_overwrite(self, tnew, told, act_h, act_p, mask):
         if mask:
             self.be.class_overwrite(tnew.buf, told.buf, tnew.ndim, act_h, act_p, mask)
         return tnew
+
+
+def make_cuda_engine(nocc, nvir, naux, device=None):
+    """Stand-alone engine (no MPCC_LL around it): a native context sized for (nocc, nvir, naux) — the sizes
+    only dimension its split-K / reduction scratch — with workspace and stream bound. Returns (engine, keepalive)."""
+    import torch
+    from . import _cabi
+    if not torch.cuda.is_available():
+        raise RuntimeError("the tensor engine needs a CUDA device; there is no CPU path")
+    device = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
+    if device.index is None:
+        device = torch.device("cuda", torch.cuda.current_device())
+    torch.cuda.set_device(device)
+    ctx = _cabi.Context(int(nocc), int(nvir), int(naux), 0, int(nvir), device.index)
+    ctx.call("mpccb_set_stream", torch.cuda.current_stream(device).cuda_stream)
+    nbytes = ctx.workspace_bytes()
+    ws = torch.empty(nbytes + 256, dtype=torch.uint8, device=device)
+    ctx.call("mpccb_bind_workspace", (ws.data_ptr() + 255) // 256 * 256, nbytes)
+    return Engine(CudaBackend(ctx, device)), (ctx, ws)

@@ -46,6 +46,14 @@ class NumpyBackend:
         else:
             buf[:] = (buf.reshape(o, o, v, v) / (eia[:, None, :, None] + eia[None, :, None, :])).reshape(-1)
 
+    def div_general(self, buf, dims, evecs, signs):
+        den = 0.0
+        for d, (e, sgn) in enumerate(zip(evecs, signs)):
+            shape = [1] * len(dims)
+            shape[d] = dims[d]
+            den = den + sgn * np.asarray(e)[:dims[d]].reshape(shape)
+        buf[:int(np.prod(dims))] = (buf[:int(np.prod(dims))].reshape(dims) / den).reshape(-1)
+
     def class_overwrite(self, new, old, rank, act_h, act_p, mask):
         o, v = self.eo.size, self.ev.size
         if rank == 2:
