@@ -64,6 +64,13 @@ int mpccb_bind_t2(mpccb_ctx* ctx, double* t2_abij_dev);
 int mpccb_bind_jk_exchange(mpccb_ctx* ctx, double* jk_local_dev, double* const* peer_jk_dev, int npeers,
                            double* jk_multicast_dev);
 
+/* Mirror scheme of the eris -> t2 step: e[(a,i),(b,j)] is a Gram matrix, so t2[a,b,i,j] = t2[b,a,j,i]; only one
+ * block of each pair is computed and its CTA also writes the mirror block (always inside one slab; option "t2_sym" 0
+ * turns it off). With several ranks and peer-mapped t2 buffers (symmetric memory) this call extends it across slabs:
+ * rank `rank` of `nranks` owns a in [slab_begin[rank], slab_begin[rank+1]); T_peers_dev[r] = rank r's t2 buffer as
+ * mapped on this device (own buffer included; replaces mpccb_bind_t2). */
+int mpccb_bind_t2_peers(mpccb_ctx* ctx, int nranks, int rank, const int* slab_begin, double* const* T_peers_dev);
+
 /* ---- one residual evaluation: MPCC_LL.updated_amps (dfrmpcc_lowlevel.py:103-152) --- */
 /* phase 1, :119-133 — T1 dressing and singles intermediates. Everything that carries a virtual index is
  * computed for the context's slab only (rows [a_begin*o, a_end*o) of JK = Jvo in [(a,i)][ldk] order,
@@ -76,6 +83,11 @@ int mpccb_dress_post(mpccb_ctx* ctx);
  * Writes the slab's partial sums to red_dev[0..nov) = Omega part [a,i], red_dev[nov] = dE part;
  * with several ranks the caller all-reduces red_dev (nov+1 doubles) before phase 3. */
 int mpccb_doubles(mpccb_ctx* ctx, double* red_dev);
+/* the same in two halves: begin = eris/t2 (with the mirror scheme of mpccb_bind_t2_peers the kernel also stores
+ * blocks into OTHER ranks' t2 buffers), end = Yvo, doubles->singles, energy. With peer-mapped t2 buffers the caller
+ * runs a cross-rank barrier on the stream between the two. */
+int mpccb_doubles_begin(mpccb_ctx* ctx, double* red_dev);
+int mpccb_doubles_end(mpccb_ctx* ctx, double* red_dev);
 /* phase 3, :128-131,:149-151 — assemble Omega, t1_new = -Omega^T/eia, scal_dev = {res^2, dE} */
 int mpccb_finish(mpccb_ctx* ctx, const double* red_dev, double* t1_new_dev, double* scal_dev);
 /* all three phases with HOST buffers and a final synchronize (single rank):
@@ -105,6 +117,12 @@ int mpccb_diis_push(mpccb_ctx* ctx, const double* t1_new_dev, const double* xpre
 /* xnew = sum_{k<nd} coeff[k] * x_list[k]  (n doubles each) */
 int mpccb_diis_combine(mpccb_ctx* ctx, const double* const* x_list_dev, const double* coeff_host,
                        int nd, double* xnew_dev, long long n);
+
+/* tiles the fused eris -> t2 kernel launches (mirror scheme) and the size of the full tile grid */
+int mpccb_t2_tiles(const mpccb_ctx* ctx, long long* launched, long long* total);
+/* the mirror-scheme rule as a pure host function (tests): bit 0 = the rank owning a computes block (a,b),
+ * bit 1 = it also writes the mirror block (b,a), bits 8.. = rank owning b */
+int mpccb_sym_query(int nranks, int rank, const int* slab_begin, int peers, int a, int b);
 
 /* ---- introspection for tests and profiling -------------------------------------------- */
 /* named scratch tensor (e.g. "JK", "Y", "Xoo", "Fvo"); see DESIGN.md for layouts */

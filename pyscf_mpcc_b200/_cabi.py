@@ -39,6 +39,11 @@ SIGNATURES = {
     "mpccb_dress": (c_int, [c_void_p, c_void_p]),
     "mpccb_dress_post": (c_int, [c_void_p]),
     "mpccb_doubles": (c_int, [c_void_p, c_void_p]),
+    "mpccb_t2_tiles": (c_int, [c_void_p, ctypes.POINTER(c_ll), ctypes.POINTER(c_ll)]),
+    "mpccb_sym_query": (c_int, [c_int, c_int, ctypes.POINTER(c_int), c_int, c_int, c_int]),
+    "mpccb_doubles_begin": (c_int, [c_void_p, c_void_p]),
+    "mpccb_doubles_end": (c_int, [c_void_p, c_void_p]),
+    "mpccb_bind_t2_peers": (c_int, [c_void_p, c_int, c_int, ctypes.POINTER(c_int), ctypes.POINTER(c_void_p)]),
     "mpccb_finish": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p]),
     "mpccb_updated_amps_host": (c_int, [c_void_p, c_void_p, c_void_p, c_double_p, c_double_p]),
     "mpccb_t2_to_aibj": (c_int, [c_void_p, c_void_p]),
@@ -125,6 +130,12 @@ class Context:
 
     def launch_count(self) -> int:
         return int(self.lib.mpccb_launch_count(self.h))
+
+    def t2_tiles(self):
+        """(launched, total) tiles of the fused eris -> t2 kernel."""
+        a, b = c_ll(), c_ll()
+        self.call("mpccb_t2_tiles", ctypes.byref(a), ctypes.byref(b))
+        return int(a.value), int(b.value)
 
     def buffer(self, name: str):
         p = c_void_p()

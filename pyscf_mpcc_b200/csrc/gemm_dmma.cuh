@@ -259,6 +259,48 @@ struct T2Params {
   int o, v, a_begin, a_end, n_a, n_b;
 };
 
+// Symmetry of the dressed integrals: e[(a,i),(b,j)] = e[(b,j),(a,i)] (a Gram matrix), hence
+// t2[a,b,i,j] = t2[b,a,j,i]. Only one block of every pair {(a,b),(b,a)} is computed; its CTA also writes the
+// mirror block t2[b,a,:,:] = t2[a,b,:,:]^T — into the local t2 buffer when b lies in the own slab, or straight into
+// the owning rank's buffer over NVLink when the t2 buffers are peer-mapped (halves the SYRK-shaped GEMM at every
+// rank count). Which block of a pair is computed (q = rank owning a, s = rank owning b, P ranks):
+//   s == q          : b >= a
+//   no peer mapping : every block with s != q is computed by q (nothing to mirror into)
+//   d = (s-q) mod P : 2d < P -> q computes;  2d > P -> s computes;  2d == P (antipodal slabs): the rank with the
+//                     smaller index computes the lower half of the other slab's b range, the larger one mirrors the rest
+struct SymInfo {
+  int enabled, nranks, rank, peers;
+  int bounds[17];            // slab begin of every rank; bounds[nranks] = nvir
+  double* Tp[16];            // t2 buffer of every rank ([a - bounds[r], b, i, j]); Tp[rank] is the local one
+  const int2* tiles;         // launch list of (tm, tn) pairs, or nullptr for the full grid
+  double* OmPm;              // [tiles_m][nov]: partial sums of t2 . Fov (:139) contributed through mirror blocks
+};
+
+__host__ __device__ __forceinline__ int sym_owner(const SymInfo& y, int b) {
+  int s = 0;
+  while (s + 1 < y.nranks && b >= y.bounds[s + 1]) ++s;
+  return s;
+}
+// does the rank that owns `a` compute block (a,b)?  mirror: must it also write block (b,a)?  s: owner of b
+__host__ __device__ __forceinline__ bool sym_compute(const SymInfo& y, int a, int b, bool& mirror, int& s) {
+  mirror = false;
+  s = y.rank;
+  if (!y.enabled) return true;
+  const int q = y.rank;
+  s = sym_owner(y, b);
+  if (s == q) { mirror = b > a; return b >= a; }
+  if (!y.peers) return true;
+  const int P = y.nranks;
+  const int d = (s - q + P) % P;
+  bool mine;
+  if (2 * d < P) mine = true;
+  else if (2 * d > P) mine = false;
+  else if (q < s) mine = b < (y.bounds[s] + y.bounds[s + 1]) / 2;
+  else mine = a >= (y.bounds[q] + y.bounds[q + 1]) / 2;
+  mirror = mine;
+  return mine;
+}
+
 template <class Cfg>
 struct T2Smem {
   static constexpr int PITCH = Cfg::TN + 1;   // odd pitch: column reads of the partner are conflict-free

@@ -108,7 +108,7 @@ struct TmaGemmParams {
 template <int EPI, int WN>
 __global__ void __launch_bounds__(TmaCfg<WN>::THREADS, TmaCfg<WN>::MIN_CTAS)
 gemm_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
-                TmaGemmParams p, T2Params t2p) {
+                TmaGemmParams p, T2Params t2p, SymInfo sym) {
   typedef TmaCfg<WN> Cfg;
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   double* ring = reinterpret_cast<double*>(smem_raw);
@@ -120,7 +120,12 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
   int tm, tn;
   const int ntiles = p.tiles_m * p.tiles_n;
   const int split = (EPI == 0 && p.ksplit > 1) ? blockIdx.x / ntiles : 0;
-  tile_coords(blockIdx.x - split * ntiles, p.tiles_m, p.tiles_n, tm, tn);
+  if (EPI == 1 && sym.tiles != nullptr) {
+    const int2 t = sym.tiles[blockIdx.x];
+    tm = t.x; tn = t.y;
+  } else {
+    tile_coords(blockIdx.x - split * ntiles, p.tiles_m, p.tiles_n, tm, tn);
+  }
   const int m0 = tm * p.tm_eff, n0 = tn * p.tn_eff;
   const bool producer = (threadIdx.x == 0);
   const int k_first = split * p.nk_split;                        // first K step of this CTA
@@ -239,6 +244,8 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
       for (int bl = 0; bl < t2p.n_b; ++bl) {
         const int b = tn * t2p.n_b + bl;
         if (b >= t2p.v) break;
+        bool mirror; int s;
+        if (!sym_compute(sym, a, b, mirror, s)) continue;      // produced by the CTA that owns the mirror block
         const double evb = t2p.ev[b];
         double* trow = t2p.T + (((i64)(a - t2p.a_begin) * t2p.v + b) * o + i) * o;
         const double* frow = t2p.Fvo + (i64)b * o;
@@ -253,6 +260,39 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
       }
       fsum = warp_sum(fsum);
       if (lane == 0) t2p.OmP[(i64)tn * mslab + (i64)(a - t2p.a_begin) * o + i] = fsum;
+    }
+    if (sym.enabled) {
+      // mirror pass: rows (b, j) of the blocks t2[b,a,:,:] = t2[a,b,:,:]^T, lanes along i (coalesced in the target)
+      const i64 nov = (i64)t2p.v * o;
+      for (int rr = warp; rr < t2p.n_b * o; rr += nwarps) {
+        const int bl = rr / o, j = rr - bl * o;
+        const int b = tn * t2p.n_b + bl;
+        if (b >= t2p.v) break;
+        const double dbj = t2p.ev[b] - t2p.eo[j];
+        double fsum = 0.0;
+        bool any = false;
+        for (int al = 0; al < t2p.n_a; ++al) {
+          const int a = t2p.a_begin + tm * t2p.n_a + al;
+          if (a >= t2p.a_end) break;
+          bool mirror; int s;
+          sym_compute(sym, a, b, mirror, s);
+          if (!mirror) continue;
+          any = true;
+          const double eva = t2p.ev[a];
+          double* trow = sym.Tp[s] + (((i64)(b - sym.bounds[s]) * t2p.v + a) * o + j) * o;
+          const double* frow = t2p.Fvo + (i64)a * o;
+          for (int i = lane; i < o; i += 32) {
+            const double e1 = S[(al * o + i) * PITCH + bl * o + j];
+            const double e2 = S[(al * o + j) * PITCH + bl * o + i];
+            const double den = -(eva - t2p.eo[i]) - dbj;
+            const double tv = (2.0 * e1 - e2) / den;
+            trow[i] = tv;
+            fsum += tv * frow[i];
+          }
+        }
+        fsum = warp_sum(fsum);
+        if (lane == 0 && any) sym.OmPm[(i64)tm * nov + (i64)b * o + j] = fsum;
+      }
     }
   }
 }

@@ -50,6 +50,10 @@ struct mpccb_ctx {
       *P, *OmRep, *OmLoc, *OmTot, *Z, *scal, *red, *YP;
   int yvo_split, yvo_split_force;
   JkTargets jk_targets;      // n == 0: plain local JK
+  SymInfo sym;               // symmetric eris/t2 scheme (host copy; tiles/OmPm are device pointers)
+  int sym_off, n_tiles;
+  int2* tiles_dev;
+  i64 tiles_cap;
   i64 P_count, OmP_count;
   int t2_na, t2_nb, t2_tiles_m, t2_tiles_n, t2_wn, t2_unfused, force_unfused;
   // optional per-stage CUDA-event timing (mpccb_set_option("profile", 1))
@@ -216,6 +220,47 @@ struct Carve {
   }
 };
 
+// the mirror scheme applies to the fused TMA kernel only
+bool t2_sym_active(const mpccb_ctx* c) { return !c->sym_off && c->use_tma && !c->t2_unfused; }
+
+// Launch list of the fused eris -> t2 kernel under the mirror scheme: every tile that holds at least one (a,b)
+// block this rank computes (sym_compute), ordered like tile_coords (8 column tiles x all row tiles per group).
+int build_tile_list(mpccb_ctx* c) {
+  c->sym.enabled = t2_sym_active(c) ? 1 : 0;
+  c->sym.tiles = nullptr;
+  c->n_tiles = c->t2_tiles_m * c->t2_tiles_n;
+  if (!c->sym.enabled) return 0;
+  if (!c->sym.peers) {               // no peer-mapped buffers: [0,a_begin) | own slab | [a_end,v), only the own slab mirrors
+    c->sym.nranks = 3; c->sym.rank = 1;
+    c->sym.bounds[0] = 0; c->sym.bounds[1] = c->a_begin; c->sym.bounds[2] = c->a_end; c->sym.bounds[3] = c->v;
+  }
+  c->sym.Tp[c->sym.rank] = c->T;
+  std::vector<int2> list;
+  list.reserve((size_t)c->n_tiles / 2 + 16);
+  for (int g0 = 0; g0 < c->t2_tiles_n; g0 += 8)
+    for (int tm = 0; tm < c->t2_tiles_m; ++tm)
+      for (int tn = g0; tn < std::min(g0 + 8, c->t2_tiles_n); ++tn) {
+        bool need = false;
+        for (int al = 0; al < c->t2_na && !need; ++al) {
+          const int a = c->a_begin + tm * c->t2_na + al;
+          if (a >= c->a_end) break;
+          for (int bl = 0; bl < c->t2_nb; ++bl) {
+            const int b = tn * c->t2_nb + bl;
+            if (b >= c->v) break;
+            bool mirror; int s;
+            if (sym_compute(c->sym, a, b, mirror, s)) { need = true; break; }
+          }
+        }
+        if (need) list.push_back(make_int2(tm, tn));
+      }
+  if ((i64)list.size() > c->tiles_cap) return fail(c, "tile list exceeds its workspace");
+  CUDA_OK(c, cudaMemcpyAsync(c->tiles_dev, list.data(), sizeof(int2) * list.size(), cudaMemcpyHostToDevice, c->stream));
+  CUDA_OK(c, cudaStreamSynchronize(c->stream));      // `list` is pageable host memory
+  c->n_tiles = (int)list.size();
+  c->sym.tiles = c->tiles_dev;
+  return 0;
+}
+
 // Split-K factor of the TMA Yvo GEMM: with few output tiles per SM (a-slab sharding) the last wave is
 // mostly idle; s K-slices turn T tiles into T*s shorter CTAs. Pick s <= 8 minimising ceil(T*s/148)/s.
 int choose_yvo_splits(const mpccb_ctx* c) {
@@ -257,6 +302,10 @@ i64 carve_workspace(mpccb_ctx* c, unsigned char* base) {
   c->Fvo = w.take(nov);
   c->OmP_count = (i64)c->t2_tiles_n * na * o;
   c->OmP = w.take(c->OmP_count);
+  const bool symm = t2_sym_active(c);
+  c->tiles_cap = symm ? (i64)c->t2_tiles_m * c->t2_tiles_n : 0;
+  c->tiles_dev = reinterpret_cast<int2*>(w.take(c->tiles_cap));          // int2 = one double each
+  c->sym.OmPm = w.take(symm ? (i64)c->t2_tiles_m * nov : 0);
   c->Y = w.take(nov * L);
   c->yvo_split = choose_yvo_splits(c);
   c->YP = w.take(c->yvo_split > 1 ? (i64)c->yvo_split * na * o * L : 0);
@@ -377,6 +426,11 @@ int mpccb_set_option(mpccb_ctx* c, const char* name, long long value) {
     return 0;
   }
   if (!strcmp(name, "profile")) { c->profile = value != 0; return 0; }
+  if (!strcmp(name, "t2_sym")) {          // 0: compute every (a,b) block (no mirror writes); before bind_workspace
+    if (c->ws) return fail(c, "set t2_sym before binding the workspace");
+    c->sym_off = value == 0;
+    return 0;
+  }
   if (!strcmp(name, "yvo_split")) {       // force the split-K factor of the TMA Yvo GEMM (0 = automatic; before bind_workspace)
     if (c->ws) return fail(c, "set yvo_split before binding the workspace");
     c->yvo_split_force = (int)value;
@@ -411,7 +465,7 @@ int mpccb_bind_workspace(mpccb_ctx* c, void* ws, size_t bytes) {
   // K padding columns of JK / E1K (ldk > L) must read as zero for the TMA path
   CUDA_OK(c, cudaMemsetAsync(c->JK, 0, sizeof(double) * c->nov * c->ldk, c->stream));
   CUDA_OK(c, cudaMemsetAsync(c->E1K, 0, sizeof(double) * c->nov * c->ldk, c->stream));
-  return 0;
+  return build_tile_list(c);
 }
 
 int mpccb_bind_integrals(mpccb_ctx* c, const double* Loo, const double* Lov, const double* Lvv,
@@ -425,7 +479,28 @@ int mpccb_bind_integrals(mpccb_ctx* c, const double* Loo, const double* Lov, con
   return 0;
 }
 
-int mpccb_bind_t2(mpccb_ctx* c, double* T) { c->T = T; return 0; }
+int mpccb_bind_t2(mpccb_ctx* c, double* T) {
+  c->T = T;
+  if (c->ws) return build_tile_list(c);
+  return 0;
+}
+
+// Several ranks with peer-mapped t2 buffers (symmetric memory): rank `rank` of `nranks` owns a in
+// [slab_begin[rank], slab_begin[rank+1]); T_peers_dev[r] is rank r's t2 buffer as seen from this device. Enables the
+// cross-rank half of the mirror scheme: blocks (a,b) with b in another rank's slab are computed by one of the two
+// ranks only, which stores the mirror block straight into the other's buffer. The caller must run a cross-rank
+// barrier on the stream between mpccb_doubles_begin and mpccb_doubles_end.
+int mpccb_bind_t2_peers(mpccb_ctx* c, int nranks, int rank, const int* slab_begin, double* const* T_peers_dev) {
+  if (nranks < 1 || nranks > 16 || rank < 0 || rank >= nranks) return fail(c, "bad rank layout");
+  if (slab_begin[rank] != c->a_begin || slab_begin[rank + 1] != c->a_end) return fail(c, "slab bounds do not match the context");
+  c->sym.peers = nranks > 1 ? 1 : 0;
+  c->sym.nranks = nranks; c->sym.rank = rank;
+  for (int r = 0; r <= nranks; ++r) c->sym.bounds[r] = slab_begin[r];
+  for (int r = 0; r < nranks; ++r) c->sym.Tp[r] = T_peers_dev[r];
+  c->T = T_peers_dev[rank];
+  if (c->ws) return build_tile_list(c);
+  return 0;
+}
 
 int mpccb_bind_jk_exchange(mpccb_ctx* c, double* jk_local_dev, double* const* peer_jk_dev, int npeers,
                            double* jk_multicast_dev) {
@@ -583,7 +658,11 @@ int launch_tma(mpccb_ctx* c, const char* what, const CUtensorMap& mA, const CUte
     CUDA_OK(c, cudaFuncSetAttribute(gemm_tma_kernel<EPI, WN>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
     attr_done = true;
   }
-  gemm_tma_kernel<EPI, WN><<<p.tiles_total > 0 ? p.tiles_total : p.tiles_m * p.tiles_n, Cfg::THREADS, smem, c->stream>>>(mA, mB, p, t2p);
+  SymInfo sym;
+  memset(&sym, 0, sizeof(sym));
+  int grid = p.tiles_total > 0 ? p.tiles_total : p.tiles_m * p.tiles_n;
+  if (EPI == 1 && c->sym.enabled) { sym = c->sym; sym.Tp[sym.rank] = c->T; grid = c->n_tiles; }
+  gemm_tma_kernel<EPI, WN><<<grid, Cfg::THREADS, smem, c->stream>>>(mA, mB, p, t2p, sym);
   LAUNCH_OK(c, what);
   return 0;
 }
@@ -711,22 +790,45 @@ int launch_yvo(mpccb_ctx* c) {
 
 }  // namespace
 
-extern "C" int mpccb_doubles(mpccb_ctx* c, double* red_dev) {
+extern "C" int mpccb_doubles_begin(mpccb_ctx* c, double* red_dev) {
   if (!c->T) return fail(c, "t2 buffer not bound");
-  const int o = c->o, v = c->v, L = c->L, na = c->na;
+  const int o = c->o, na = c->na;
   const i64 nov = c->nov;
-  double* Om = red_dev;   // [a][i] partial over the local slab
+  double* Om = red_dev;   // [a][i] partial sums
   CUDA_OK(c, cudaMemsetAsync(red_dev, 0, sizeof(double) * (nov + 1), c->stream));
   // the slab's W.Joo singles term from mpccb_dress (:126-127) joins the partial sums
   CUDA_OK(c, cudaMemcpyAsync(Om + (i64)c->a_begin * o, c->OmRep + (i64)c->a_begin * o, sizeof(double) * na * o,
                              cudaMemcpyDeviceToDevice, c->stream));
+  const bool symm = c->sym.enabled && !c->t2_unfused && c->use_tma;
+  if (symm) {   // tiles that are not launched / rows that are not mirrored must read as zero in the reductions
+    CUDA_OK(c, cudaMemsetAsync(c->OmP, 0, sizeof(double) * c->OmP_count, c->stream));
+    CUDA_OK(c, cudaMemsetAsync(c->sym.OmPm, 0, sizeof(double) * c->t2_tiles_m * nov, c->stream));
+  }
   {
     StageTimer timer(c, ST_ERIS_T2);
     if (launch_eris_t2(c)) return 1;                                 // :135-137 (+ :139 partials)
   }
-  // :139  Om[a_loc][i] += sum_tiles OmP
+  // :139  Om[a_loc][i] += sum_tiles OmP;  mirror blocks contribute to rows (b,j) of any slab
   if (reduce_splits(c, Om + (i64)c->a_begin * o, c->OmP, c->t2_tiles_n, (i64)na * o, (i64)na * o, 1.0, 1.0))
     return 1;
+  if (symm && reduce_splits(c, Om, c->sym.OmPm, c->t2_tiles_m, nov, nov, 1.0, 1.0)) return 1;
+  return 0;
+}
+
+extern "C" int mpccb_doubles_end(mpccb_ctx* c, double* red_dev);
+
+extern "C" int mpccb_doubles(mpccb_ctx* c, double* red_dev) {
+  if (c->sym.enabled && c->sym.peers)
+    return fail(c, "peer-mapped t2: call mpccb_doubles_begin, a cross-rank barrier, then mpccb_doubles_end");
+  if (mpccb_doubles_begin(c, red_dev)) return 1;
+  return mpccb_doubles_end(c, red_dev);
+}
+
+extern "C" int mpccb_doubles_end(mpccb_ctx* c, double* red_dev) {
+  if (!c->T) return fail(c, "t2 buffer not bound");
+  const int o = c->o, v = c->v, L = c->L, na = c->na;
+  const i64 nov = c->nov;
+  double* Om = red_dev;
   {
     StageTimer timer(c, ST_YVO);
     if (launch_yvo(c)) return 1;                                     // :138
@@ -912,6 +1014,25 @@ extern "C" int mpccb_ao2mo_block(mpccb_ctx* c, const double* packed_dev, int nb,
     else           { if (launch_gemm<CfgM64RR>(c, "ao2mo.full", A, B, C, b.np, nb * b.nq, nao, 1, nullptr)) return 1; }
   }
   return 0;
+}
+
+// tiles of the fused eris -> t2 kernel: launched under the mirror scheme vs the full grid
+extern "C" int mpccb_t2_tiles(const mpccb_ctx* c, long long* launched, long long* total) {
+  *total = (long long)c->t2_tiles_m * c->t2_tiles_n;
+  *launched = c->sym.enabled ? c->n_tiles : *total;
+  return 0;
+}
+
+// pure host query of the mirror-scheme rule (no context, no GPU): bit 0 = the rank owning `a` computes block
+// (a,b), bit 1 = it also writes the mirror block (b,a), bits 8.. = rank that owns b
+extern "C" int mpccb_sym_query(int nranks, int rank, const int* slab_begin, int peers, int a, int b) {
+  SymInfo y;
+  memset(&y, 0, sizeof(y));
+  y.enabled = 1; y.nranks = nranks; y.rank = rank; y.peers = peers;
+  for (int r = 0; r <= nranks && r < 17; ++r) y.bounds[r] = slab_begin[r];
+  bool mirror; int s;
+  const bool comp = sym_compute(y, a, b, mirror, s);
+  return (comp ? 1 : 0) | (mirror ? 2 : 0) | (s << 8);
 }
 
 // ===========================================================================

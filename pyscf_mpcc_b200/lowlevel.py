@@ -103,7 +103,7 @@ class MPCC_LL:
     """GPU-resident equivalent of ``pyscf.mpcc.dfrmpcc_lowlevel.MPCC_LL``."""
 
     def __init__(self, mf=None, *, blocks=None, device=None, group=None, use_tma=True, t2_wide_tiles=None, t2_unfused=None, yvo_split=None,
-                 jk_exchange=None):
+                 jk_exchange=None, t2_sym=None):
         """``MPCC_LL(mf)`` as in the reference (:7-43). Extensions (keyword only):
 
         blocks : (Loo, Lov, Lvv, foo, fvv, mo_energy) numpy arrays or CUDA tensors
@@ -166,6 +166,11 @@ class MPCC_LL:
         self._ctx.call("mpccb_set_option", b"tma", int(bool(use_tma)))
         if t2_wide_tiles is None and os.environ.get("MPCC_T2_WIDE_TILES"):
             t2_wide_tiles = os.environ["MPCC_T2_WIDE_TILES"] != "0"
+        if t2_sym is None and os.environ.get("MPCC_T2_SYM"):
+            t2_sym = os.environ["MPCC_T2_SYM"] != "0"
+        if t2_sym is not None:             # mirror scheme of the eris -> t2 step (default on)
+            self._ctx.call("mpccb_set_option", b"t2_sym", int(bool(t2_sym)))
+        self._t2_sym = True if t2_sym is None else bool(t2_sym)
         if yvo_split is not None:
             self._ctx.call("mpccb_set_option", b"yvo_split", int(yvo_split))
         if t2_unfused is not None:
@@ -180,8 +185,12 @@ class MPCC_LL:
         self._jk_mode = "local"
         if self.world_size > 1:
             self._setup_jk_exchange(jk_exchange or os.environ.get("MPCC_JK_EXCHANGE", "auto"))
-        self._T = torch.empty(self._na * v * o * o, **f64)
-        self._ctx.call("mpccb_bind_t2", self._T.data_ptr())
+        self._t2_peers = False
+        if self.world_size > 1 and self._t2_sym and self._jk_mode in ("multicast", "p2p"):
+            self._setup_t2_peers()
+        if not self._t2_peers:
+            self._T = torch.empty(self._na * v * o * o, **f64)
+            self._ctx.call("mpccb_bind_t2", self._T.data_ptr())
         self._t2_serial = 0
         self._red = torch.zeros(self.nov + 1, **f64)
         self._t1_dev = torch.zeros(self.nov, **f64)
@@ -361,6 +370,43 @@ class MPCC_LL:
         self._equal_slabs = len({hi - lo for lo, hi in self._jk_rows}) == 1
         self._jk_mode = "nccl"
 
+    def _setup_t2_peers(self):
+        """Cross-rank half of the mirror scheme (include/mpcc_b200.h, mpccb_bind_t2_peers): the t2 slabs live in
+        symmetric memory so that the rank computing block (a,b) can store the mirror block t2[b,a] straight into
+        the buffer of the rank that owns b. All ranks agree; on failure everyone keeps private buffers."""
+        dist = torch.distributed
+        o, v = self.nocc, self.nvir
+        bounds = [sharding.slab_bounds(v, self.world_size, r)[0] for r in range(self.world_size)] + [v]
+        n_max = max(bounds[r + 1] - bounds[r] for r in range(self.world_size)) * v * o * o
+        ok, buf, hdl = 0, None, None
+        try:
+            import torch.distributed._symmetric_memory as symm
+            buf = symm.empty(n_max, dtype=torch.float64, device=self.device)
+            hdl = symm.rendezvous(buf, self.group)
+            ok = 1
+        except Exception as e:
+            self._t2_peers_error = repr(e)
+        flag = torch.tensor([ok], device=self.device)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=self.group)
+        if int(flag.item()) != 1:
+            return
+        peers = (ctypes.c_void_p * self.world_size)(*[int(p) for p in hdl.buffer_ptrs])
+        self._ctx.call("mpccb_bind_t2_peers", self.world_size, self.rank, (ctypes.c_int * (self.world_size + 1))(*bounds), peers)
+        self._T = buf[:self._na * v * o * o]
+        self._t2_buf, self._t2_hdl = buf, hdl
+        self._t2_peers = True
+
+    def _doubles(self):
+        """Phase 2 (:135-147). With peer-mapped t2 buffers other ranks store mirror blocks into this rank's slab
+        during the eris/t2 kernel, so a cross-rank barrier separates it from the Yvo GEMM that reads the slab."""
+        ctx = self._ctx
+        if not self._t2_peers:
+            ctx.call("mpccb_doubles", self._red.data_ptr())
+            return
+        ctx.call("mpccb_doubles_begin", self._red.data_ptr())
+        self._t2_hdl.barrier(channel=1)
+        ctx.call("mpccb_doubles_end", self._red.data_ptr())
+
     def _dress(self, t1_dev):
         """T1 dressing (:119-133). One rank: a single native call. Several ranks: each dresses its own
         virtual slab, the dressed integrals Jvo (rows of the K-major JK buffer; a slab is a contiguous
@@ -396,7 +442,7 @@ class MPCC_LL:
             self.h2d_bytes += self.nov * 8
         ctx = self._ctx
         self._dress(self._t1_dev)
-        ctx.call("mpccb_doubles", self._red.data_ptr())
+        self._doubles()
         self._t2_serial += 1
         if self.world_size > 1:
             torch.distributed.all_reduce(self._red, group=self.group)
@@ -420,7 +466,7 @@ class MPCC_LL:
         self._bind_stream()
         ctx = self._ctx
         self._dress(t1_dev)
-        ctx.call("mpccb_doubles", self._red.data_ptr())
+        self._doubles()
         self._t2_serial += 1
         if self.world_size > 1:
             torch.distributed.all_reduce(self._red, group=self.group)

@@ -147,3 +147,34 @@ def test_flop_and_byte_counts():
     assert flops.eris_flops(64, 512, 1536, 512) == 2.0 * 1536 * 32768 ** 2
     n = 32768 + 32768 * 32769 // 2
     assert flops.diis_bytes(64, 512, 6) == 8.0 * n * 16
+
+
+@pytest.mark.parametrize("nranks,v", [(1, 7), (2, 8), (2, 9), (3, 10), (4, 13), (8, 16), (8, 37)])
+def test_mirror_scheme_covers_every_block_exactly_once(nranks, v):
+    """Rule of the symmetric eris/t2 scheme (include/mpcc_b200.h, mpccb_bind_t2_peers): of every pair of blocks
+    {(a,b),(b,a)} exactly one is computed, by the rank that owns its first index, and that rank mirrors it; the
+    work is balanced to within one slab-half. Pure host function of the library (no GPU)."""
+    import ctypes
+    from pyscf_mpcc_b200 import _cabi, sharding
+    lib = _cabi.load()
+    bounds = [sharding.slab_bounds(v, nranks, r)[0] for r in range(nranks)] + [v]
+    arr = (ctypes.c_int * (nranks + 1))(*bounds)
+    owner = lambda x: max(r for r in range(nranks) if bounds[r] <= x)
+    work = [0] * nranks
+    for a in range(v):
+        for b in range(v):
+            qa, qb = owner(a), owner(b)
+            fa = lib.mpccb_sym_query(nranks, qa, arr, 1, a, b)
+            fb = lib.mpccb_sym_query(nranks, qb, arr, 1, b, a)
+            assert (fa >> 8) == qb and (fb >> 8) == qa
+            if a == b:
+                assert fa & 1 and not fa & 2
+            else:
+                assert (fa & 1) + (fb & 1) == 1, (a, b)          # exactly one of the pair is computed ...
+                assert bool(fa & 1) == bool(fa & 2) and bool(fb & 1) == bool(fb & 2)   # ... and mirrored by its owner
+            work[qa] += fa & 1
+            # without peer mapping every cross-slab block is computed locally and nothing is mirrored across slabs
+            f0 = lib.mpccb_sym_query(nranks, qa, arr, 0, a, b)
+            assert (f0 & 1) == (1 if qa != qb else int(b >= a)) and bool(f0 & 2) == (qa == qb and b > a)
+    if v % nranks == 0 and (v // nranks) % 2 == 0:
+        assert max(work) - min(work) <= v // nranks          # balanced: P/2 slab-blocks each (+- the diagonal)
