@@ -1,13 +1,16 @@
-// TMA-fed, warp-specialised FP64 DMMA GEMM for the two O(naux * nov^2) products of the DF-MPCC
+// TMA-fed FP64 DMMA GEMM for the two O(naux * nov^2) products of the DF-MPCC
 // iteration (reference pyscf/mpcc/dfrmpcc_lowlevel.py:135 "eris" and :138 "Yvo").
 //
 //   C[m, n] = sum_k A[m, k] * B[n, k],  A and B K-major in global memory.
 //
 // Blackwell has no tcgen05 kind for FP64, so the math is DMMA.8x8x4 from registers;
-// what is sm_100a-native here is the data path: one producer warp issues cp.async.bulk.tensor (TMA)
-// loads of 128-row x 16-k operand boxes into a 4-stage shared-memory ring (SWIZZLE_128B), completion
-// is signalled on mbarriers, and 16 consumer warps (4 per SM sub-partition, 32x32 accumulators each)
-// never touch global memory or block-wide barriers inside the K loop.
+// what is sm_100a-native here is the data path: cp.async.bulk.tensor (TMA) loads of 128-row x 16-k
+// operand boxes into a 4-stage shared-memory ring (SWIZZLE_128B), completion signalled on mbarriers;
+// every warp (4 per SM sub-partition, 32x32 accumulators each) is a consumer that never touches global
+// memory or block-wide barriers inside the K loop, and lane 0 of warp 0 doubles as the TMA producer
+// (a separate producer warp would be the 5th warp of one sub-partition and cap the kernel at 96 registers).
+// Epilogues: plain / split-K store (Yvo, generic products) and the fused eris -> t2 epilogue with the
+// mirror scheme (SymInfo, gemm_dmma.cuh).
 //
 // Bank conflicts: a fragment load reads element (row, k = 4*ks + tig) for the 8 rows `g` of a group.
 // With the 128-byte swizzle the 16-byte chunk index is (k/2) ^ (row % 8); mapping fragment row g to

@@ -357,7 +357,7 @@ void set_t2_geometry(mpccb_ctx* c, int wn) {
 
 extern "C" {
 
-const char* mpccb_version(void) { return "mpcc_b200 0.1 (sm_100a, DMMA.8x8x4)"; }
+const char* mpccb_version(void) { return "mpcc_b200 0.2 (sm_100a, DMMA.8x8x4, TMA)"; }
 
 int mpccb_create(mpccb_ctx** out, int nocc, int nvir, int naux, int a_begin, int a_end, int device) {
   if (!out) return 1;
