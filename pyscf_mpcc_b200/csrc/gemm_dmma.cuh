@@ -47,6 +47,10 @@ struct GemmDims {
   int tm_eff, tn_eff;  // rows/cols a tile advances by (<= TM/TN); == TM/TN for plain GEMMs
   int tiles_m, tiles_n;
   int kchunk;          // K range per blockIdx.z (multiple of 16)
+  // mirror scheme of the unfused eris GEMM (0 = off): rows are global indices sym_row0 + m over (a,i), columns (b,j);
+  // a tile whose columns all lie in [sym_col_lo, ...) and whose last column block b is below its first row block a
+  // holds only blocks that are produced as mirrors, and is skipped
+  int sym_o, sym_row0, sym_col_lo;
 };
 
 constexpr int TK = 16;
@@ -208,6 +212,7 @@ gemm_store_kernel(Operand A, Operand B, Output C, GemmDims d) {
   int tm, tn;
   tile_coords(blockIdx.x, d.tiles_m, d.tiles_n, tm, tn);
   const int m0 = tm * d.tm_eff, n0 = tn * d.tn_eff;
+  if (d.sym_o > 0 && n0 >= d.sym_col_lo && (min(n0 + Cfg::TN, d.N) - 1) / d.sym_o < (d.sym_row0 + m0) / d.sym_o) return;
   const int kbeg = blockIdx.z * d.kchunk;
   const int kend = min(d.K, kbeg + d.kchunk);
   double acc[Cfg::MT][Cfg::NT][2];

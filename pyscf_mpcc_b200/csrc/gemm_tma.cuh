@@ -143,8 +143,12 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
     if (p.a_mode == 0) {
       tma_load_2d(a_dst, &mapA, &full[s], kt * TMA_TK, m0);
     } else {
+      // K runs over (b, j); j in chunks of 16 — for nocc not a multiple of 16 the last chunk of every b reads past
+      // the j extent of the 4-D map and TMA zero-fills it, which also cancels B's columns of the next b
       const int b = kt / p.jsteps, j0 = (kt - b * p.jsteps) * TMA_TK;
       tma_load_4d(a_dst, &mapA, &full[s], j0, 0, b, tm * p.n_a);
+      tma_load_2d(b_dst, &mapB, &full[s], b * p.o + j0, n0);
+      return;
     }
     tma_load_2d(b_dst, &mapB, &full[s], kt * TMA_TK, n0);
   };

@@ -338,10 +338,16 @@ namespace mpccb {
 // fixed order) from the block's own freshly written (L1/L2-hot) values.
 __global__ void __launch_bounds__(256)
 k_t2_finalize(double* __restrict__ T, const double* __restrict__ eo, const double* __restrict__ ev,
-              const double* __restrict__ Fvo, double* __restrict__ OmP, int o, int v, int a_begin, int na) {
-  const int b = blockIdx.x, al = blockIdx.y;
+              const double* __restrict__ Fvo, double* __restrict__ OmP, int o, int v, int a_begin, int na, int sym) {
+  // sym: mirror scheme inside the slab — blocks with b < a are not touched by the GEMM nor here; block (a,b), b > a,
+  // also writes t2[b,a,:,:] = t2[a,b,:,:]^T; of a diagonal block only the j >= i half of e was computed (e is symmetric).
+  const int b = blockIdx.x, al = blockIdx.y, a = a_begin + al;
+  const bool in_slab = sym && b >= a_begin && b < a_begin + na;
+  if (in_slab && b < a) return;
   double* blk = T + ((i64)al * v + b) * o * o;
-  const double dab = ev[a_begin + al] + ev[b];
+  double* mir = (in_slab && b > a) ? T + ((i64)(b - a_begin) * v + a) * o * o : nullptr;
+  const bool diag = in_slab && b == a;
+  const double dab = ev[a] + ev[b];
   const int npair = o * (o + 1) / 2;
   for (int p = threadIdx.x; p < npair; p += blockDim.x) {
     // p -> (j, i) with i <= j: row j of the packed lower triangle
@@ -349,10 +355,16 @@ k_t2_finalize(double* __restrict__ T, const double* __restrict__ eo, const doubl
     while (j * (j + 1) / 2 > p) --j;
     while ((j + 1) * (j + 2) / 2 <= p) ++j;
     const int i = p - j * (j + 1) / 2;
-    const double eij = blk[i * o + j], eji = blk[j * o + i];
+    const double eij = blk[i * o + j];
+    const double eji = diag ? eij : blk[j * o + i];
     const double den = eo[i] + eo[j] - dab;
-    blk[i * o + j] = (2.0 * eij - eji) / den;
-    if (i != j) blk[j * o + i] = (2.0 * eji - eij) / den;
+    const double tij = (2.0 * eij - eji) / den, tji = (2.0 * eji - eij) / den;
+    blk[i * o + j] = tij;
+    if (i != j) blk[j * o + i] = tji;
+    if (mir) {
+      mir[j * o + i] = tij;
+      if (i != j) mir[i * o + j] = tji;
+    }
   }
   __threadfence_block();
   __syncthreads();
@@ -363,6 +375,15 @@ k_t2_finalize(double* __restrict__ T, const double* __restrict__ eo, const doubl
     for (int j = lane; j < o; j += 32) s += blk[i * o + j] * f[j];
     s = warp_sum(s);
     if (lane == 0) OmP[((i64)b * na + al) * o + i] = s;
+  }
+  if (mir) {   // the mirror block's share of sum t2 . Fov: rows (b, j), slot of the block (b, a)
+    const double* fa = Fvo + (i64)a * o;
+    for (int j = warp; j < o; j += nw) {
+      double s = 0.0;
+      for (int i = lane; i < o; i += 32) s += mir[j * o + i] * fa[i];
+      s = warp_sum(s);
+      if (lane == 0) OmP[((i64)a * na + (b - a_begin)) * o + j] = s;
+    }
   }
 }
 }  // namespace mpccb

@@ -146,9 +146,10 @@ int choose_splits(int tiles, int K) {
 
 template <class Cfg>
 int launch_gemm(mpccb_ctx* c, const char* what, const Operand& A, const Operand& B, Output C,
-                int M, int N, int K, int splits, double* partial) {
+                int M, int N, int K, int splits, double* partial, int sym_o = 0, int sym_row0 = 0, int sym_col_lo = 0) {
   GemmDims d;
   d.M = M; d.N = N; d.K = K;
+  d.sym_o = sym_o; d.sym_row0 = sym_row0; d.sym_col_lo = sym_col_lo;
   d.tm_eff = Cfg::TM; d.tn_eff = Cfg::TN;
   d.tiles_m = cdiv(M, Cfg::TM); d.tiles_n = cdiv(N, Cfg::TN);
   d.kchunk = (int)align_up(cdiv(K, splits), TK);
@@ -265,10 +266,10 @@ int build_tile_list(mpccb_ctx* c) {
 // mostly idle; s K-slices turn T tiles into T*s shorter CTAs. Pick s <= 8 minimising ceil(T*s/148)/s.
 int choose_yvo_splits(const mpccb_ctx* c) {
   const int o = c->o;
-  if (!c->use_tma || o % TMA_TK != 0 || o > 128 || (128 / o) * o < 96) return 1;
+  if (!c->use_tma || o % 2 != 0 || o > 128 || (128 / o) * o < 96) return 1;
   const int n_a = 128 / o;
   const i64 T = (i64)cdiv(c->na, n_a) * cdiv(c->L, 128);
-  const i64 nk = (i64)c->v * (o / TMA_TK);
+  const i64 nk = (i64)c->v * cdiv(o, TMA_TK);
   if (c->yvo_split_force > 0) return (int)std::min<i64>(c->yvo_split_force, nk);
   double best = (double)cdiv(T, NSM);
   int best_s = 1;
@@ -711,8 +712,8 @@ int launch_yvo_tma(mpccb_ctx* c) {
   p.M = c->na * o; p.N = L;
   p.tm_eff = n_a * o; p.tn_eff = TN;
   p.tiles_m = cdiv(c->na, n_a); p.tiles_n = cdiv(L, TN);
-  p.nk = v * (o / TMA_TK);
-  p.a_mode = 1; p.jsteps = o / TMA_TK; p.o = o; p.n_a = n_a;
+  p.nk = v * cdiv(o, TMA_TK);
+  p.a_mode = 1; p.jsteps = cdiv(o, TMA_TK); p.o = o; p.n_a = n_a;
   p.a_bytes = (uint32_t)(TMA_TK * o * n_a * 8); p.b_bytes = TN * TMA_TK * 8;
   double* Yslab = c->Y + (i64)c->a_begin * o * L;
   p.C = Yslab; p.ldc = L;
@@ -742,9 +743,11 @@ int launch_eris_t2_unfused(mpccb_ctx* c) {
   Output C = flat_output(c->T, 0, 0);
   C.mdiv = o; C.m_hi = (i64)v * o * o; C.m_lo = o;      // m = (a_l, i)
   C.ndiv = o; C.n_hi = (i64)o * o;     C.n_lo = 1;      // n = (b, j)
-  if (launch_gemm<CfgBigKK>(c, "eris(unfused)", A, B, C, c->na * o, v * o, L, 1, nullptr)) return 1;
+  const int symm = c->sym_off ? 0 : 1;     // mirror scheme inside the slab
+  if (launch_gemm<CfgBigKK>(c, "eris(unfused)", A, B, C, c->na * o, v * o, L, 1, nullptr,
+                            symm ? o : 0, c->a_begin * o, c->a_begin * o)) return 1;
   dim3 grid(v, c->na);
-  k_t2_finalize<<<grid, 256, 0, c->stream>>>(c->T, c->eo, c->ev, c->Fvo, c->OmP, o, v, c->a_begin, c->na);
+  k_t2_finalize<<<grid, 256, 0, c->stream>>>(c->T, c->eo, c->ev, c->Fvo, c->OmP, o, v, c->a_begin, c->na, symm);
   LAUNCH_OK(c, "k_t2_finalize");
   return 0;
 }
@@ -764,6 +767,7 @@ int launch_eris_t2(mpccb_ctx* c) {
   d.tm_eff = c->t2_na * o; d.tn_eff = c->t2_nb * o;
   d.tiles_m = c->t2_tiles_m; d.tiles_n = c->t2_tiles_n;
   d.kchunk = L;
+  d.sym_o = 0; d.sym_row0 = 0; d.sym_col_lo = 0;
   static bool attr_done = false;
   if (!attr_done) {
     CUDA_OK(c, cudaFuncSetAttribute(gemm_t2_kernel<Cfg>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -777,7 +781,8 @@ int launch_eris_t2(mpccb_ctx* c) {
 
 int launch_yvo(mpccb_ctx* c) {
   const int o = c->o, v = c->v, L = c->L;
-  if (c->use_tma && o % TMA_TK == 0 && o <= 128 && (128 / o) * o >= 96) return launch_yvo_tma(c);
+  // TMA strides must be multiples of 16 bytes: even nocc
+  if (c->use_tma && o % 2 == 0 && o <= 128 && (128 / o) * o >= 96) return launch_yvo_tma(c);
   // :138  Y[(a,i)][L] = sum_{(b,j)} T[a][b][i][j] Lvo[L][(b,j)]
   Operand A;
   A.base = c->T; A.rows = c->na * o;
