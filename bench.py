@@ -55,6 +55,10 @@ def parse_args():
     ap.add_argument("--seed", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-tma", action="store_true")
+    ap.add_argument("--diis-layout", default=None, choices=["columns", "rows"],
+                    help="t2 part of the DIIS vector over ranks: balanced column ownership (default for N>1) or row segments")
+    ap.add_argument("--slabs", default="equal", choices=["balanced", "equal"],
+                    help="split of the virtual index over ranks (sharding.balanced_bounds / equal widths)")
     return ap.parse_args()
 
 
@@ -220,7 +224,8 @@ def run_b200(args):
     Loo, Lov, Lvv, eo, ev = device_blocks(o, v, L, seed=args.seed, scale=default_scale(o, v), device=dev)
     foo = torch.diag(eo)
     fvv = torch.diag(ev)
-    ll = MPCC_LL(blocks=(Loo, Lov, Lvv, foo, fvv, torch.cat([eo, ev])), device=dev, use_tma=not args.no_tma)
+    ll = MPCC_LL(blocks=(Loo, Lov, Lvv, foo, fvv, torch.cat([eo, ev])), device=dev, use_tma=not args.no_tma,
+                 slabs=args.slabs, diis_layout=args.diis_layout)
     ll.verbose_print = False
     ctx = ll._ctx
     nov = o * v
@@ -337,7 +342,8 @@ def run_b200(args):
         "config": {"workload": f"synthetic DF-MPCC nocc={o} nvir={v} naux={L} (BASELINE.json configs[2])",
                    "step": "updated_amps + run_diis (first K iterations of a solve from t1=0, DIIS on)",
                    "l2": "inputs_exceed_l2 (t2 buffer 8.6 GB, DIIS vectors 4.3 GB each at the default shape)",
-                   "parallelism": f"a-slab x{world}", "jk_exchange": ll._jk_mode, "t2_peer_mirror": bool(ll._t2_peers),
+                   "parallelism": f"a-slab x{world}", "slab_bounds": list(ll._bounds) if world > 1 else None,
+                   "diis_vector": "column-owned" if ll._diis_columns else "row-owned", "jk_exchange": ll._jk_mode, "t2_peer_mirror": bool(ll._t2_peers),
                    "flop_per_iteration": flop_it,
                    "flop_note": "value counts the ALGORITHMIC flops of the reference iteration (SURVEY.md 8d: 4 L nov^2 + ...); "
                                 "the eris GEMM executes about half of its share by symmetry, so value can exceed the FP64 peak"},

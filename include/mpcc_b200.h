@@ -101,6 +101,15 @@ int mpccb_updated_amps_host(mpccb_ctx* ctx, const double* t1_host, double* t1_ne
 int mpccb_t2_to_aibj(mpccb_ctx* ctx, double* out_dev);
 /* lower-triangle rows [a_begin*o, a_end*o) of the t2 buffer read as an (nov,nov) matrix */
 int mpccb_pack_tril_rows(mpccb_ctx* ctx, double* seg_dev);
+/* Several ranks: switch the t2 part of the DIIS vector from row-owned (rank = owner of the first virtual index;
+ * contiguous but (2P-1):1 unbalanced) to column-owned (rank = owner of the second virtual index, read from the
+ * local slab through t2[A,B,I,J] = t2[B,A,J,I]; balanced). prefix_dev: na*nvir + 1 device int64, number of packed
+ * elements before local block k = (a - a_begin)*nvir + b (sharding.column_owned_prefix). Affects
+ * mpccb_pack_tril_rows and mpccb_diis_push; NULL switches back. */
+int mpccb_bind_diis_columns(mpccb_ctx* ctx, const long long* prefix_dev);
+/* column-owned t2 part -> its positions in a full reference-order packed vector (nov(nov+1)/2 doubles, which the
+ * caller zero-fills and sums over the ranks): the host-facing gather of dfrmpcc_lowlevel.py:162-168's vector */
+int mpccb_diis_scatter_tril(mpccb_ctx* ctx, const double* seg_dev, double* full_packed_dev);
 /* packed (nov(nov+1)/2) -> symmetric (nov,nov) -> (o,v,o,v) -> transpose(0,2,1,3): out (o,o,v,v) */
 int mpccb_unpack_oovv(mpccb_ctx* ctx, const double* packed_dev, double* out_dev);
 

@@ -48,6 +48,8 @@ SIGNATURES = {
     "mpccb_updated_amps_host": (c_int, [c_void_p, c_void_p, c_void_p, c_double_p, c_double_p]),
     "mpccb_t2_to_aibj": (c_int, [c_void_p, c_void_p]),
     "mpccb_pack_tril_rows": (c_int, [c_void_p, c_void_p]),
+    "mpccb_bind_diis_columns": (c_int, [c_void_p, c_void_p]),
+    "mpccb_diis_scatter_tril": (c_int, [c_void_p, c_void_p, c_void_p]),
     "mpccb_unpack_oovv": (c_int, [c_void_p, c_void_p, c_void_p]),
     "mpccb_diis_push": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                 ctypes.POINTER(c_void_p), c_int, c_int, c_int, c_int, c_void_p]),

@@ -33,6 +33,8 @@ typedef GemmCfg<2, 4, 8, 4, false, false> CfgBigRR;   // 128 x 128, both row-maj
 typedef GemmCfg<2, 4, 4, 4, false, false> CfgM64RR;   // 64 x 128
 }  // namespace
 
+constexpr int DIIS_COLS_GRID = 148 * 16;
+
 struct mpccb_ctx {
   int o, v, L, device, a_begin, a_end, na, ldk;
   i64 nov;
@@ -43,6 +45,7 @@ struct mpccb_ctx {
   // bound tensors
   const double *Loo, *Lov, *Lvv, *foo, *fvv, *eo, *ev;
   double* T;
+  const long long* diis_prefix;   // column-owned DIIS vector: packed elements before local block k (na*v + 1 entries)
   unsigned char* ws;
   size_t ws_bytes;
   // workspace carve-up (doubles)
@@ -316,7 +319,8 @@ i64 carve_workspace(mpccb_ctx* c, unsigned char* base) {
   mx(splitk_scratch((int)na, (int)o, (int)(o * L), 128, 64));  // S7
   mx(splitk_scratch((int)v, (int)o, (int)(na * L), 128, 64));  // G2
   mx(splitk_scratch((int)o, (int)o, (int)(na * L), 128, 64));  // S8
-  mx((na * o + 1) * 7);                                        // DIIS dot partials
+  mx((na * o + 1) * 7);                                        // DIIS dot partials (row-owned vector)
+  mx((DIIS_COLS_GRID + 1) * 7);                                //   "   (column-owned vector)
   c->P_count = p;
   c->P = w.take(p);
   c->OmRep = w.take(nov);
@@ -922,11 +926,42 @@ extern "C" int mpccb_t2_to_aibj(mpccb_ctx* c, double* out_dev) {
   return 0;
 }
 
+namespace {
+int launch_diis_cols(mpccb_ctx* c, const double* t1_new_dev, const double* xprev_dev, double* x_slot_dev,
+                     double* e_slot_dev, const DiisPtrs& ep, int nd, int slot, int first_call, int count_t1,
+                     double* scatter_to, int* grid_out) {
+  const i64 nblocks = (i64)c->na * c->v;
+  const int G = (int)std::min<i64>(nblocks, DIIS_COLS_GRID);
+  if ((i64)(G + 1) * 7 > c->P_count) return fail(c, "DIIS partial scratch too small");
+  k_diis_push_cols<<<G + 1, 256, 0, c->stream>>>(c->T, t1_new_dev, xprev_dev, x_slot_dev, e_slot_dev, ep, nd, slot,
+                                                 first_call, count_t1, c->o, c->v, c->a_begin, c->na,
+                                                 reinterpret_cast<const i64*>(c->diis_prefix), G, c->P, scatter_to);
+  LAUNCH_OK(c, "k_diis_push_cols");
+  if (grid_out) *grid_out = G + 1;
+  return 0;
+}
+}  // namespace
+
+extern "C" int mpccb_bind_diis_columns(mpccb_ctx* c, const long long* prefix_dev) {
+  c->diis_prefix = prefix_dev;
+  return 0;
+}
+
 extern "C" int mpccb_pack_tril_rows(mpccb_ctx* c, double* seg_dev) {
   if (!c->T) return fail(c, "t2 buffer not bound");
+  if (c->diis_prefix) {                      // column-owned order; seg_dev is the t2 part (vector + nov)
+    DiisPtrs ep = {};
+    return launch_diis_cols(c, nullptr, nullptr, seg_dev - c->nov, nullptr, ep, 0, 0, 1, 0, nullptr, nullptr);
+  }
   k_pack_rows<<<c->na * c->o, 256, 0, c->stream>>>(c->T, seg_dev, c->nov, (i64)c->a_begin * c->o);
   LAUNCH_OK(c, "k_pack_rows");
   return 0;
+}
+
+extern "C" int mpccb_diis_scatter_tril(mpccb_ctx* c, const double* seg_dev, double* full_packed_dev) {
+  if (!c->diis_prefix) return fail(c, "the DIIS vector is row-owned: its segments are contiguous, no scatter needed");
+  DiisPtrs ep = {};
+  return launch_diis_cols(c, nullptr, seg_dev - c->nov, nullptr, nullptr, ep, 0, 0, 0, 0, full_packed_dev, nullptr);
 }
 
 extern "C" int mpccb_unpack_oovv(mpccb_ctx* c, const double* packed_dev, double* out_dev) {
@@ -943,6 +978,18 @@ extern "C" int mpccb_diis_push(mpccb_ctx* c, const double* t1_new_dev, const dou
   if (!c->T) return fail(c, "t2 buffer not bound");
   if (nd < 0 || nd > 6 || slot < 0 || slot > 5) return fail(c, "bad DIIS slot/nd");
   StageTimer timer(c, ST_DIIS_PUSH);
+  if (c->diis_prefix) {
+    DiisPtrs ep;
+    for (int k = 0; k < 6; ++k) ep.e[k] = (k < nd && e_list_dev) ? e_list_dev[k] : nullptr;
+    int grid = 0;
+    if (launch_diis_cols(c, t1_new_dev, xprev_dev, x_slot_dev, e_slot_dev, ep, nd, slot, first_call, count_t1,
+                         nullptr, &grid)) return 1;
+    if (!first_call) {
+      k_final_sums_strided<<<1, 256, 0, c->stream>>>(c->P, dots_dev, grid, 7, nd);
+      LAUNCH_OK(c, "k_final_sums_strided");
+    }
+    return 0;
+  }
   const int nrows = c->na * c->o;
   const int nblk = nrows + 1;
   // partial sums live in the (idle) split-K scratch

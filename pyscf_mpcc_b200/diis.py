@@ -165,11 +165,8 @@ class AmplitudeVector:
         (the packed t2 segments are all-gathered; the t1 part is replicated)."""
         ll = self.solver
         v = self.packed_device()
-        if ll.world_size > 1:
-            from . import sharding
-            lens = [sharding.local_vector_length(ll.nocc, ll.nvir, *sharding.slab_bounds(ll.nvir, ll.world_size, r))
-                    - ll.nov for r in range(ll.world_size)]
-            v = torch.cat([v[:ll.nov], ll._gather_flat(v[ll.nov:], lens)])
+        if ll.world_size > 1 or ll._diis_columns:
+            v = torch.cat([v[:ll.nov], ll._gather_packed(v[ll.nov:])])
         ll._sync()
         return v.cpu().numpy()
 

@@ -64,8 +64,7 @@ class DeviceT2:
             slab = self._local_device()                      # (na, o, v, o)
             return ll._gather_rows(slab.reshape(ll._na, -1), v).reshape(v, o, v, o).cpu().numpy()
         seg = self.packed                                    # local packed rows of the lower triangle
-        full = ll._gather_flat(seg, [sharding.local_vector_length(o, v, *sharding.slab_bounds(v, ll.world_size, r))
-                                     - ll.nov for r in range(ll.world_size)])
+        full = ll._gather_packed(seg)
         out = torch.empty((o, o, v, v), dtype=torch.float64, device=ll.device)
         ll._ctx.call("mpccb_unpack_oovv", full.data_ptr(), out.data_ptr())
         ll._sync()
@@ -89,8 +88,9 @@ class DeviceT2:
             return self._local_device().cpu().numpy()
         if ll.world_size > 1:
             raise RuntimeError("the (o,o,v,v) form of a sharded vector needs the collective numpy()")
+        packed = ll._gather_packed(self.packed) if ll._diis_columns else self.packed
         out = torch.empty((o, o, v, v), dtype=torch.float64, device=ll.device)
-        ll._ctx.call("mpccb_unpack_oovv", self.packed.data_ptr(), out.data_ptr())
+        ll._ctx.call("mpccb_unpack_oovv", packed.data_ptr(), out.data_ptr())
         ll._sync()
         return out.cpu().numpy()
 
@@ -103,7 +103,7 @@ class MPCC_LL:
     """GPU-resident equivalent of ``pyscf.mpcc.dfrmpcc_lowlevel.MPCC_LL``."""
 
     def __init__(self, mf=None, *, blocks=None, device=None, group=None, use_tma=True, t2_wide_tiles=None, t2_unfused=None, yvo_split=None,
-                 jk_exchange=None, t2_sym=None):
+                 jk_exchange=None, t2_sym=None, slabs=None, diis_layout=None):
         """``MPCC_LL(mf)`` as in the reference (:7-43). Extensions (keyword only):
 
         blocks : (Loo, Lov, Lvv, foo, fvv, mo_energy) numpy arrays or CUDA tensors
@@ -111,6 +111,12 @@ class MPCC_LL:
         device : torch device (default ``cuda:<LOCAL_RANK or 0>``).
         group  : torch.distributed process group to shard the doubles over
                  (default: the WORLD group if torch.distributed is initialised).
+        slabs  : how the virtual index is split over the ranks: "equal" (default), "balanced" (widths from the
+                 cost model ``sharding.balanced_bounds``; measured slower) or an explicit list
+                 of world_size + 1 bounds.
+        diis_layout : t2 part of the DIIS vector. "columns" (default with several ranks: each rank keeps the packed elements whose SECOND
+                 virtual index is in its slab — 1/P of the vector each) or "rows" (contiguous reference-order
+                 segments, (2P-1):1 unbalanced; the only form on one rank).
         """
         if not torch.cuda.is_available():
             raise RuntimeError("pyscf_mpcc_b200 needs a CUDA device (B200, sm_100a); there is no CPU path")
@@ -158,12 +164,36 @@ class MPCC_LL:
         o, v, L = self.nocc, self.nvir, self.naux
 
         # --- native context, workspace, device buffers (torch owns the memory) ---
-        self._a_begin, self._a_end = sharding.slab_bounds(v, self.world_size, self.rank)
+        if slabs is None:
+            slabs = os.environ.get("MPCC_SLABS", "equal")
+        if isinstance(slabs, str):
+            if slabs not in ("balanced", "equal"):
+                raise ValueError(f"slabs={slabs!r}")
+            self._bounds = (sharding.balanced_bounds(o, v, L, self.world_size) if slabs == "balanced" else
+                            [sharding.slab_bounds(v, self.world_size, r)[0] for r in range(self.world_size)] + [v])
+        else:
+            self._bounds = [int(b) for b in slabs]
+            if (len(self._bounds) != self.world_size + 1 or self._bounds[0] != 0 or self._bounds[-1] != v
+                    or any(hi <= lo for lo, hi in zip(self._bounds[:-1], self._bounds[1:]))):
+                raise ValueError(f"slabs={slabs!r}: need {self.world_size + 1} increasing bounds from 0 to nvir={v}")
+        self._a_begin, self._a_end = self._bounds[self.rank], self._bounds[self.rank + 1]
         self._na = self._a_end - self._a_begin
         self._count_t1 = (self.rank == 0)
         self._vec_len_local = sharding.local_vector_length(o, v, self._a_begin, self._a_end)
+        if diis_layout is None:
+            diis_layout = os.environ.get("MPCC_DIIS_LAYOUT", "columns" if self.world_size > 1 else "rows")
+        if diis_layout not in ("columns", "rows"):
+            raise ValueError(f"diis_layout={diis_layout!r}")
+        self._diis_columns = diis_layout == "columns"
+        self._diis_prefix = None
+        if self._diis_columns:
+            prefix = sharding.column_owned_prefix(o, v, self._a_begin, self._a_end)
+            self._vec_len_local = self.nov + int(prefix[-1])
+            self._diis_prefix = torch.from_numpy(prefix).to(self.device)
         self._ctx = _cabi.Context(o, v, L, self._a_begin, self._a_end, self.device.index)
         self._ctx.call("mpccb_set_option", b"tma", int(bool(use_tma)))
+        if self._diis_columns:
+            self._ctx.call("mpccb_bind_diis_columns", self._diis_prefix.data_ptr())
         if t2_wide_tiles is None and os.environ.get("MPCC_T2_WIDE_TILES"):
             t2_wide_tiles = os.environ["MPCC_T2_WIDE_TILES"] != "0"
         if t2_sym is None and os.environ.get("MPCC_T2_SYM"):
@@ -259,10 +289,24 @@ class MPCC_LL:
         """All-gather of the per-rank (na_r, width) row slabs into (nvir, width)."""
         width = slab.shape[1]
         lens = []
-        for r in range(self.world_size):
-            a0, a1 = sharding.slab_bounds(nvir, self.world_size, r)
+        for a0, a1 in zip(self._bounds[:-1], self._bounds[1:]):
             lens.append((a1 - a0) * width)
         return self._gather_flat(slab.reshape(-1), lens).reshape(nvir, width)
+
+    def _gather_packed(self, seg):
+        """The reference-order packed lower triangle (nov(nov+1)/2 doubles, on every rank) from the per-rank t2
+        parts of a DIIS vector. Collective; host-facing paths only (``numpy()`` of a vector / an (o,o,v,v) t2)."""
+        if not self._diis_columns:
+            lens = [sharding.local_vector_length(self.nocc, self.nvir, a0, a1) - self.nov
+                    for a0, a1 in zip(self._bounds[:-1], self._bounds[1:])]
+            return self._gather_flat(seg, lens)
+        full = torch.zeros(self.nov * (self.nov + 1) // 2, dtype=torch.float64, device=self.device)
+        self._bind_stream()
+        self._ctx.call("mpccb_diis_scatter_tril", seg.data_ptr(), full.data_ptr())
+        self._sync()
+        if self.world_size > 1:
+            torch.distributed.all_reduce(full, group=self.group)     # disjoint supports: a sum of one value and zeros
+        return full
 
     # host-readable views of the device-resident tensors (reference attribute names, :66-69,:36-37)
     Loo = property(lambda self: self._host_attr("Loo"))
@@ -364,8 +408,7 @@ class MPCC_LL:
         off = ptr - self._ws.data_ptr()
         self._jk_view = self._ws[off:off + count * 8].view(torch.float64)
         self._jk_rows = []
-        for r in range(self.world_size):
-            b0, b1 = sharding.slab_bounds(v, self.world_size, r)
+        for b0, b1 in zip(self._bounds[:-1], self._bounds[1:]):
             self._jk_rows.append((b0 * o * ldk, b1 * o * ldk))
         self._equal_slabs = len({hi - lo for lo, hi in self._jk_rows}) == 1
         self._jk_mode = "nccl"
@@ -376,7 +419,7 @@ class MPCC_LL:
         the buffer of the rank that owns b. All ranks agree; on failure everyone keeps private buffers."""
         dist = torch.distributed
         o, v = self.nocc, self.nvir
-        bounds = [sharding.slab_bounds(v, self.world_size, r)[0] for r in range(self.world_size)] + [v]
+        bounds = self._bounds
         n_max = max(bounds[r + 1] - bounds[r] for r in range(self.world_size)) * v * o * o
         ok, buf, hdl = 0, None, None
         try:

@@ -47,6 +47,17 @@ def _worker(rank, world, port, out):
     d = torch.tensor([float(seg @ seg) + (float(vec[:nov] @ vec[:nov]) if rank == 0 else 0.0)], dtype=torch.float64)
     dist.all_reduce(d)
     ok = ok and abs(d.item() - float(vec @ vec)) < 1e-10 * float(vec @ vec)
+    # column-owned DIIS vector (the multi-GPU default): elements whose second virtual index is in the slab, read
+    # from the local [a,b,i,j] slab through t2[A,B,I,J] = t2[B,A,J,I]; same dot after the all-reduce
+    loc, ref = sharding.column_owned_positions(o, v, a0, a1)
+    segc = m_local.reshape(-1)[loc]
+    ok = ok and np.allclose(segc, vec[nov + ref], rtol=0, atol=1e-14)
+    ok = ok and len(segc) == int(sharding.column_owned_prefix(o, v, a0, a1)[-1])
+    d = torch.tensor([float(segc @ segc) + (float(vec[:nov] @ vec[:nov]) if rank == 0 else 0.0), float(len(segc))],
+                     dtype=torch.float64)
+    dist.all_reduce(d)
+    ok = ok and abs(d[0].item() - float(vec @ vec)) < 1e-10 * float(vec @ vec)
+    ok = ok and int(d[1].item()) == nov * (nov + 1) // 2
     out[rank] = bool(ok)
     dist.destroy_process_group()
 

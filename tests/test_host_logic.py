@@ -178,3 +178,57 @@ def test_mirror_scheme_covers_every_block_exactly_once(nranks, v):
             assert (f0 & 1) == (1 if qa != qb else int(b >= a)) and bool(f0 & 2) == (qa == qb and b > a)
     if v % nranks == 0 and (v // nranks) % 2 == 0:
         assert max(work) - min(work) <= v // nranks          # balanced: P/2 slab-blocks each (+- the diagonal)
+
+
+@pytest.mark.parametrize("o,v,L,p", [(64, 512, 1536, 2), (64, 512, 1536, 8), (80, 848, 2224, 4), (32, 256, 768, 8),
+                                     (5, 13, 40, 2), (3, 7, 11, 7)])
+def test_balanced_bounds(o, v, L, p):
+    """Cost-balanced slabs: a partition of [0, nvir) in tile granularity whose modelled spread is no worse than
+    the equal split's (and wider slabs come first, since packed rows get longer with a)."""
+    b = sharding.balanced_bounds(o, v, L, p)
+    assert len(b) == p + 1 and b[0] == 0 and b[-1] == v
+    widths = [hi - lo for lo, hi in zip(b[:-1], b[1:])]
+    assert all(w >= 1 for w in widths)
+    equal = [sharding.slab_bounds(v, p, r)[0] for r in range(p)] + [v]
+    if b != equal:
+        gran = 128 // o if 128 % o == 0 else 1
+        assert all(x % gran == 0 for x in b[:-1])
+        assert widths[0] >= widths[-1]
+        spread = lambda bb: max(sharding.modelled_cost(o, v, L, bb)) / (sum(sharding.modelled_cost(o, v, L, bb)) / p)
+        assert spread(b) <= spread(equal) + 1e-12
+    assert sharding.balanced_bounds(o, v, L, p, diis=False) == equal
+    assert sharding.balanced_bounds(o, v, L, 1) == [0, v]
+
+
+@pytest.mark.parametrize("o,v,p", [(3, 7, 2), (4, 10, 3), (5, 13, 4), (8, 12, 2), (6, 5, 2), (2, 9, 8)])
+def test_column_owned_diis_vector_is_a_partition_of_the_packed_triangle(o, v, p):
+    """Column ownership (mpccb_bind_diis_columns): over the ranks every packed element appears exactly once, the
+    values read from the local slabs are the reference vector's, and the shares are close to 1/P."""
+    rng = np.random.default_rng(o * 100 + v)
+    nov = o * v
+    m = rng.standard_normal((nov, nov))
+    m = m + m.T                                                   # (ai|bj)-type symmetry: T[a,b,i,j] = T[b,a,j,i]
+    T = m.reshape(v, o, v, o).transpose(0, 2, 1, 3).copy()         # [a,b,i,j] buffer
+    ref_vec = T.reshape(nov, nov)[np.tril_indices(nov)]           # dfrmpcc_lowlevel.py:162-168 on that buffer
+    seen = np.zeros(ref_vec.size, dtype=int)
+    sizes = []
+    for r in range(p):
+        b0, b1 = sharding.slab_bounds(v, p, r)
+        prefix = sharding.column_owned_prefix(o, v, b0, b1)
+        loc, ref = sharding.column_owned_positions(o, v, b0, b1)
+        assert prefix[-1] == loc.size == ref.size
+        seen[ref] += 1
+        slab = T[b0:b1].reshape(-1)
+        assert np.array_equal(slab[loc], ref_vec[ref])
+        sizes.append(loc.size)
+    assert np.all(seen == 1)
+    assert sum(sizes) == nov * (nov + 1) // 2
+
+
+def test_column_owned_shares_are_balanced_at_the_target_shape():
+    o, v = 64, 512
+    for p in (2, 8):
+        sizes = [int(sharding.column_owned_prefix(o, v, *sharding.slab_bounds(v, p, r))[-1]) for r in range(p)]
+        assert max(sizes) / (sum(sizes) / p) < 1.003
+        rows = [sharding.local_vector_length(o, v, *sharding.slab_bounds(v, p, r)) - o * v for r in range(p)]
+        assert max(rows) / (sum(rows) / p) > 1.4                 # what the row-owned split costs

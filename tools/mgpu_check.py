@@ -31,39 +31,62 @@ def main():
         o, v, L = (int(x) for x in g["shape"])
         if v < world:
             continue
-        ll = MPCC_LL(SyntheticMF(o, v, L, seed=0, scale=float(g["scale"])), device=dev)
-        ll.verbose_print = False
-        e = ll.kernel()
-        tr = np.array(ll.history)
-        t2 = np.asarray(ll.t2)                                  # collective: all-gather + symmetric unpack
-        ok = (ll.iterations == int(g["iterations"])
-              and np.abs(tr[:, 1] - g["trace_dE"]).max() <= E_TOL
-              and np.allclose(tr[:, 2], g["trace_res"], rtol=1e-6, atol=1e-12)
-              and np.abs(ll.t1 - g["final_t1"]).max() <= AMP_TOL
-              and t2.shape == (o, o, v, v)
-              and np.abs(t2.reshape(-1)[::STRIDE] - g["final_t2_samples"]).max() <= AMP_TOL
-              and abs(np.linalg.norm(t2) - g["final_t2_norm"]) <= 1e-9)
-        # one residual evaluation: gathered (v,o,v,o) t2 and the flat DIIS vector
-        ll.t1 = g["kat_rand_t1_in"]
-        res, dE, t1n, t2h = ll.updated_amps()
-        t2a = np.asarray(t2h)
-        vec = ll.amplitudes_to_vector(t1n, t2h).numpy()
-        ok = (ok and abs(dE - g["kat_rand_dE"]) <= E_TOL and np.abs(t1n - g["kat_rand_t1_new"]).max() <= AMP_TOL
-              and np.abs(t2a.reshape(-1)[::STRIDE] - g["kat_rand_t2_samples"]).max() <= AMP_TOL
-              and np.abs(vec[::STRIDE] - g["kat_rand_vec_samples"]).max() <= AMP_TOL
-              and abs(np.linalg.norm(vec) - g["kat_rand_vec_norm"]) <= 1e-9)
-        flag = torch.tensor([0 if ok else 1], device=dev)
-        dist.all_reduce(flag)
-        if rank == 0:
-            print(f"{os.path.basename(path)} world={world} jk={ll._jk_mode} its={ll.iterations} E={e:.12e} "
-                  f"{'OK' if flag.item() == 0 else 'MISMATCH'}", flush=True)
-        bad += int(flag.item())
-        del ll
+        for slabs in (None, uneven_bounds(v, world)):
+            if slabs is not None and slabs == even_bounds(v, world):
+                continue
+            ll = MPCC_LL(SyntheticMF(o, v, L, seed=0, scale=float(g["scale"])), device=dev, slabs=slabs)
+            ll.verbose_print = False
+            e = ll.kernel()
+            tr = np.array(ll.history)
+            t2 = np.asarray(ll.t2)                                  # collective: all-gather + symmetric unpack
+            ok = (ll.iterations == int(g["iterations"])
+                  and np.abs(tr[:, 1] - g["trace_dE"]).max() <= E_TOL
+                  and np.allclose(tr[:, 2], g["trace_res"], rtol=1e-6, atol=1e-12)
+                  and np.abs(ll.t1 - g["final_t1"]).max() <= AMP_TOL
+                  and t2.shape == (o, o, v, v)
+                  and np.abs(t2.reshape(-1)[::STRIDE] - g["final_t2_samples"]).max() <= AMP_TOL
+                  and abs(np.linalg.norm(t2) - g["final_t2_norm"]) <= 1e-9)
+            # one residual evaluation: gathered (v,o,v,o) t2 and the flat DIIS vector
+            ll.t1 = g["kat_rand_t1_in"]
+            res, dE, t1n, t2h = ll.updated_amps()
+            t2a = np.asarray(t2h)
+            vec = ll.amplitudes_to_vector(t1n, t2h).numpy()
+            ok = (ok and abs(dE - g["kat_rand_dE"]) <= E_TOL and np.abs(t1n - g["kat_rand_t1_new"]).max() <= AMP_TOL
+                  and np.abs(t2a.reshape(-1)[::STRIDE] - g["kat_rand_t2_samples"]).max() <= AMP_TOL
+                  and np.abs(vec[::STRIDE] - g["kat_rand_vec_samples"]).max() <= AMP_TOL
+                  and abs(np.linalg.norm(vec) - g["kat_rand_vec_norm"]) <= 1e-9)
+            flag = torch.tensor([0 if ok else 1], device=dev)
+            dist.all_reduce(flag)
+            if rank == 0:
+                print(f"{os.path.basename(path)} world={world} slabs={ll._bounds} jk={ll._jk_mode} its={ll.iterations} E={e:.12e} "
+                      f"{'OK' if flag.item() == 0 else 'MISMATCH'}", flush=True)
+            bad += int(flag.item())
+            del ll
     if "--full" in sys.argv:
         bad += full_shape(rank, world, dev)
     dist.destroy_process_group()
     if bad:
         sys.exit(1)
+
+
+def even_bounds(v, world):
+    from pyscf_mpcc_b200 import sharding
+    return [sharding.slab_bounds(v, world, r)[0] for r in range(world)] + [v]
+
+
+def uneven_bounds(v, world):
+    """Equal split with one index moved from each of the last ranks to the first ones (exercises the
+    unequal-slab paths that sharding.balanced_bounds produces at large shapes)."""
+    b = even_bounds(v, world)
+    w = [hi - lo for lo, hi in zip(b[:-1], b[1:])]
+    for r in range(world // 2):
+        if w[-1 - r] > 1:
+            w[r] += 1
+            w[-1 - r] -= 1
+    out = [0]
+    for x in w:
+        out.append(out[-1] + x)
+    return out
 
 
 def full_shape(rank, world, dev):
