@@ -39,7 +39,8 @@ struct TmaCfg {
   static constexpr int STAGE_BYTES = (TMA_TM + TN) * TMA_TK * 8;
   static constexpr int RING_BYTES = TMA_STAGES * STAGE_BYTES;
   static constexpr int STAGING_BYTES = 8 * TMA_TM * (TN + 1);      // fused-t2 epilogue staging (aliases the ring)
-  static constexpr int AREA_EPI1 = STAGING_BYTES > RING_BYTES ? STAGING_BYTES : RING_BYTES;
+  static constexpr int FLAG_BYTES = TMA_TM * TN;                   // one byte per (a,b) block of the tile (nocc = 1)
+  static constexpr int AREA_EPI1 = STAGING_BYTES + FLAG_BYTES > RING_BYTES ? STAGING_BYTES + FLAG_BYTES : RING_BYTES;
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -85,6 +86,44 @@ __device__ __forceinline__ int rho(int g) { return ((g & 3) << 1) | (g >> 2); }
 
 // 8-byte element (row, k) of a [rows][16] swizzle-128B tile, as a double index
 __device__ __forceinline__ int swz(int row, int k) { return row * 16 + ((((k >> 1) ^ (row & 7)) << 1) | (k & 1)); }
+
+// x / y without the compiler's special-case branch: MUFU.RCP64H seed (about 20 bits), Newton steps, one
+// residual correction of the quotient. Within 1 ulp of the IEEE quotient for normal y (orbital-energy
+// denominators); branch-free, so that many independent divisions interleave in one thread.
+__device__ __forceinline__ double fast_div(double x, double y) {
+  double r;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(y));
+  double e = fma(-y, r, 1.0);
+  r = fma(r, e, r);
+  e = fma(-y, r, 1.0);
+  r = fma(r, e, r);
+  e = fma(-y, r, 1.0);
+  r = fma(r, e, r);
+  double q = x * r;
+  const double rem = fma(-q, y, x);
+  return fma(rem, r, q);
+}
+
+// N independent quotients with every Newton step issued for all of them before the next one
+template <int N>
+__device__ __forceinline__ void fast_div_batch(const double* x, const double* y, double* q) {
+  double r[N], e[N];
+#pragma unroll
+  for (int u = 0; u < N; ++u) asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r[u]) : "d"(y[u]));
+#pragma unroll
+  for (int it = 0; it < 2; ++it) {
+#pragma unroll
+    for (int u = 0; u < N; ++u) e[u] = fma(-y[u], r[u], 1.0);
+#pragma unroll
+    for (int u = 0; u < N; ++u) r[u] = fma(r[u], e[u], r[u]);
+  }
+#pragma unroll
+  for (int u = 0; u < N; ++u) q[u] = x[u] * r[u];
+#pragma unroll
+  for (int u = 0; u < N; ++u) e[u] = fma(-q[u], y[u], x[u]);
+#pragma unroll
+  for (int u = 0; u < N; ++u) q[u] = fma(e[u], r[u], q[u]);
+}
 
 struct TmaGemmParams {
   int M, N;              // valid rows of A / B for this launch
@@ -238,63 +277,123 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
           for (int c = 0; c < 2; ++c)
             S[(wm * 32 + i * 8 + rho(g)) * PITCH + wn * 32 + j * 8 + rho(2 * tig + c)] = acc[i][j][c];
     }
+    // which (a,b) blocks of the tile this CTA produces (bit 0) and mirrors (bit 1): the mirror rule, once per block
+    unsigned char* flags = smem_raw + Cfg::STAGING_BYTES;
+    for (int q = threadIdx.x; q < t2p.n_a * t2p.n_b; q += Cfg::THREADS) {
+      const int al = q / t2p.n_b, bl = q - al * t2p.n_b;
+      const int a = t2p.a_begin + tm * t2p.n_a + al, b = tn * t2p.n_b + bl;
+      unsigned char f = 0;
+      if (a < t2p.a_end && b < t2p.v) {
+        bool mirror; int s;
+        const bool comp = sym_compute(sym, a, b, mirror, s);
+        f = (comp ? 1 : 0) | (mirror ? 2 : 0);
+      }
+      flags[q] = f;
+    }
     __syncthreads();
     const int o = t2p.o;
-    const int nwarps = Cfg::WARPS;
+    constexpr int nwarps = Cfg::WARPS;
+    constexpr int RPW = TMA_TM / nwarps;          // tile rows per warp
+    constexpr int CPL = Cfg::TN / 32;             // tile columns per lane
     const int mslab = (t2p.a_end - t2p.a_begin) * o;
-    for (int r = warp; r < p.tm_eff; r += nwarps) {
-      const int al = r / o, i = r - al * o;
-      const int a = t2p.a_begin + tm * t2p.n_a + al;
-      if (a >= t2p.a_end) break;
-      const double dai = t2p.ev[a] - t2p.eo[i];
-      double fsum = 0.0;
-      for (int bl = 0; bl < t2p.n_b; ++bl) {
-        const int b = tn * t2p.n_b + bl;
-        if (b >= t2p.v) break;
-        bool mirror; int s;
-        if (!sym_compute(sym, a, b, mirror, s)) continue;      // produced by the CTA that owns the mirror block
-        const double evb = t2p.ev[b];
-        double* trow = t2p.T + (((i64)(a - t2p.a_begin) * t2p.v + b) * o + i) * o;
-        const double* frow = t2p.Fvo + (i64)b * o;
-        for (int j = lane; j < o; j += 32) {
-          const double e1 = S[r * PITCH + bl * o + j];
-          const double e2 = S[(al * o + j) * PITCH + bl * o + i];
-          const double den = -dai - (evb - t2p.eo[j]);
-          const double tv = (2.0 * e1 - e2) / den;
-          trow[j] = tv;
-          fsum += tv * frow[j];
+    const i64 nov = (i64)t2p.v * o;
+
+    // phase 1: t2 = (2 e - e^x) / D for the whole tile, branch-free, RPW x CPL independent divisions per thread.
+    // The FP64 pipe is shared with the sibling CTA's DMMAs, so every dependent FP64 instruction waits long;
+    // a row-at-a-time loop (one division chain per thread) made this epilogue as long as the K loop.
+    // x / o for x < 2^16 without a division (no control flow inside the batches): umulhi(x, floor(2^32/o) + 1)
+    const unsigned magic = o > 1 ? 0xFFFFFFFFu / (unsigned)o + 1u : 0u;
+    auto div_o = [&](int x) -> int { return o > 1 ? (int)__umulhi((unsigned)x, magic) : x; };
+    int cbl[CPL], cj[CPL], cok[CPL];
+    double cden[CPL], cfvo[CPL];
+    i64 coloff[CPL];
+#pragma unroll
+    for (int cc = 0; cc < CPL; ++cc) {
+      const int c = lane + cc * 32;
+      const bool in = c < p.tn_eff;
+      const int bl = in ? div_o(c) : 0;
+      const int j = in ? c - bl * o : 0;
+      const int b = tn * t2p.n_b + bl;
+      cok[cc] = in && b < t2p.v;
+      cbl[cc] = bl; cj[cc] = j;
+      cden[cc] = t2p.ev[cok[cc] ? b : 0] - t2p.eo[j];
+      coloff[cc] = (i64)b * o * o + j;
+      cfvo[cc] = cok[cc] ? t2p.Fvo[(i64)b * o + j] : 0.0;
+    }
+    double tv[RPW][CPL];
+    constexpr int RB = 8 / CPL;                   // rows per batch: 8 divisions in lockstep
+#pragma unroll
+    for (int r0 = 0; r0 < RPW; r0 += RB) {
+      double num[RB][CPL], den[RB][CPL];
+      bool mine[RB][CPL];
+      i64 rowoff[RB];
+      int omp[RB];
+#pragma unroll
+      for (int u = 0; u < RB; ++u) {
+        const int r = warp + (r0 + u) * nwarps;
+        const bool in = r < p.tm_eff;
+        const int al = in ? div_o(r) : 0;
+        const int i = in ? r - al * o : 0;
+        const int a = t2p.a_begin + tm * t2p.n_a + al;
+        const bool rok = in && a < t2p.a_end;
+        const double dai = t2p.ev[rok ? a : t2p.a_begin] - t2p.eo[i];
+        rowoff[u] = ((i64)(a - t2p.a_begin) * t2p.v * o + i) * o;
+        omp[u] = rok ? (a - t2p.a_begin) * o + i : -1;
+#pragma unroll
+        for (int cc = 0; cc < CPL; ++cc) {
+          const double e1 = S[r * PITCH + lane + cc * 32];
+          const double e2 = S[(al * o + cj[cc]) * PITCH + cbl[cc] * o + i];
+          num[u][cc] = 2.0 * e1 - e2;
+          den[u][cc] = -dai - cden[cc];
+          mine[u][cc] = rok && cok[cc] && (flags[al * t2p.n_b + cbl[cc]] & 1);
         }
       }
-      fsum = warp_sum(fsum);
-      if (lane == 0) t2p.OmP[(i64)tn * mslab + (i64)(a - t2p.a_begin) * o + i] = fsum;
+      double q[RB][CPL];
+      fast_div_batch<RB * CPL>(&num[0][0], &den[0][0], &q[0][0]);
+      // rows (a,i) -> t2[a,b,i,:] straight from the registers (lanes run along j: coalesced) and the row's share
+      // of sum t2 . Fov (:139); blocks produced by the CTA that owns the mirror block stay untouched
+#pragma unroll
+      for (int u = 0; u < RB; ++u) {
+        double fsum = 0.0;
+#pragma unroll
+        for (int cc = 0; cc < CPL; ++cc) {
+          const double x = mine[u][cc] ? q[u][cc] : 0.0;
+          tv[r0 + u][cc] = x;
+          if (mine[u][cc]) t2p.T[rowoff[u] + coloff[cc]] = x;
+          fsum = fma(x, cfvo[cc], fsum);
+        }
+        fsum = warp_sum(fsum);
+        if (lane == 0 && omp[u] >= 0) t2p.OmP[(i64)tn * mslab + omp[u]] = fsum;
+      }
     }
+    // phase 2 (mirror scheme): rows (b,j) of t2[b,a,:,:] = t2[a,b,:,:]^T, lanes along i (coalesced in the target,
+    // which is the local buffer or, over NVLink, the buffer of the rank that owns b). The amplitudes go back into
+    // the staging tile (in place, once every thread has read its exchange partners) to be read column-wise.
     if (sym.enabled) {
-      // mirror pass: rows (b, j) of the blocks t2[b,a,:,:] = t2[a,b,:,:]^T, lanes along i (coalesced in the target)
-      const i64 nov = (i64)t2p.v * o;
+      __syncthreads();
+#pragma unroll
+      for (int rr = 0; rr < RPW; ++rr)
+#pragma unroll
+        for (int cc = 0; cc < CPL; ++cc) S[(warp + rr * nwarps) * PITCH + lane + cc * 32] = tv[rr][cc];
+      __syncthreads();
       for (int rr = warp; rr < t2p.n_b * o; rr += nwarps) {
         const int bl = rr / o, j = rr - bl * o;
         const int b = tn * t2p.n_b + bl;
         if (b >= t2p.v) break;
-        const double dbj = t2p.ev[b] - t2p.eo[j];
+        const int s = sym_owner(sym, b);
         double fsum = 0.0;
         bool any = false;
         for (int al = 0; al < t2p.n_a; ++al) {
           const int a = t2p.a_begin + tm * t2p.n_a + al;
           if (a >= t2p.a_end) break;
-          bool mirror; int s;
-          sym_compute(sym, a, b, mirror, s);
-          if (!mirror) continue;
+          if (!(flags[al * t2p.n_b + bl] & 2)) continue;
           any = true;
-          const double eva = t2p.ev[a];
           double* trow = sym.Tp[s] + (((i64)(b - sym.bounds[s]) * t2p.v + a) * o + j) * o;
           const double* frow = t2p.Fvo + (i64)a * o;
           for (int i = lane; i < o; i += 32) {
-            const double e1 = S[(al * o + i) * PITCH + bl * o + j];
-            const double e2 = S[(al * o + j) * PITCH + bl * o + i];
-            const double den = -(eva - t2p.eo[i]) - dbj;
-            const double tv = (2.0 * e1 - e2) / den;
-            trow[i] = tv;
-            fsum += tv * frow[i];
+            const double x = S[(al * o + i) * PITCH + bl * o + j];
+            trow[i] = x;
+            fsum += x * frow[i];
           }
         }
         fsum = warp_sum(fsum);
