@@ -376,26 +376,47 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
 #pragma unroll
         for (int cc = 0; cc < CPL; ++cc) S[(warp + rr * nwarps) * PITCH + lane + cc * 32] = tv[rr][cc];
       __syncthreads();
-      for (int rr = warp; rr < t2p.n_b * o; rr += nwarps) {
-        const int bl = rr / o, j = rr - bl * o;
+      // thread-fixed mapping again: tile columns rr = warp + k * nwarps are the target rows (b,j); lanes (+32 m)
+      // run over the tile rows (a,i), which are contiguous along i in the target
+      constexpr int MR = Cfg::TN / nwarps;        // target rows per warp
+      constexpr int MC = TMA_TM / 32;             // (a,i) positions per lane
+      i64 mcol[MC];
+      double mfvo[MC];
+      int mal[MC];
+      bool mok[MC];
+#pragma unroll
+      for (int m = 0; m < MC; ++m) {
+        const int c = lane + 32 * m;
+        const bool in = c < p.tm_eff;
+        const int al = in ? div_o(c) : 0;
+        const int i = in ? c - al * o : 0;
+        const int a = t2p.a_begin + tm * t2p.n_a + al;
+        mok[m] = in && a < t2p.a_end;
+        mal[m] = al;
+        mcol[m] = (i64)a * o * o + i;
+        mfvo[m] = mok[m] ? t2p.Fvo[(i64)a * o + i] : 0.0;
+      }
+#pragma unroll
+      for (int k = 0; k < MR; ++k) {
+        const int rr = warp + k * nwarps;
+        const bool in = rr < p.tn_eff;
+        const int bl = in ? div_o(rr) : 0;
+        const int j = in ? rr - bl * o : 0;
         const int b = tn * t2p.n_b + bl;
-        if (b >= t2p.v) break;
-        const int s = sym_owner(sym, b);
+        const bool rok = in && b < t2p.v;
+        const int s = sym_owner(sym, rok ? b : 0);
+        double* tgt = sym.Tp[s] + ((i64)(b - sym.bounds[s]) * t2p.v * o + j) * o;
         double fsum = 0.0;
         bool any = false;
-        for (int al = 0; al < t2p.n_a; ++al) {
-          const int a = t2p.a_begin + tm * t2p.n_a + al;
-          if (a >= t2p.a_end) break;
-          if (!(flags[al * t2p.n_b + bl] & 2)) continue;
-          any = true;
-          double* trow = sym.Tp[s] + (((i64)(b - sym.bounds[s]) * t2p.v + a) * o + j) * o;
-          const double* frow = t2p.Fvo + (i64)a * o;
-          for (int i = lane; i < o; i += 32) {
-            const double x = S[(al * o + i) * PITCH + bl * o + j];
-            trow[i] = x;
-            fsum += x * frow[i];
-          }
+#pragma unroll
+        for (int m = 0; m < MC; ++m) {
+          const bool w = rok && mok[m] && (flags[mal[m] * t2p.n_b + bl] & 2);
+          const double x = S[(lane + 32 * m) * PITCH + rr];
+          if (w) tgt[mcol[m]] = x;
+          fsum = fma(w ? x : 0.0, mfvo[m], fsum);
+          any |= w;
         }
+        any = __any_sync(0xffffffffu, any);
         fsum = warp_sum(fsum);
         if (lane == 0 && any) sym.OmPm[(i64)tm * nov + (i64)b * o + j] = fsum;
       }
