@@ -69,6 +69,9 @@ struct GemmCfg {
   static constexpr size_t MAIN_SMEM = sizeof(double) * 2 * (ASZ + BSZ) + sizeof(i64) * (TM + TN + 4 * TK);
   static_assert((TM * TK) % NTH == 0 && (TN * TK) % NTH == 0, "tile/threads mismatch");
   static_assert(NTH % TK == 0, "a thread keeps one k lane for K-major operands");
+  // 32 x 32 warp tiles fit in 128 registers: two CTAs (16 warps) per SM hide the global -> register -> shared
+  // staging latency that a single 8-warp CTA exposes
+  static constexpr int MIN_CTAS = (MT * NT <= 16 && NTH <= 256) ? 2 : 1;
 };
 
 __device__ __forceinline__ i64 row_offset(const Operand& op, int r) {
@@ -206,7 +209,7 @@ __device__ __forceinline__ void gemm_mainloop(const Operand& A, const Operand& B
 // blockIdx.z selects the K chunk and the output slice).
 // ---------------------------------------------------------------------------
 template <class Cfg>
-__global__ void __launch_bounds__(Cfg::NTH, 1)
+__global__ void __launch_bounds__(Cfg::NTH, Cfg::MIN_CTAS)
 gemm_store_kernel(Operand A, Operand B, Output C, GemmDims d) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   int tm, tn;

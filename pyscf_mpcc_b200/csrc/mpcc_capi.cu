@@ -23,13 +23,13 @@ constexpr int BIG = 1 << 30;
 constexpr int NSM = 148;
 
 // tile configurations of the generic DMMA GEMM (warps m x n, fragments m x n, A K-major?, B K-major?)
-typedef GemmCfg<2, 4, 8, 4, true, true> CfgBigKK;     // 128 x 128
+typedef GemmCfg<4, 4, 4, 4, true, true> CfgBigKK;     // 128 x 128, 16 warps
 typedef GemmCfg<4, 2, 4, 4, true, true> CfgN64KK;     // 128 x 64
 typedef GemmCfg<4, 2, 4, 4, false, false> CfgN64RR;
 typedef GemmCfg<4, 2, 4, 4, true, false> CfgN64KR;
 typedef GemmCfg<4, 2, 4, 4, false, true> CfgN64RK;
-typedef GemmCfg<2, 4, 8, 4, true, false> CfgBigKR;    // 128 x 128, B row-major
-typedef GemmCfg<2, 4, 8, 4, false, false> CfgBigRR;   // 128 x 128, both row-major
+typedef GemmCfg<4, 4, 4, 4, true, false> CfgBigKR;    // 128 x 128, B row-major
+typedef GemmCfg<4, 4, 4, 4, false, false> CfgBigRR;   // 128 x 128, both row-major
 typedef GemmCfg<2, 4, 4, 4, false, false> CfgM64RR;   // 64 x 128
 }  // namespace
 
