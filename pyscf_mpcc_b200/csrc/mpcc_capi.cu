@@ -45,6 +45,10 @@ struct mpccb_ctx {
   // bound tensors
   const double *Loo, *Lov, *Lvv, *foo, *fvv, *eo, *ev;
   double* T;
+  cudaStream_t side;              // second stream: the F2 GEMM runs beside the bandwidth-bound dressing kernel
+  cudaEvent_t ev_fork, ev_join;
+  double* P2;                     // split-K scratch of the side stream
+  i64 P2_count;
   const long long* diis_prefix;   // column-owned DIIS vector: packed elements before local block k (na*v + 1 entries)
   unsigned char* ws;
   size_t ws_bytes;
@@ -323,6 +327,8 @@ i64 carve_workspace(mpccb_ctx* c, unsigned char* base) {
   mx((DIIS_COLS_GRID + 1) * 7);                                //   "   (column-owned vector)
   c->P_count = p;
   c->P = w.take(p);
+  c->P2_count = splitk_scratch((int)v, (int)o, (int)(L * o), 128, 64);
+  c->P2 = w.take(c->P2_count);
   c->OmRep = w.take(nov);
   c->OmLoc = w.take(nov);
   c->OmTot = w.take(nov);
@@ -392,6 +398,11 @@ void mpccb_destroy(mpccb_ctx* ctx) {
     for (int s = 0; s < ST_COUNT; ++s)
       for (cudaEvent_t e : ctx->prof_ev[s]) cudaEventDestroy(e);
     delete[] ctx->prof_ev;
+  }
+  if (ctx->side) {
+    cudaStreamDestroy(ctx->side);
+    cudaEventDestroy(ctx->ev_fork);
+    cudaEventDestroy(ctx->ev_join);
   }
   delete ctx;
 }
@@ -573,6 +584,28 @@ extern "C" int mpccb_dress(mpccb_ctx* c, const double* t1_dev) {
     if (na >= 96) { if (launch_gemm<CfgBigKK>(c, "XT|JT", A, B, C, 2 * L * o, na, o, 1, nullptr)) return 1; }
     else          { if (launch_gemm<CfgN64KK>(c, "XT|JT", A, B, C, 2 * L * o, na, o, 1, nullptr)) return 1; }
   }
+  // :133 second half   F2[b][j] = sum_{(L,i)} Lov[(L,i)][b] Xoo[(L,i)][j]      (replicated)
+  // Needs only Xoo and is compute-bound, while k_dress_finalize is bound by HBM (one rank) or by the NVLink stores
+  // of the JK exchange (several ranks): it runs on a side stream next to it.
+  if (!c->side) {
+    CUDA_OK(c, cudaStreamCreateWithFlags(&c->side, cudaStreamNonBlocking));
+    CUDA_OK(c, cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+    CUDA_OK(c, cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
+  }
+  CUDA_OK(c, cudaEventRecord(c->ev_fork, c->stream));
+  CUDA_OK(c, cudaStreamWaitEvent(c->side, c->ev_fork, 0));
+  {
+    cudaStream_t main_stream = c->stream;
+    double* main_P = c->P;
+    const i64 main_P_count = c->P_count;
+    c->stream = c->side; c->P = c->P2; c->P_count = c->P2_count;
+    Operand A = flat_operand(c->Lov, v, 1, v);
+    Operand B = flat_operand(c->Xoo, o, 1, o);
+    const int rc = splitk_gemm<CfgN64RR>(c, "Xoo.Lov", A, B, c->F2, v, o, L * o, 1.0, 0.0);
+    c->stream = main_stream; c->P = main_P; c->P_count = main_P_count;
+    if (rc) return 1;
+    CUDA_OK(c, cudaEventRecord(c->ev_join, c->side));
+  }
   {  // :124, :146 integrand, W = XT - Xov   (columns a of the slab -> JK/E1K rows of the slab)
     dim3 grid(cdiv(na, 32), cdiv(L, 32), o), block(32, 8);
     JkTargets jk = c->jk_targets;
@@ -586,11 +619,7 @@ extern "C" int mpccb_dress(mpccb_ctx* c, const double* t1_dev) {
     Operand B = flat_operand(c->Joo, o, 1, o);
     if (splitk_gemm<CfgN64RR>(c, "W.Joo", A, B, c->OmRep + (i64)a0 * o, na, o, L * o, 1.0, 0.0)) return 1;
   }
-  {  // :133 second half   F2[b][j] = sum_{(L,i)} Lov[(L,i)][b] Xoo[(L,i)][j]      (replicated)
-    Operand A = flat_operand(c->Lov, v, 1, v);
-    Operand B = flat_operand(c->Xoo, o, 1, o);
-    if (splitk_gemm<CfgN64RR>(c, "Xoo.Lov", A, B, c->F2, v, o, L * o, 1.0, 0.0)) return 1;
-  }
+  CUDA_OK(c, cudaStreamWaitEvent(c->stream, c->ev_join, 0));
   }
   if (na == v) return mpccb_dress_post(c);
   return 0;
