@@ -23,13 +23,14 @@ constexpr int BIG = 1 << 30;
 constexpr int NSM = 148;
 
 // tile configurations of the generic DMMA GEMM (warps m x n, fragments m x n, A K-major?, B K-major?)
-typedef GemmCfg<4, 4, 4, 4, true, true> CfgBigKK;     // 128 x 128, 16 warps
+typedef GemmCfg<2, 4, 8, 4, true, true> CfgBigKK;     // 128 x 128, 8 warps x (64 x 32): fewest LDS per DMMA, for long K
+typedef GemmCfg<4, 4, 4, 4, true, true> CfgBig16KK;   // 128 x 128, 16 warps x (32 x 32): short K (latency-bound)
 typedef GemmCfg<4, 2, 4, 4, true, true> CfgN64KK;     // 128 x 64
 typedef GemmCfg<4, 2, 4, 4, false, false> CfgN64RR;
 typedef GemmCfg<4, 2, 4, 4, true, false> CfgN64KR;
 typedef GemmCfg<4, 2, 4, 4, false, true> CfgN64RK;
-typedef GemmCfg<4, 4, 4, 4, true, false> CfgBigKR;    // 128 x 128, B row-major
-typedef GemmCfg<4, 4, 4, 4, false, false> CfgBigRR;   // 128 x 128, both row-major
+typedef GemmCfg<2, 4, 8, 4, true, false> CfgBigKR;    // 128 x 128, B row-major
+typedef GemmCfg<2, 4, 8, 4, false, false> CfgBigRR;   // 128 x 128, both row-major
 typedef GemmCfg<2, 4, 4, 4, false, false> CfgM64RR;   // 64 x 128
 }  // namespace
 
@@ -581,7 +582,7 @@ extern "C" int mpccb_dress(mpccb_ctx* c, const double* t1_dev) {
     Operand A = flat_operand(c->Xoo, 2 * L * o, o, 1);
     Operand B = flat_operand(c->t1T + (i64)a0 * o, na, o, 1);
     Output C = flat_output(c->XT + a0, v, 1);
-    if (na >= 96) { if (launch_gemm<CfgBigKK>(c, "XT|JT", A, B, C, 2 * L * o, na, o, 1, nullptr)) return 1; }
+    if (na >= 96) { if (launch_gemm<CfgBig16KK>(c, "XT|JT", A, B, C, 2 * L * o, na, o, 1, nullptr)) return 1; }
     else          { if (launch_gemm<CfgN64KK>(c, "XT|JT", A, B, C, 2 * L * o, na, o, 1, nullptr)) return 1; }
   }
   // :133 second half   F2[b][j] = sum_{(L,i)} Lov[(L,i)][b] Xoo[(L,i)][j]      (replicated)
