@@ -3,7 +3,10 @@ no DIIS) per shape, CUDA-event timed, FP64 TFLOP/s from the SURVEY.md §8d flop 
 
     python tools/sweep.py [--out gpurun_out/sweep.json] [--shapes o,v,L ...]
 
-Single GPU; shapes whose t2 buffer + integrals do not fit 180 GB are skipped (they need the a-slab sharding).
+One GPU, or several under torchrun (a-slab sharding; `ms` is the max over ranks); shapes whose t2 slab + integrals
+do not fit the free memory are skipped.
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 tools/sweep.py --shapes 128,1024,3072
 """
 import argparse
 import json
@@ -21,14 +24,19 @@ DEFAULT = [(21, 243, 654), (32, 256, 768), (32, 512, 1536), (32, 1024, 3072), (6
            (64, 1024, 3072), (80, 848, 2224), (128, 256, 768), (128, 512, 1536)]
 
 
+WORLD = int(os.environ.get("WORLD_SIZE", 1))
+RANK = int(os.environ.get("RANK", 0))
+
+
 def need_bytes(o, v, L):
     nov = o * v
-    return 8 * (nov * nov + 2 * L * v * v + 9 * L * nov + 600 * nov) + (2 << 30)
+    return 8 * (nov * nov // WORLD + 2 * L * v * v + 9 * L * nov + 600 * nov) + (2 << 30)
 
 
 def run(o, v, L, steps, warmup):
     Loo, Lov, Lvv, eo, ev = device_blocks(o, v, L, seed=0, scale=default_scale(o, v), device="cuda")
-    ll = MPCC_LL(blocks=(Loo, Lov, Lvv, torch.diag(eo), torch.diag(ev), torch.cat([eo, ev])))
+    group = torch.distributed.group.WORLD if WORLD > 1 else None
+    ll = MPCC_LL(blocks=(Loo, Lov, Lvv, torch.diag(eo), torch.diag(ev), torch.cat([eo, ev])), group=group)
     ll._ctx.call("mpccb_set_option", b"profile", 1)
     t1 = torch.zeros(o * v, dtype=torch.float64, device="cuda")
     for _ in range(warmup):
@@ -36,17 +44,23 @@ def run(o, v, L, steps, warmup):
     ll._ctx.profile_read()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize()
+    if WORLD > 1:
+        torch.distributed.barrier()
     e0.record()
     for _ in range(steps):
         res, dE, t1 = ll.step_device(t1, None)
     e1.record()
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / steps
+    if WORLD > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+        ms = float(t.item())
     st = ll._ctx.profile_read()
     fl = F.updated_amps_flops(o, v, L)
-    er = F.eris_flops(o, v, L, v) / (st["eris_t2"][0] / steps * 1e-3) * 1e-12
-    yv = F.yvo_flops(o, v, L, v) / (st["yvo"][0] / steps * 1e-3) * 1e-12
-    return {"nocc": o, "nvir": v, "naux": L, "ms_per_updated_amps": ms, "tflops": fl / (ms * 1e-3) * 1e-12,
+    er = F.eris_flops(o, v, L, ll._na) / (st["eris_t2"][0] / steps * 1e-3) * 1e-12      # this rank's slab
+    yv = F.yvo_flops(o, v, L, ll._na) / (st["yvo"][0] / steps * 1e-3) * 1e-12
+    return {"nocc": o, "nvir": v, "naux": L, "n_gpus": WORLD, "ms_per_updated_amps": ms, "tflops": fl / (ms * 1e-3) * 1e-12,
             "frac_of_nominal_37.2": fl / (ms * 1e-3) * 1e-12 / 37.2, "eris_t2_tflops": er, "yvo_tflops": yv,
             "stages_ms": {k: s[0] / steps for k, s in st.items() if s[1]}, "res": res, "dE": dE}
 
@@ -59,6 +73,9 @@ if __name__ == "__main__":
     ap.add_argument("--shapes", nargs="*")
     a = ap.parse_args()
     shapes = [tuple(int(x) for x in s.split(",")) for s in a.shapes] if a.shapes else DEFAULT
+    if WORLD > 1:
+        torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", 0)))
+        torch.distributed.init_process_group("nccl", device_id=torch.device("cuda", torch.cuda.current_device()))
     free = torch.cuda.mem_get_info()[0]
     rows = []
     for o, v, L in shapes:
@@ -70,7 +87,11 @@ if __name__ == "__main__":
             rows.append(run(o, v, L, a.steps, a.warmup))
         except Exception as e:                                   # keep the sweep going; record the failure
             rows.append({"nocc": o, "nvir": v, "naux": L, "error": repr(e)[:300]})
-        print(json.dumps(rows[-1]), flush=True)
+        if RANK == 0:
+            print(json.dumps(rows[-1]), flush=True)
         torch.cuda.empty_cache()
-    with open(a.out, "w") as f:
-        json.dump(rows, f, indent=1)
+    if RANK == 0:
+        with open(a.out, "w") as f:
+            json.dump(rows, f, indent=1)
+    if WORLD > 1:
+        torch.distributed.destroy_process_group()
