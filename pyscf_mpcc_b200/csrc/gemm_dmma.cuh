@@ -40,6 +40,11 @@ struct Output {
   i64 m_hi, m_lo, n_hi, n_lo;
   int mdiv, ndiv;
   i64 split_stride;    // offset between split-K slices (0 if none)
+  // optional store mask (mirror scheme of the unfused eris GEMM): element (m, n) belongs to block
+  // (m / mdiv, n / ndiv); it is stored only if keep[(m / mdiv) * keep_ld + n / ndiv] & 1, and a tile without any
+  // kept block returns before its K loop. nullptr: store everything.
+  const unsigned char* keep;
+  int keep_ld;
 };
 
 struct GemmDims {
@@ -47,10 +52,6 @@ struct GemmDims {
   int tm_eff, tn_eff;  // rows/cols a tile advances by (<= TM/TN); == TM/TN for plain GEMMs
   int tiles_m, tiles_n;
   int kchunk;          // K range per blockIdx.z (multiple of 16)
-  // mirror scheme of the unfused eris GEMM (0 = off): rows are global indices sym_row0 + m over (a,i), columns (b,j);
-  // a tile whose columns all lie in [sym_col_lo, ...) and whose last column block b is below its first row block a
-  // holds only blocks that are produced as mirrors, and is skipped
-  int sym_o, sym_row0, sym_col_lo;
 };
 
 constexpr int TK = 16;
@@ -215,7 +216,14 @@ gemm_store_kernel(Operand A, Operand B, Output C, GemmDims d) {
   int tm, tn;
   tile_coords(blockIdx.x, d.tiles_m, d.tiles_n, tm, tn);
   const int m0 = tm * d.tm_eff, n0 = tn * d.tn_eff;
-  if (d.sym_o > 0 && n0 >= d.sym_col_lo && (min(n0 + Cfg::TN, d.N) - 1) / d.sym_o < (d.sym_row0 + m0) / d.sym_o) return;
+  if (C.keep) {
+    bool any = false;
+    const int r1 = (min(m0 + d.tm_eff, d.M) - 1) / C.mdiv, c1 = (min(n0 + d.tn_eff, d.N) - 1) / C.ndiv;
+    for (int r = m0 / C.mdiv; r <= r1 && !any; ++r)
+      for (int cidx = n0 / C.ndiv; cidx <= c1; ++cidx)
+        if (C.keep[(i64)r * C.keep_ld + cidx] & 1) { any = true; break; }
+    if (!any) return;
+  }
   const int kbeg = blockIdx.z * d.kchunk;
   const int kend = min(d.K, kbeg + d.kchunk);
   double acc[Cfg::MT][Cfg::NT][2];
@@ -238,6 +246,7 @@ gemm_store_kernel(Operand A, Operand B, Output C, GemmDims d) {
         const int nl = wn * Cfg::NT * 8 + j * 8 + 2 * tig + c;
         const int n = n0 + nl;
         if (nl >= d.tn_eff || n >= d.N) continue;
+        if (C.keep && !(C.keep[(i64)(m / C.mdiv) * C.keep_ld + n / C.ndiv] & 1)) continue;
         const i64 off = moff + (i64)(n / C.ndiv) * C.n_hi + (i64)(n % C.ndiv) * C.n_lo;
         const double v = acc[i][j][c];
         C.base[off] = v;

@@ -5,6 +5,7 @@
 // unit-stride index and warp-shuffle reductions.
 #pragma once
 #include "common.cuh"
+#include "gemm_dmma.cuh"   // SymInfo (mirror scheme)
 
 namespace mpccb {
 
@@ -456,15 +457,20 @@ namespace mpccb {
 // fixed order) from the block's own freshly written (L1/L2-hot) values.
 __global__ void __launch_bounds__(256)
 k_t2_finalize(double* __restrict__ T, const double* __restrict__ eo, const double* __restrict__ ev,
-              const double* __restrict__ Fvo, double* __restrict__ OmP, int o, int v, int a_begin, int na, int sym) {
-  // sym: mirror scheme inside the slab — blocks with b < a are not touched by the GEMM nor here; block (a,b), b > a,
-  // also writes t2[b,a,:,:] = t2[a,b,:,:]^T; of a diagonal block only the j >= i half of e was computed (e is symmetric).
+              const double* __restrict__ Fvo, double* __restrict__ OmP, int o, int v, int a_begin, int na,
+              SymInfo sym, const unsigned char* __restrict__ flags) {
+  // Mirror scheme (flags != nullptr; one byte per (a,b) block of the slab: bit 0 = this rank computes the block,
+  // bit 1 = it also writes t2[b,a,:,:] = t2[a,b,:,:]^T, bits 4.. = rank that owns b): blocks without bit 0 were
+  // not stored by the GEMM and are not touched here — they arrive as somebody's mirror, in this rank's buffer or,
+  // over NVLink, from the rank that computed the transposed block. Of a diagonal block only the j >= i half of e
+  // is read (e is symmetric).
   const int b = blockIdx.x, al = blockIdx.y, a = a_begin + al;
-  const bool in_slab = sym && b >= a_begin && b < a_begin + na;
-  if (in_slab && b < a) return;
+  const unsigned char f = flags ? flags[(i64)al * v + b] : (unsigned char)1;
+  if (!(f & 1)) return;
   double* blk = T + ((i64)al * v + b) * o * o;
-  double* mir = (in_slab && b > a) ? T + ((i64)(b - a_begin) * v + a) * o * o : nullptr;
-  const bool diag = in_slab && b == a;
+  const int s = f >> 4;
+  double* mir = (f & 2) ? sym.Tp[s] + ((i64)(b - sym.bounds[s]) * v + a) * o * o : nullptr;
+  const bool diag = flags && b == a;
   const double dab = ev[a] + ev[b];
   const int npair = o * (o + 1) / 2;
   for (int p = threadIdx.x; p < npair; p += blockDim.x) {
@@ -487,20 +493,21 @@ k_t2_finalize(double* __restrict__ T, const double* __restrict__ eo, const doubl
   __threadfence_block();
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
-  const double* f = Fvo + (i64)b * o;
+  const double* f_b = Fvo + (i64)b * o;
   for (int i = warp; i < o; i += nw) {
-    double s = 0.0;
-    for (int j = lane; j < o; j += 32) s += blk[i * o + j] * f[j];
-    s = warp_sum(s);
-    if (lane == 0) OmP[((i64)b * na + al) * o + i] = s;
+    double sum = 0.0;
+    for (int j = lane; j < o; j += 32) sum += blk[i * o + j] * f_b[j];
+    sum = warp_sum(sum);
+    if (lane == 0) OmP[((i64)b * na + al) * o + i] = sum;
   }
-  if (mir) {   // the mirror block's share of sum t2 . Fov: rows (b, j), slot of the block (b, a)
-    const double* fa = Fvo + (i64)a * o;
+  if (mir) {   // the mirror block's share of sum t2 . Fov: rows (b, j) of whichever slab owns b, from the local block
+    const double* f_a = Fvo + (i64)a * o;
+    const i64 nov = (i64)o * v;
     for (int j = warp; j < o; j += nw) {
-      double s = 0.0;
-      for (int i = lane; i < o; i += 32) s += mir[j * o + i] * fa[i];
-      s = warp_sum(s);
-      if (lane == 0) OmP[((i64)a * na + (b - a_begin)) * o + j] = s;
+      double sum = 0.0;
+      for (int i = lane; i < o; i += 32) sum += blk[i * o + j] * f_a[i];
+      sum = warp_sum(sum);
+      if (lane == 0) sym.OmPm[(i64)al * nov + (i64)b * o + j] = sum;
     }
   }
 }

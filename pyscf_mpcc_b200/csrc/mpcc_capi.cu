@@ -60,6 +60,7 @@ struct mpccb_ctx {
   JkTargets jk_targets;      // n == 0: plain local JK
   SymInfo sym;               // symmetric eris/t2 scheme (host copy; tiles/OmPm are device pointers)
   int sym_off, n_tiles;
+  const unsigned char* blkflags;   // unfused t2 path under the mirror scheme (see build_tile_list)
   int2* tiles_dev;
   i64 tiles_cap;
   i64 P_count, OmP_count;
@@ -140,6 +141,7 @@ Output flat_output(double* base, i64 m_stride, i64 n_stride) {
   c.m_hi = 0; c.m_lo = m_stride; c.mdiv = BIG;
   c.n_hi = 0; c.n_lo = n_stride; c.ndiv = BIG;
   c.split_stride = 0;
+  c.keep = nullptr; c.keep_ld = 0;
   return c;
 }
 
@@ -154,10 +156,9 @@ int choose_splits(int tiles, int K) {
 
 template <class Cfg>
 int launch_gemm(mpccb_ctx* c, const char* what, const Operand& A, const Operand& B, Output C,
-                int M, int N, int K, int splits, double* partial, int sym_o = 0, int sym_row0 = 0, int sym_col_lo = 0) {
+                int M, int N, int K, int splits, double* partial) {
   GemmDims d;
   d.M = M; d.N = N; d.K = K;
-  d.sym_o = sym_o; d.sym_row0 = sym_row0; d.sym_col_lo = sym_col_lo;
   d.tm_eff = Cfg::TM; d.tn_eff = Cfg::TN;
   d.tiles_m = cdiv(M, Cfg::TM); d.tiles_n = cdiv(N, Cfg::TN);
   d.kchunk = (int)align_up(cdiv(K, splits), TK);
@@ -230,7 +231,8 @@ struct Carve {
 };
 
 // the mirror scheme applies to the fused TMA kernel only
-bool t2_sym_active(const mpccb_ctx* c) { return !c->sym_off && c->use_tma && !c->t2_unfused; }
+// fused kernel: only the TMA form has the mirror passes; unfused path: any GEMM (store mask + k_t2_finalize)
+bool t2_sym_active(const mpccb_ctx* c) { return !c->sym_off && (c->use_tma || c->t2_unfused); }
 
 // Launch list of the fused eris -> t2 kernel under the mirror scheme: every tile that holds at least one (a,b)
 // block this rank computes (sym_compute), ordered like tile_coords (8 column tiles x all row tiles per group).
@@ -244,6 +246,26 @@ int build_tile_list(mpccb_ctx* c) {
     c->sym.bounds[0] = 0; c->sym.bounds[1] = c->a_begin; c->sym.bounds[2] = c->a_end; c->sym.bounds[3] = c->v;
   }
   c->sym.Tp[c->sym.rank] = c->T;
+  if (c->t2_unfused) {
+    // one byte per (a,b) block of the slab: bit 0 computed here, bit 1 mirrored from here, bits 4.. owner of b
+    // (store mask of the GEMM and work list of k_t2_finalize); lives in the tile-list workspace
+    std::vector<unsigned char> flags((size_t)c->na * c->v);
+    int computed = 0;
+    for (int al = 0; al < c->na; ++al)
+      for (int b = 0; b < c->v; ++b) {
+        bool mirror; int s;
+        const bool comp = sym_compute(c->sym, c->a_begin + al, b, mirror, s);
+        flags[(size_t)al * c->v + b] = (unsigned char)((comp ? 1 : 0) | (mirror ? 2 : 0) | (s << 4));
+        computed += comp;
+      }
+    if ((i64)flags.size() > c->tiles_cap * (i64)sizeof(int2)) return fail(c, "block flags exceed their workspace");
+    CUDA_OK(c, cudaMemcpyAsync(c->tiles_dev, flags.data(), flags.size(), cudaMemcpyHostToDevice, c->stream));
+    CUDA_OK(c, cudaStreamSynchronize(c->stream));
+    c->n_tiles = computed;
+    c->blkflags = reinterpret_cast<const unsigned char*>(c->tiles_dev);
+    return 0;
+  }
+  c->blkflags = nullptr;
   std::vector<int2> list;
   list.reserve((size_t)c->n_tiles / 2 + 16);
   for (int g0 = 0; g0 < c->t2_tiles_n; g0 += 8)
@@ -777,11 +799,13 @@ int launch_eris_t2_unfused(mpccb_ctx* c) {
   Output C = flat_output(c->T, 0, 0);
   C.mdiv = o; C.m_hi = (i64)v * o * o; C.m_lo = o;      // m = (a_l, i)
   C.ndiv = o; C.n_hi = (i64)o * o;     C.n_lo = 1;      // n = (b, j)
-  const int symm = c->sym_off ? 0 : 1;     // mirror scheme inside the slab
-  if (launch_gemm<CfgBigKK>(c, "eris(unfused)", A, B, C, c->na * o, v * o, L, 1, nullptr,
-                            symm ? o : 0, c->a_begin * o, c->a_begin * o)) return 1;
+  const unsigned char* flags = c->sym.enabled ? c->blkflags : nullptr;     // mirror scheme (build_tile_list)
+  C.keep = flags; C.keep_ld = v;
+  if (launch_gemm<CfgBigKK>(c, "eris(unfused)", A, B, C, c->na * o, v * o, L, 1, nullptr)) return 1;
   dim3 grid(v, c->na);
-  k_t2_finalize<<<grid, 256, 0, c->stream>>>(c->T, c->eo, c->ev, c->Fvo, c->OmP, o, v, c->a_begin, c->na, symm);
+  SymInfo sym = c->sym;
+  sym.Tp[sym.rank] = c->T;
+  k_t2_finalize<<<grid, 256, 0, c->stream>>>(c->T, c->eo, c->ev, c->Fvo, c->OmP, o, v, c->a_begin, c->na, sym, flags);
   LAUNCH_OK(c, "k_t2_finalize");
   return 0;
 }
@@ -801,7 +825,6 @@ int launch_eris_t2(mpccb_ctx* c) {
   d.tm_eff = c->t2_na * o; d.tn_eff = c->t2_nb * o;
   d.tiles_m = c->t2_tiles_m; d.tiles_n = c->t2_tiles_n;
   d.kchunk = L;
-  d.sym_o = 0; d.sym_row0 = 0; d.sym_col_lo = 0;
   static bool attr_done = false;
   if (!attr_done) {
     CUDA_OK(c, cudaFuncSetAttribute(gemm_t2_kernel<Cfg>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -838,7 +861,7 @@ extern "C" int mpccb_doubles_begin(mpccb_ctx* c, double* red_dev) {
   // the slab's W.Joo singles term from mpccb_dress (:126-127) joins the partial sums
   CUDA_OK(c, cudaMemcpyAsync(Om + (i64)c->a_begin * o, c->OmRep + (i64)c->a_begin * o, sizeof(double) * na * o,
                              cudaMemcpyDeviceToDevice, c->stream));
-  const bool symm = c->sym.enabled && !c->t2_unfused && c->use_tma;
+  const bool symm = c->sym.enabled;
   if (symm) {   // tiles that are not launched / rows that are not mirrored must read as zero in the reductions
     CUDA_OK(c, cudaMemsetAsync(c->OmP, 0, sizeof(double) * c->OmP_count, c->stream));
     CUDA_OK(c, cudaMemsetAsync(c->sym.OmPm, 0, sizeof(double) * c->t2_tiles_m * nov, c->stream));

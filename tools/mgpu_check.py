@@ -31,10 +31,11 @@ def main():
         o, v, L = (int(x) for x in g["shape"])
         if v < world:
             continue
-        for slabs in (None, uneven_bounds(v, world)):
+        for slabs, unfused in ((None, None), (uneven_bounds(v, world), None), (None, True)):
             if slabs is not None and slabs == even_bounds(v, world):
                 continue
-            ll = MPCC_LL(SyntheticMF(o, v, L, seed=0, scale=float(g["scale"])), device=dev, slabs=slabs)
+            ll = MPCC_LL(SyntheticMF(o, v, L, seed=0, scale=float(g["scale"])), device=dev, slabs=slabs,
+                         t2_unfused=unfused)
             ll.verbose_print = False
             e = ll.kernel()
             tr = np.array(ll.history)
@@ -58,7 +59,7 @@ def main():
             flag = torch.tensor([0 if ok else 1], device=dev)
             dist.all_reduce(flag)
             if rank == 0:
-                print(f"{os.path.basename(path)} world={world} slabs={ll._bounds} jk={ll._jk_mode} its={ll.iterations} E={e:.12e} "
+                print(f"{os.path.basename(path)} world={world} slabs={ll._bounds} t2={'unfused' if unfused else 'auto'} peers={ll._t2_peers} jk={ll._jk_mode} its={ll.iterations} E={e:.12e} "
                       f"{'OK' if flag.item() == 0 else 'MISMATCH'}", flush=True)
             bad += int(flag.item())
             del ll
