@@ -1,4 +1,4 @@
-"""Development probe: every intermediate of one updated_amps vs the oracle, then full kernel() traces."""
+"""Development probe (test infrastructure: it uses the oracle, so it lives under tests/; not collected by pytest): every intermediate of one updated_amps vs the oracle, then full kernel() traces."""
 import sys, os, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
