@@ -133,6 +133,7 @@ struct TmaGemmParams {
   // A-operand addressing: mode 0 = 2-D map (k, row); mode 1 = 4-D map over T[a][b][i][j]:
   //   k step kt -> (b = kt / jsteps, j0 = 16 * (kt % jsteps)), rows = (a, i)
   int a_mode, jsteps, o, n_a;
+  int i0;                // a_mode 1: first occupied index i of the rows this launch covers (box = 16 j x w i x 1 b x n_a a)
   uint32_t a_bytes, b_bytes;   // bytes one stage receives for A / B (box sizes)
   // plain store epilogue
   double* C;
@@ -141,9 +142,12 @@ struct TmaGemmParams {
   // stores to C + s*split_stride (partials reduced afterwards in fixed order). ksplit == 1: none.
   int ksplit, nk_split, tiles_total;
   i64 split_stride;
+  // EPI 2: store through a two-level index map with an optional block mask (gemm_dmma.cuh, Output): the unfused
+  // eris GEMM scatters e[(a,i),(b,j)] into T[a][b][i][j] and skips the blocks that arrive as somebody's mirror
+  Output out;
 };
 
-// EPI: 0 = plain row-major store (Yvo), 1 = fused eris -> t2 epilogue.
+// EPI: 0 = plain row-major store (Yvo), 1 = fused eris -> t2 epilogue, 2 = index-mapped, masked store (p.out).
 // Every warp is a consumer; lane 0 of warp 0 doubles as the TMA producer: at the top of K step kt it
 // refills the stage that all warps released at the end of step kt-1 with the operands of step
 // kt + STAGES-1. No 17th warp, so a sub-partition holds 4 (or 2 x 2) warps and ptxas gets 128 registers.
@@ -169,6 +173,14 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
     tile_coords(blockIdx.x - split * ntiles, p.tiles_m, p.tiles_n, tm, tn);
   }
   const int m0 = tm * p.tm_eff, n0 = tn * p.tn_eff;
+  if (EPI == 2 && p.out.keep) {           // no kept block in this tile: nothing to compute (uniform over the CTA)
+    bool any = false;
+    const int r1 = (min(m0 + p.tm_eff, p.M) - 1) / p.out.mdiv, c1 = (min(n0 + p.tn_eff, p.N) - 1) / p.out.ndiv;
+    for (int r = m0 / p.out.mdiv; r <= r1 && !any; ++r)
+      for (int cidx = n0 / p.out.ndiv; cidx <= c1; ++cidx)
+        if (p.out.keep[(i64)r * p.out.keep_ld + cidx] & 1) { any = true; break; }
+    if (!any) return;
+  }
   const bool producer = (threadIdx.x == 0);
   const int k_first = split * p.nk_split;                        // first K step of this CTA
   const int nk = (EPI == 0 && p.ksplit > 1) ? min(p.nk_split, p.nk - k_first) : p.nk;
@@ -185,7 +197,7 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
       // K runs over (b, j); j in chunks of 16 — for nocc not a multiple of 16 the last chunk of every b reads past
       // the j extent of the 4-D map and TMA zero-fills it, which also cancels B's columns of the next b
       const int b = kt / p.jsteps, j0 = (kt - b * p.jsteps) * TMA_TK;
-      tma_load_4d(a_dst, &mapA, &full[s], j0, 0, b, tm * p.n_a);
+      tma_load_4d(a_dst, &mapA, &full[s], j0, p.i0, b, tm * p.n_a);
       tma_load_2d(b_dst, &mapB, &full[s], b * p.o + j0, n0);
       return;
     }
@@ -260,6 +272,27 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
           const int nl = wn * 32 + j * 8 + rho(2 * tig + c);
           const int n = n0 + nl;
           if (nl < p.tn_eff && n < p.N) p.C[split * p.split_stride + (i64)m * p.ldc + n] = acc[i][j][c];
+        }
+    }
+  } else if (EPI == 2) {
+    const Output& C = p.out;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int ml = wm * 32 + i * 8 + rho(g);
+      const int m = m0 + ml;
+      if (ml >= p.tm_eff || m >= p.M) continue;
+      const int mq = m / C.mdiv;
+      const i64 moff = (i64)mq * C.m_hi + (i64)(m - mq * C.mdiv) * C.m_lo;
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          const int nl = wn * 32 + j * 8 + rho(2 * tig + c);
+          const int n = n0 + nl;
+          if (nl >= p.tn_eff || n >= p.N) continue;
+          const int nq = n / C.ndiv;
+          if (C.keep && !(C.keep[(i64)mq * C.keep_ld + nq] & 1)) continue;
+          C.base[moff + (i64)nq * C.n_hi + (i64)(n - nq * C.ndiv) * C.n_lo] = acc[i][j][c];
         }
     }
   } else {

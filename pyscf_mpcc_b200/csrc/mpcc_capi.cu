@@ -292,11 +292,15 @@ int build_tile_list(mpccb_ctx* c) {
   return 0;
 }
 
+// Yvo through one TMA launch whose 128-row tiles hold 128/nocc whole values of a: when those fill >= 85 % of the
+// tile (nocc = 64, 32, 22, 42, 110..128, ...). Other even nocc: power-of-two pieces (launch_yvo_tma_pieces).
+bool yvo_single_launch(int o) { return o % 2 == 0 && o <= 128 && (128 / o) * o >= 109; }
+
 // Split-K factor of the TMA Yvo GEMM: with few output tiles per SM (a-slab sharding) the last wave is
 // mostly idle; s K-slices turn T tiles into T*s shorter CTAs. Pick s <= 8 minimising ceil(T*s/148)/s.
 int choose_yvo_splits(const mpccb_ctx* c) {
   const int o = c->o;
-  if (!c->use_tma || o % 2 != 0 || o > 128 || (128 / o) * o < 96) return 1;
+  if (!c->use_tma || !yvo_single_launch(o)) return 1;      // split-K only on the single-launch path (launch_yvo)
   const int n_a = 128 / o;
   const i64 T = (i64)cdiv(c->na, n_a) * cdiv(c->L, 128);
   const i64 nk = (i64)c->v * cdiv(o, TMA_TK);
@@ -792,6 +796,46 @@ int launch_yvo_tma(mpccb_ctx* c) {
 
 // unfused form of :135-137,:139 for occupied counts that tile badly: e -> T[a][b][i][j] with the
 // generic DMMA GEMM (any tile alignment), then t2 = (2e - e^T)/D in place per (a,b) block
+// Yvo for an even nocc that does not divide 128: the occupied index of the rows is cut into power-of-two pieces
+// (80 = 64 + 16, 22 = 16 + 4 + 2, ...); a piece of width w is one launch whose 128-row tiles hold 128/w values of a
+// (4-D box 16 j x w i x 1 b x 128/w a), so every tile is full whatever nocc is. Rows go back to Y[(a,i)][L]
+// through the index-mapped store (EPI 2). TMA needs 16-byte strides, hence even nocc; odd nocc stays on the generic
+// kernel.
+int launch_yvo_tma_pieces(mpccb_ctx* c) {
+  constexpr int TN = TmaCfg<4>::TN;
+  const int o = c->o, v = c->v, L = c->L;
+  double* Yslab = c->Y + (i64)c->a_begin * o * L;
+  CUtensorMap mB;
+  if (make_map_2d(c, &mB, c->Lvo, (i64)v * o, L, (i64)v * o, TN)) return 1;
+  int i0 = 0;
+  for (int w = 128; w >= 2; w >>= 1) {
+    while (o - i0 >= w) {
+      const int n_a = 128 / w;
+      CUtensorMap mA;
+      cuuint64_t dims[4] = {(cuuint64_t)o, (cuuint64_t)o, (cuuint64_t)v, (cuuint64_t)c->na};
+      cuuint64_t strides[3] = {(cuuint64_t)o * 8, (cuuint64_t)o * o * 8, (cuuint64_t)v * o * o * 8};
+      cuuint32_t box[4] = {(cuuint32_t)TMA_TK, (cuuint32_t)w, 1, (cuuint32_t)n_a};
+      if (make_tensor_map(c, &mA, c->T, 4, dims, strides, box)) return 1;
+      TmaGemmParams p;
+      memset(&p, 0, sizeof(p));
+      p.M = c->na * w; p.N = L;
+      p.tm_eff = TMA_TM; p.tn_eff = TN;
+      p.tiles_m = cdiv(c->na, n_a); p.tiles_n = cdiv(L, TN);
+      p.nk = v * cdiv(o, TMA_TK);
+      p.a_mode = 1; p.jsteps = cdiv(o, TMA_TK); p.o = o; p.n_a = n_a; p.i0 = i0;
+      p.a_bytes = TMA_TM * TMA_TK * 8; p.b_bytes = TN * TMA_TK * 8;
+      p.ksplit = 1;
+      p.out = flat_output(Yslab + (i64)i0 * L, 0, 1);
+      p.out.mdiv = w; p.out.m_hi = (i64)o * L; p.out.m_lo = L;      // tile row m -> a = m / w, i = i0 + m % w
+      T2Params t;
+      memset(&t, 0, sizeof(t));
+      if (launch_tma<2, 4>(c, "gemm_tma_kernel<yvo piece>", mA, mB, p, t)) return 1;
+      i0 += w;
+    }
+  }
+  return 0;
+}
+
 int launch_eris_t2_unfused(mpccb_ctx* c) {
   const int o = c->o, v = c->v, L = c->L;
   Operand A = flat_operand(c->JK + (i64)c->a_begin * o * c->ldk, c->na * o, c->ldk, 1);
@@ -801,7 +845,28 @@ int launch_eris_t2_unfused(mpccb_ctx* c) {
   C.ndiv = o; C.n_hi = (i64)o * o;     C.n_lo = 1;      // n = (b, j)
   const unsigned char* flags = c->sym.enabled ? c->blkflags : nullptr;     // mirror scheme (build_tile_list)
   C.keep = flags; C.keep_ld = v;
-  if (launch_gemm<CfgBigKK>(c, "eris(unfused)", A, B, C, c->na * o, v * o, L, 1, nullptr)) return 1;
+  if (c->use_tma) {
+    // JK rows are a plain K-major matrix whatever nocc is: the TMA-fed kernel with the index-mapped, masked store
+    constexpr int TN = TmaCfg<4>::TN;
+    CUtensorMap mA, mB;
+    if (make_map_2d(c, &mA, c->JK + (i64)c->a_begin * o * c->ldk, L, (i64)c->na * o, c->ldk, TMA_TM)) return 1;
+    if (make_map_2d(c, &mB, c->JK, L, (i64)v * o, c->ldk, TN)) return 1;
+    TmaGemmParams p;
+    memset(&p, 0, sizeof(p));
+    p.M = c->na * o; p.N = v * o;
+    p.tm_eff = TMA_TM; p.tn_eff = TN;
+    p.tiles_m = cdiv(p.M, TMA_TM); p.tiles_n = cdiv(p.N, TN);
+    p.nk = cdiv(L, TMA_TK);
+    p.a_mode = 0;
+    p.a_bytes = TMA_TM * TMA_TK * 8; p.b_bytes = TN * TMA_TK * 8;
+    p.ksplit = 1;
+    p.out = C;
+    T2Params t;
+    memset(&t, 0, sizeof(t));
+    if (launch_tma<2, 4>(c, "gemm_tma_kernel<scatter>", mA, mB, p, t)) return 1;
+  } else if (launch_gemm<CfgBigKK>(c, "eris(unfused)", A, B, C, c->na * o, v * o, L, 1, nullptr)) {
+    return 1;
+  }
   dim3 grid(v, c->na);
   SymInfo sym = c->sym;
   sym.Tp[sym.rank] = c->T;
@@ -839,7 +904,8 @@ int launch_eris_t2(mpccb_ctx* c) {
 int launch_yvo(mpccb_ctx* c) {
   const int o = c->o, v = c->v, L = c->L;
   // TMA strides must be multiples of 16 bytes: even nocc
-  if (c->use_tma && o % 2 == 0 && o <= 128 && (128 / o) * o >= 96) return launch_yvo_tma(c);
+  if (c->use_tma && yvo_single_launch(o)) return launch_yvo_tma(c);
+  if (c->use_tma && o % 2 == 0) return launch_yvo_tma_pieces(c);
   // :138  Y[(a,i)][L] = sum_{(b,j)} T[a][b][i][j] Lvo[L][(b,j)]
   Operand A;
   A.base = c->T; A.rows = c->na * o;

@@ -103,10 +103,12 @@ def test_t2_kernel_variants_agree_with_fixture(variant):
 
 
 @pytest.mark.parametrize("shape", [(5, 19, 116, 0.1), (7, 33, 65, 0.15), (16, 48, 150, 0.1), (33, 70, 129, 0.05),
-                                   (64, 66, 130, 0.05), (80, 90, 100, 0.04), (128, 130, 64, 0.03), (131, 140, 48, 0.03)])
+                                   (64, 66, 130, 0.05), (80, 90, 100, 0.04), (128, 130, 64, 0.03), (131, 140, 48, 0.03),
+                                   (48, 50, 70, 0.05), (100, 102, 40, 0.03)])
 def test_intermediates_against_oracle(shape):
     """Every stage of updated_amps vs the oracle on the same seeded inputs (odd sizes, occupied counts on
-    both sides of the fused-epilogue limit of 128, badly tiling nocc = 80 (unfused path), naux not a multiple of the K tile)."""
+    both sides of the fused-epilogue limit of 128, badly tiling nocc = 80 (unfused path), naux not a multiple of the K
+    tile; nocc = 48, 80, 100: Yvo through power-of-two pieces of the occupied index, 32+16, 64+16, 64+32+4)."""
     from oracle.mpcc_oracle import LowLevelOracle
     o, v, L, scale = shape
     mf, ll = _solver(o, v, L, scale, seed=3)
