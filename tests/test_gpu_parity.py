@@ -88,12 +88,14 @@ def test_yvo_split_k_matches_oracle(split):
     assert abs(dE - dE_o) <= E_TOL and np.abs(t1n - t1n_o).max() <= AMP_TOL
 
 
-@pytest.mark.parametrize("variant", ["default", "wide", "unfused", "unfused_no_sym", "no_tma", "no_sym", "wide_no_sym"])
+@pytest.mark.parametrize("variant", ["default", "wide", "unfused", "unfused_no_sym", "unfused_no_tma", "no_tma", "no_sym",
+                                     "wide_no_sym"])
 def test_t2_kernel_variants_agree_with_fixture(variant):
     """All forms of the eris -> t2 step (128x64 two-CTA tiles, 128x128 tiles, unfused GEMM + in-place pass,
     generic non-TMA kernel) reproduce the reference fixture."""
     g, o, v, L, scale = _load([p for p in golden_cases() if "12_64_192" in p][0])
-    kw = {"default": {}, "wide": {"t2_wide_tiles": True}, "unfused": {"t2_unfused": True}, "unfused_no_sym": {"t2_unfused": True, "t2_sym": False}, "no_tma": {"use_tma": False},
+    kw = {"default": {}, "wide": {"t2_wide_tiles": True}, "unfused": {"t2_unfused": True}, "unfused_no_sym": {"t2_unfused": True, "t2_sym": False},
+          "unfused_no_tma": {"t2_unfused": True, "use_tma": False}, "no_tma": {"use_tma": False},
           "no_sym": {"t2_sym": False}, "wide_no_sym": {"t2_sym": False, "t2_wide_tiles": True}}[variant]
     mf, ll = _solver(o, v, L, scale, **kw)
     e = ll.kernel()
