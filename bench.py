@@ -12,14 +12,22 @@ the configuration the metric is quoted on; it fits one GPU). FP64 throughout.
   amplitudes resident in HBM (``MPCC_LL.step_device``); CUDA-event timed.
 * ``e2e``    — same metric through the public API the reference user calls
   (``updated_amps()`` / ``run_diis()`` with host numpy t1 in and out every step).
-* ``roofline`` — the dominant kernel (fused eris/t2 DMMA GEMM), timed live with
-  CUDA events on its stream inside the timed region, against the FP64 GEMM rate
-  measured on this pool's B200 (cuBLAS DGEMM yardstick, profiles/r1_fp64_microbench.txt).
-* ``cpu_baseline`` — the oracle port of the reference's einsum path on a bounded
-  sample (rank 0, N=1 only).
+* ``roofline`` — the dominant kernel (Yvo DMMA GEMM), timed live with CUDA events on
+  its stream inside the timed region, against the FP64 GEMM rate measured IN THIS RUN
+  (cuBLAS DGEMM of the same product through ``torch.matmul``, outside the timed region,
+  with its own clock sample) and against the nominal 37.2 TFLOP/s.
+* ``parity_vs_fixture`` — the (dE, res) trace of the timed steps against the committed
+  fixtures (oracle trace ``tests/golden/trace_64_512_1536.npz`` for the iterations the
+  oracle ran, one-rank GPU trace ``tests/golden/bench_trace_64_512_1536.json`` beyond),
+  at every N: |dE| <= 1e-8 Eh, res to 1e-6 relative (+1e-9 absolute once converged).
+* ``cpu_baseline`` — the reference's own files (staged under oracle/_ref, executed
+  unmodified) on a bounded sample: the same aspect ratio at 1/4 of every extent
+  (rank 0, N=1 only). ``--impl reference`` times the same thing for K steps.
 
-With N > 1 (torchrun, one rank per GPU, NCCL) the virtual index is sharded over
-ranks (strong scaling: the problem is fixed).
+Inputs: ``pyscf_mpcc_b200.synthetic.host_blocks`` (the seeded generator of every
+fixture, drawn on the host and uploaded before the timed region), so the CPU oracle
+sees the same tensors. With N > 1 (torchrun, one rank per GPU, NCCL) the virtual
+index is sharded over ranks (strong scaling: the problem is fixed).
 """
 from __future__ import annotations
 
@@ -36,11 +44,10 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-# FP64 GEMM rate measured on this pool's B200 with cuBLAS DGEMM on the eris-shaped product
-# (32768 x 8192 x 1536; tools/fp64_yardstick.py -> profiles/r1_fp64_microbench.txt). MEASURED_PEAKS.json
-# holds no FP64 figure. Nominal: 148 SMs x 64 DFMA/clk x 1.965 GHz = 37.2 TFLOP/s.
-FP64_PEAK_TFLOPS_MEASURED = 36.07
+# MEASURED_PEAKS.json holds no FP64 figure (bf16 and HBM only), so the FP64 ceiling is measured in this run
+# (fp64_yardstick) and quoted next to the nominal one: 148 SMs x 64 DFMA/clk x 1.965 GHz = 37.2 TFLOP/s.
 FP64_PEAK_TFLOPS_NOMINAL = 37.2
+GOLDEN = os.path.join(ROOT, "tests", "golden")
 
 
 def parse_args():
@@ -59,6 +66,8 @@ def parse_args():
                     help="t2 part of the DIIS vector over ranks: balanced column ownership (default for N>1) or row segments")
     ap.add_argument("--slabs", default="equal", choices=["balanced", "equal"],
                     help="split of the virtual index over ranks (sharding.balanced_bounds / equal widths)")
+    ap.add_argument("--write-trace", default=None,
+                    help="write the (dE, res) trace of the timed steps to this JSON file (one-rank fixture)")
     return ap.parse_args()
 
 
@@ -117,98 +126,249 @@ class ClockSampler:
 
 
 # ---------------------------------------------------------------------------------------------
-# CPU legs (oracle port of the reference's einsum path). Only these functions touch oracle/.
+# CPU legs. Only these functions touch oracle/: the reference's own files (oracle/_ref, staged by
+# oracle/make_ref.py, executed unmodified through oracle/ref_shim.py) are what is timed.
 # ---------------------------------------------------------------------------------------------
-def cpu_sample_inputs(o, v, L, seed):
+def sample_shape(o, v, L):
+    """The bounded sample of the workload the reference can finish in seconds per step: the same aspect ratio at 1/4
+    of every extent ((64,512,1536) -> (16,128,384); 1/256 of the flops)."""
+    return max(o // 4, 2), max(v // 4, 4), max(L // 4, 8)
+
+
+class ReferenceSample:
+    """The reference's MPCC_LL (pyscf/mpcc/dfrmpcc_lowlevel.py, unmodified) on the sample shape; one step = one trip
+    of kernel()'s loop: updated_amps() + run_diis() (:84-86)."""
+
+    def __init__(self, o, v, L, seed):
+        import contextlib
+        import io
+        from oracle import ref_shim
+        from pyscf_mpcc_b200.synthetic import SyntheticMF, default_scale
+        self.kind = "reference"
+        self.shape = (o, v, L)
+        mf = SyntheticMF(o, v, L, seed=seed, scale=default_scale(o, v))
+        self.root = ref_shim.REFERENCE_ROOT
+        ll, diis = ref_shim.load_reference()
+        with contextlib.redirect_stdout(io.StringIO()):
+            self.ref = ll.MPCC_LL(mf)
+        self.ref.t1 = np.zeros((o, v))
+        self.ref.t2 = np.zeros((o, o, v, v))
+        self.adiis = diis.DIIS()
+        self.trace = []
+
+    def step(self):
+        ref = self.ref
+        t0 = time.perf_counter()
+        res, dE, t1n, t2n = ref.updated_amps()
+        t_upd = time.perf_counter() - t0
+        ref.t1, ref.t2 = ref.run_diis(t1n, t2n, self.adiis)
+        dt = time.perf_counter() - t0
+        self.trace.append((float(dE), float(res)))
+        return dt, t_upd
+
+
+class PortSample:
+    """Fallback when the staged reference files are missing: the oracle's einsum port of the same loop."""
+
+    def __init__(self, o, v, L, seed):
+        from oracle.mpcc_oracle import LowLevelOracle, PulayDIIS
+        from pyscf_mpcc_b200.synthetic import SyntheticMF, default_scale
+        self.kind = "port"
+        self.shape = (o, v, L)
+        self.root = None
+        self.orc = LowLevelOracle(SyntheticMF(o, v, L, seed=seed, scale=default_scale(o, v)), mode="einsum")
+        self.orc.t1 = np.zeros((o, v))
+        self.adiis = PulayDIIS()
+        self.trace = []
+
+    def step(self):
+        orc = self.orc
+        t0 = time.perf_counter()
+        res, dE, t1n, t2n = orc.updated_amps()
+        t_upd = time.perf_counter() - t0
+        orc.t1, orc.t2 = orc.run_diis(t1n, t2n, self.adiis)
+        dt = time.perf_counter() - t0
+        self.trace.append((float(dE), float(res)))
+        return dt, t_upd
+
+
+def make_cpu_sample(o, v, L, seed):
+    from oracle import ref_shim
+    so, sv, sL = sample_shape(o, v, L)
+    if ref_shim.reference_available():
+        return ReferenceSample(so, sv, sL, seed)
+    return PortSample(so, sv, sL, seed)
+
+
+def blas_fair(o, v, L, seed):
+    """Not the reference: the same two O(L nov^2) contractions as multi-threaded GEMMs (OpenBLAS) on a slab of rows."""
+    from oracle.mpcc_oracle import doubles_sample
+    from pyscf_mpcc_b200.flops import updated_amps_flops
     rng = np.random.default_rng(seed)
     amp = 0.1 / np.sqrt(L)
     Jvo = rng.standard_normal((L, v, o)) * amp
     Lov = rng.standard_normal((L, o, v)) * amp
     eo = np.sort(rng.uniform(-2.0, -0.5, o))
     ev = np.sort(rng.uniform(0.3, 3.0, v))
-    return Jvo, Lov, eo, ev
-
-
-def cpu_step(inputs, na, mode):
-    """One bounded sample: the two O(L nov^2) contractions + t2 build on `na` virtual rows."""
-    from oracle.mpcc_oracle import doubles_sample
-    Jvo, Lov, eo, ev = inputs
+    na = max(1, min(v, 64))
+    doubles_sample(Jvo, Lov, eo, ev, 0, min(4, na), mode="blas")      # thread-pool warm-up
     t0 = time.perf_counter()
-    _, _, flops = doubles_sample(Jvo, Lov, eo, ev, 0, na, mode=mode)
-    return time.perf_counter() - t0, flops
-
-
-def cpu_baseline(o, v, L, seed):
-    from pyscf_mpcc_b200.flops import updated_amps_flops
-    inputs = cpu_sample_inputs(o, v, L, seed)
-    na_e = 1
-    dt_e, fl_e = cpu_step(inputs, na_e, "einsum")
-    na_b = max(1, min(v, 64))
-    cpu_step(inputs, min(4, na_b), "blas")          # thread-pool warm-up
-    dt_b, fl_b = cpu_step(inputs, na_b, "blas")
-    total = updated_amps_flops(o, v, L)
+    _, _, fl = doubles_sample(Jvo, Lov, eo, ev, 0, na, mode="blas")
+    dt = time.perf_counter() - t0
     try:
         import threadpoolctl
-        blas_threads = max((p.get("num_threads", 1) for p in threadpoolctl.threadpool_info()), default=1)
+        threads = max((p.get("num_threads", 1) for p in threadpoolctl.threadpool_info()), default=1)
     except Exception:
-        blas_threads = os.cpu_count()
+        threads = os.cpu_count()
+    return {"value": fl / dt * 1e-12, "unit": "TFLOP/s", "cores": int(threads),
+            "sample": f"eris+t2+Yvo as GEMMs (OpenBLAS) on {na} of {v} virtual rows of the full shape, {dt:.2f} s",
+            "s_per_iteration_extrapolated": updated_amps_flops(o, v, L) / (fl / dt),
+            "note": "not the reference: what a BLAS-backed CPU implementation would reach"}
+
+
+def cpu_baseline(o, v, L, seed, steps=3):
+    from pyscf_mpcc_b200.flops import updated_amps_flops
+    smp = make_cpu_sample(o, v, L, seed)
+    so, sv, sL = smp.shape
+    times = [smp.step() for _ in range(steps)]
+    dt = sum(t[0] for t in times) / steps
+    fl = updated_amps_flops(so, sv, sL)
+    rate = fl / dt
     return {
-        "value": fl_e / dt_e * 1e-12, "unit": "TFLOP/s", "cores": 1, "kind": "port",
-        "host_cores": os.cpu_count(),
-        "sample": (f"oracle einsum port of eris+t2+Yvo (dfrmpcc_lowlevel.py:135-138) on {na_e} of {v} virtual rows "
-                   f"({fl_e:.3g} flop, {dt_e:.2f} s); np.einsum is single-threaded as in the reference"),
-        "s_per_iteration_extrapolated": total / (fl_e / dt_e),
-        "blas_fair": {"value": fl_b / dt_b * 1e-12, "unit": "TFLOP/s", "cores": int(blas_threads),
-                      "sample": f"same contractions as GEMMs (OpenBLAS) on {na_b} of {v} virtual rows, {dt_b:.2f} s",
-                      "s_per_iteration_extrapolated": total / (fl_b / dt_b),
-                      "note": "not the reference: what a BLAS-backed CPU implementation would reach"},
+        "value": rate * 1e-12, "unit": "TFLOP/s", "cores": 1, "kind": smp.kind, "host_cores": os.cpu_count(),
+        "sample": (f"{'the reference MPCC_LL (dfrmpcc_lowlevel.py + lib/diis.py, unmodified, ' + str(smp.root) + ')' if smp.kind == 'reference' else 'oracle einsum port'}"
+                   f" at nocc={so} nvir={sv} naux={sL} (the workload's aspect ratio at 1/4 of every extent): {steps} x "
+                   f"[updated_amps() + run_diis()], {dt:.2f} s per step, {fl:.3g} flop per step; np.einsum runs on one core"),
+        "s_per_step_sample": dt,
+        "s_per_iteration_extrapolated_to_full_shape": updated_amps_flops(o, v, L) / rate,
+        "extrapolation": "flop-scaled from the sample rate; labelled, not measured",
+        "blas_fair": blas_fair(o, v, L, seed),
     }
 
 
 def run_reference(args):
-    """--impl reference: the reference's CPU path (oracle port) on bounded samples of the same workload."""
+    """--impl reference: the reference's own CPU implementation of the path (unmodified files) on the box's host
+    cores; every step is one iteration (updated_amps + run_diis) on the bounded sample shape."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     from pyscf_mpcc_b200.flops import updated_amps_flops
     o, v, L = args.nocc, args.nvir, args.naux
-    inputs = cpu_sample_inputs(o, v, L, args.seed)
-    na = 1
+    smp = make_cpu_sample(o, v, L, args.seed)
+    so, sv, sL = smp.shape
     for _ in range(args.warmup):
-        cpu_step(inputs, na, "einsum")
-    t, fl = 0.0, 0.0
+        smp.step()
+    t = 0.0
     for _ in range(args.steps):
-        dt, f = cpu_step(inputs, na, "einsum")
-        t += dt
-        fl += f
-    rate = fl / t * 1e-12
-    total = updated_amps_flops(o, v, L)
+        t += smp.step()[0]
+    fl = updated_amps_flops(so, sv, sL)
+    rate = fl * args.steps / t * 1e-12
     line = {
         "impl": "reference", "metric": "dfmpcc_iteration_fp64_tflops", "value": rate, "unit": "TFLOP/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": total / (rate * 1e12) * 1e3, "higher_is_better": True, "scaling": "strong",
+        "ms_per_step": t / args.steps * 1e3, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"synthetic DF-MPCC nocc={o} nvir={v} naux={L}",
-                   "ms_per_step_is": "extrapolated from the sample rate to one full iteration"},
-        "cpu_baseline": {"value": rate, "unit": "TFLOP/s", "cores": 1, "kind": "port", "host_cores": os.cpu_count(),
-                         "sample": f"per step: oracle einsum port of eris+t2+Yvo on {na} of {v} virtual rows "
-                                   f"({fl / args.steps:.3g} flop, {t / args.steps:.2f} s)"},
+        "config": {"workload": f"synthetic DF-MPCC nocc={o} nvir={v} naux={L} (BASELINE.json configs[2])",
+                   "sample": f"each step runs the workload's bounded sample nocc={so} nvir={sv} naux={sL} "
+                             "(same aspect ratio, 1/4 of every extent); ms_per_step is the measured time of that step",
+                   "step": "updated_amps + run_diis (iterations of a solve from t1=0, DIIS on)"},
+        "cpu_baseline": {"value": rate, "unit": "TFLOP/s", "cores": 1, "kind": smp.kind, "host_cores": os.cpu_count(),
+                         "sample": f"per step: MPCC_LL.updated_amps() + run_diis() of "
+                                   f"{'the unmodified reference files (' + str(smp.root) + ')' if smp.kind == 'reference' else 'the oracle einsum port'} "
+                                   f"at nocc={so} nvir={sv} naux={sL} ({fl:.3g} flop, {t / args.steps:.2f} s); "
+                                   "np.einsum runs on one core whatever the host has"},
+        "s_per_iteration_extrapolated_to_full_shape": updated_amps_flops(o, v, L) / (rate * 1e12),
+        "extrapolation": "flop-scaled from the sample rate to the full workload; labelled, not measured",
         "e2e": {"value": rate, "unit": "TFLOP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
+        "trace_dE_res": smp.trace[-args.steps:],
     }
     print(json.dumps(line), flush=True)
 
 
 # ---------------------------------------------------------------------------------------------
+# parity of the timed trace against the committed fixtures
+# ---------------------------------------------------------------------------------------------
+def parity_vs_fixture(o, v, L, seed, trace):
+    """Compare the (dE, res) of the timed steps with (1) the oracle's trace on the same inputs for the iterations the
+    oracle ran and (2) the committed one-rank GPU trace for the rest. None when the shape has no fixture."""
+    if seed != 0:
+        return None, {"reason": "fixtures are for seed 0"}
+    orc_path = os.path.join(GOLDEN, f"trace_{o}_{v}_{L}.npz")
+    gpu_path = os.path.join(GOLDEN, f"bench_trace_{o}_{v}_{L}.json")
+    if not os.path.isfile(orc_path) and not os.path.isfile(gpu_path):
+        return None, {"reason": "no fixture for this shape"}
+    orc = np.load(orc_path) if os.path.isfile(orc_path) else None
+    gpu = None
+    if os.path.isfile(gpu_path):
+        with open(gpu_path) as f:
+            gpu = json.load(f)["trace_dE_res"]
+    n_orc = len(orc["trace_dE"]) if orc is not None else 0
+    ok, worst_dE, worst_res, compared = True, 0.0, 0.0, 0
+    for k, (dE, res) in enumerate(trace):
+        if k < n_orc:
+            ref_dE, ref_res, floor = float(orc["trace_dE"][k]), float(orc["trace_res"][k]), 1e-12
+        elif gpu is not None and k < len(gpu):
+            ref_dE, ref_res, floor = gpu[k][0], gpu[k][1], 1e-9      # converged: res is at the rounding floor
+        else:
+            break
+        d_e = abs(dE - ref_dE)
+        d_r = abs(res - ref_res)
+        worst_dE = max(worst_dE, d_e)
+        worst_res = max(worst_res, d_r / max(ref_res, 1e-300) if d_r > floor else 0.0)
+        ok = ok and d_e <= 1e-8 and d_r <= 1e-6 * ref_res + floor
+        compared += 1
+    detail = {"steps_compared": compared, "steps_vs_oracle": min(n_orc, len(trace)),
+              "max_abs_dE_diff": worst_dE, "max_rel_res_diff_above_floor": worst_res,
+              "tolerance": "|dE| <= 1e-8 Eh; |res - ref| <= 1e-6 ref (+1e-12 vs the oracle, +1e-9 vs the one-rank trace once converged)",
+              "fixtures": [os.path.relpath(p, ROOT) for p in (orc_path, gpu_path) if os.path.isfile(p)]}
+    return bool(ok and compared > 0), detail
+
+
+# ---------------------------------------------------------------------------------------------
 # GPU arm
 # ---------------------------------------------------------------------------------------------
+def fp64_yardstick(ll, clock_index):
+    """cuBLAS DGEMM rate of this rank's Yvo product — C[(a,i), L] = T[(a,i), (b,j)] . Lvo[L, (b,j)]^T — on the
+    solver's own buffers (whatever they hold: only the rate matters). A yardstick, not part of the product path."""
+    import torch
+    o, v, L, na = ll.nocc, ll.nvir, ll.naux, ll._na
+    nov = o * v
+    A = ll._T[:na * o * nov].view(na * o, nov)
+    p, n = ll._ctx.buffer("Lvo")
+    off = p - ll._ws.data_ptr()
+    B = ll._ws[off:off + n * 8].view(torch.float64).view(L, nov)
+    sampler = ClockSampler(clock_index) if clock_index is not None else None
+    C = torch.empty((na * o, L), dtype=torch.float64, device=ll.device)
+    for _ in range(2):
+        torch.matmul(A, B.t(), out=C)
+    torch.cuda.synchronize()
+    if sampler:
+        sampler.start()
+    times = []
+    for _ in range(4):
+        e0 = torch.cuda.Event(enable_timing=True)
+        e1 = torch.cuda.Event(enable_timing=True)
+        e0.record()
+        torch.matmul(A, B.t(), out=C)
+        e1.record()
+        e1.synchronize()
+        times.append(e0.elapsed_time(e1))
+    clocks = sampler.stop() if sampler else None
+    fl = 2.0 * na * o * float(nov) * L
+    del C
+    return {"tflops": fl / (min(times) * 1e-3) * 1e-12, "tflops_mean": fl / (sum(times) / len(times) * 1e-3) * 1e-12,
+            "ms_best": min(times), "shape_mnk": [na * o, L, nov], "how": "torch.matmul float64 (cuBLAS DGEMM), best of 4 after 2 warm-up",
+            "clocks": clocks}
+
+
 def run_b200(args):
     import torch
     import torch.distributed as dist
     from pyscf_mpcc_b200 import flops as F
     from pyscf_mpcc_b200.diis import DIIS
     from pyscf_mpcc_b200.lowlevel import MPCC_LL
-    from pyscf_mpcc_b200.synthetic import device_blocks, default_scale
+    from pyscf_mpcc_b200.synthetic import host_blocks, default_scale
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -220,8 +380,10 @@ def run_b200(args):
     o, v, L = args.nocc, args.nvir, args.naux
     K, W = args.steps, args.warmup
 
-    # synthetic DF tensors generated on the device (same seed on every rank -> replicated inputs)
-    Loo, Lov, Lvv, eo, ev = device_blocks(o, v, L, seed=args.seed, scale=default_scale(o, v), device=dev)
+    # synthetic DF tensors from the seeded host generator of the fixtures (same seed on every rank -> replicated
+    # inputs; reproducible by the CPU oracle), uploaded once before anything is timed
+    Loo, Lov, Lvv, eo, ev = (torch.from_numpy(x).to(dev) for x in
+                             host_blocks(o, v, L, seed=args.seed, scale=default_scale(o, v)))
     foo = torch.diag(eo)
     fvv = torch.diag(ev)
     ll = MPCC_LL(blocks=(Loo, Lov, Lvv, foo, fvv, torch.cat([eo, ev])), device=dev, use_tma=not args.no_tma,
@@ -290,6 +452,10 @@ def run_b200(args):
     clocks = sampler.stop() if rank == 0 else None
     h2d, d2h = ll.h2d_bytes / K, ll.d2h_bytes / K + 7 * 8
 
+    # ---- FP64 yardstick measured in this run (outside the timed region): cuBLAS DGEMM of the Yvo product of this
+    # rank's slab, (na*o x nov) . (nov x naux), through torch.matmul on the solver's own buffers ----
+    yard = fp64_yardstick(ll, local if rank == 0 else None)
+
     flop_it = F.updated_amps_flops(o, v, L)
     tflops = flop_it * K / (ms_dev * 1e-3) * 1e-12
     tflops_e2e = flop_it * K / (ms_e2e * 1e-3) * 1e-12
@@ -307,21 +473,22 @@ def run_b200(args):
     traffic = ncu_traffic(o, v, L, world) or {}
     eris_info = {"kernel": ("gemm_tma_kernel<1,WN>" if not args.no_tma else "gemm_t2_kernel")
                            + " (fused eris -> t2 with mirror scheme, TMA-fed DMMA.8x8x4)",
-                 "achieved": er_tf, "frac": er_tf / FP64_PEAK_TFLOPS_MEASURED,
+                 "achieved": er_tf, "frac": er_tf / yard["tflops"],
                  "frac_of_nominal": er_tf / FP64_PEAK_TFLOPS_NOMINAL, "ms_per_launch": er_ms / max(er_n, 1),
                  "flops_counted": "executed: eris is a Gram matrix, the kernel computes one tile of every mirror pair "
                                   f"({launched} of {total_tiles} tiles) and writes both t2 blocks",
                  "algorithmic_tflops": er_tf_alg, "traffic": traffic.get("eris_t2_bytes")}
     yvo_info = {"kernel": "gemm_tma_kernel<0,4> (Yvo = t2 . Lov, TMA-fed DMMA.8x8x4, 4-D tensor map over t2)",
-                "achieved": yv_tf, "frac": yv_tf / FP64_PEAK_TFLOPS_MEASURED,
+                "achieved": yv_tf, "frac": yv_tf / yard["tflops"],
                 "frac_of_nominal": yv_tf / FP64_PEAK_TFLOPS_NOMINAL, "ms_per_launch": yv_ms / max(yv_n, 1),
                 "traffic": traffic.get("yvo_bytes")}
     dom, other = (yvo_info, eris_info) if yv_ms >= er_ms else (eris_info, yvo_info)
     roofline = {
-        "bound": "tensor", "kernel": dom["kernel"], "achieved": dom["achieved"], "peak": FP64_PEAK_TFLOPS_MEASURED,
+        "bound": "tensor", "kernel": dom["kernel"], "achieved": dom["achieved"], "peak": yard["tflops"],
         "unit": "TFLOP/s", "frac": dom["frac"], "traffic": dom["traffic"],
-        "peak_source": "cuBLAS DGEMM 32768x8192x1536 measured on this pool's B200 (FP64; MEASURED_PEAKS.json has "
-                       "only bf16); nominal 37.2",
+        "peak_source": "cuBLAS DGEMM (torch.matmul f64) of the Yvo product, measured in this run outside the timed "
+                       "region (MEASURED_PEAKS.json has no FP64 entry); nominal 148 SM x 64 DFMA/clk x 1.965 GHz = 37.2",
+        "peak_measured_here": yard, "peak_nominal": FP64_PEAK_TFLOPS_NOMINAL,
         "frac_of_nominal": dom["frac_of_nominal"], "ms_per_launch": dom["ms_per_launch"],
         "second_kernel": other,
         "stages_ms_per_step": {k: s[0] / K for k, s in stages.items()},
@@ -334,6 +501,12 @@ def run_b200(args):
         if world > 1:
             dist.destroy_process_group()
         return
+    parity_ok, parity_detail = parity_vs_fixture(o, v, L, args.seed, trace[:K])
+    if args.write_trace:
+        with open(args.write_trace, "w") as f:
+            json.dump({"shape": [o, v, L], "seed": args.seed, "n_gpus": world, "steps": K,
+                       "inputs": "pyscf_mpcc_b200.synthetic.host_blocks(seed=0, scale=default_scale)",
+                       "trace_dE_res": trace[:K]}, f)
     line = {
         "metric": "dfmpcc_iteration_fp64_tflops", "value": tflops, "unit": "TFLOP/s",
         "n_gpus": world, "steps": K, "warmup": max(W, 3), "ms_per_step": ms_dev / K,
@@ -342,6 +515,7 @@ def run_b200(args):
         "config": {"workload": f"synthetic DF-MPCC nocc={o} nvir={v} naux={L} (BASELINE.json configs[2])",
                    "step": "updated_amps + run_diis (first K iterations of a solve from t1=0, DIIS on)",
                    "l2": "inputs_exceed_l2 (t2 buffer 8.6 GB, DIIS vectors 4.3 GB each at the default shape)",
+                   "inputs": "pyscf_mpcc_b200.synthetic.host_blocks (seeded host generator of the fixtures), uploaded before the timed region",
                    "parallelism": f"a-slab x{world}", "slab_bounds": list(ll._bounds) if world > 1 else None,
                    "diis_vector": "column-owned" if ll._diis_columns else "row-owned", "jk_exchange": ll._jk_mode, "t2_peer_mirror": bool(ll._t2_peers),
                    "flop_per_iteration": flop_it,
@@ -353,6 +527,8 @@ def run_b200(args):
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": roofline,
+        "parity_vs_fixture": parity_ok,
+        "parity_detail": parity_detail,
         "trace_dE_res": trace[:K],
     }
     if world == 1 and not args.no_cpu_baseline:

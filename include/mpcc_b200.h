@@ -178,6 +178,9 @@ int mpccb_class_overwrite(mpccb_ctx* ctx, double* tnew_dev, const double* told_d
                           const int* act_h_dev, const int* act_p_dev, unsigned class_mask);
 /* out_dev[0] = x . y (deterministic two-pass reduction) */
 int mpccb_dot(mpccb_ctx* ctx, const double* x_dev, const double* y_dev, long long n, double* out_dev);
+/* test hook: q[i] = x[i] / y[i] with the branch-free quotient of the fused t2 epilogue (replaces the IEEE division of
+ * dfrmpcc_lowlevel.py:137; within 1 ulp for normal denominators — tests/test_gpu_parity.py sweeps it) */
+int mpccb_test_fast_div(mpccb_ctx* ctx, const double* x_dev, const double* y_dev, double* q_dev, long long n);
 
 #ifdef __cplusplus
 }

@@ -164,9 +164,16 @@ class PulayDIIS:
             self.B[k + 1, self.head] = d
         c = self.solve(self.B[:nd + 1, :nd + 1])
         self.last_coeff = c
+        # xnew = sum_k xs[k] * c[k+1] in slot order (diis.py:268-275), formed block by block so that no vector-sized
+        # temporary exists (same products, same order of additions: bit-identical to the whole-array form)
         xnew = np.zeros_like(x)
-        for k in range(nd):
-            xnew += self.xs[k] * c[k + 1]
+        step = 1 << 22
+        buf = np.empty(min(step, x.size))
+        for lo in range(0, x.size, step):
+            hi = min(lo + step, x.size)
+            for k in range(nd):
+                np.multiply(self.xs[k][lo:hi], c[k + 1], out=buf[:hi - lo])
+                xnew[lo:hi] += buf[:hi - lo]
         self.xprev = xnew
         return xnew
 
@@ -366,6 +373,75 @@ class LowLevelOracle:
         dE = float(es("Lai,Lai", e1, Y))
         res = float(np.linalg.norm(t1 + Om.T / self.eia))
         return res, dE, -Om.T / self.eia, t2
+
+    def updated_amps_packed(self, t1=None, slab=32):
+        """``updated_amps`` (:103-152) followed by ``amplitudes_to_vector`` (:162-168) for shapes whose t2 (8.6 GB at
+        (64,512,1536)) should not be held next to ``eris``: the doubles part runs over slabs of ``slab`` values of
+        the first virtual index — ``eris``, ``t2``, ``Yvo`` rows and the rows of the (nov x nov) matrix the DIIS
+        vector packs are all slab-local. GEMM-shaped arithmetic as ``mode="blas"``; agrees with
+        ``_updated_amps_blas`` to rounding (``tests/test_oracle_golden.py::test_packed_form_equals_plain``).
+
+        Returns (res, dE, t1_new, vec, t2_sumsq) with ``vec = [t1_new | tril(M)]`` the reference's DIIS vector.
+        """
+        if t1 is None:
+            t1 = self.t1
+        o, v, L = self.nocc, self.nvir, self.naux
+        nov = o * v
+        Loo, Lov, Lvv = self.Loo, self.Lov, self.Lvv
+        Xvo = (Lvv.reshape(L * v, v) @ t1.T).reshape(L, v, o)
+        Xoo = (Lov.reshape(L * o, v) @ t1.T).reshape(L, o, o)
+        X = Lov.reshape(L, o * v) @ t1.reshape(o * v)
+        Joo = Xoo + Loo
+        Joo_t1 = (Joo.reshape(L * o, o) @ t1).reshape(L, o, v)
+        Jvo = Xvo + Lov.transpose(0, 2, 1) - Joo_t1.transpose(0, 2, 1)
+        del Joo_t1
+        Xoo_t1 = (Xoo.reshape(L * o, o) @ t1).reshape(L, o, v)
+        W = Xoo_t1.transpose(0, 2, 1) - Xvo
+        Om = np.einsum("Laj,Lji->ai", W, Joo, optimize=True)
+        del W
+        JvoX = np.tensordot(X, Jvo, axes=(0, 0))
+        Om += JvoX
+        Om += (t1 @ self.fvv).T
+        Om -= (self.foo @ t1).T
+        Fov = JvoX.T - np.einsum("Lij,Lib->jb", Xoo, Lov, optimize=True)
+        Jm = np.ascontiguousarray(Jvo.reshape(L, nov))
+        eo = self.mo_energy[:o]
+        ev = self.mo_energy[o:]
+        Lvo_flat = np.ascontiguousarray(Lov.transpose(0, 2, 1)).reshape(L, nov)
+        Fvo_flat = np.ascontiguousarray(Fov.T).reshape(nov)
+        Y = np.zeros((L, v, o))
+        vec = np.empty(nov + nov * (nov + 1) // 2)
+        t2_sumsq = 0.0
+        for a0 in range(0, v, slab):
+            a1 = min(a0 + slab, v)
+            na = a1 - a0
+            eris = (Jm[:, a0 * o:a1 * o].T @ Jm).reshape(na, o, v, o)               # [a,i,b,j] (:135)
+            denom = (eo[None, :, None, None] + eo[None, None, None, :]
+                     - ev[a0:a1, None, None, None] - ev[None, None, :, None])
+            t2 = (2.0 * eris - eris.transpose(0, 3, 2, 1)) / denom                   # (:137)
+            del eris, denom
+            t2m = t2.reshape(na * o, nov)
+            Y[:, a0:a1, :] = (Lvo_flat @ t2m.T).reshape(L, na, o)                     # (:138)
+            Om[a0:a1, :] += (t2m @ Fvo_flat).reshape(na, o)                           # (:139)
+            t2_sumsq += float(np.vdot(t2m, t2m))
+            # rows a0*o .. a1*o of M = t2.transpose(0,2,1,3) read as (nov, nov)  (:166)
+            rows = np.ascontiguousarray(t2.transpose(0, 2, 1, 3)).reshape(na * o, nov)
+            del t2, t2m
+            for q in range(na * o):
+                r = a0 * o + q
+                p0 = nov + r * (r + 1) // 2
+                vec[p0:p0 + r + 1] = rows[q, :r + 1]
+            del rows
+        Om += np.einsum("Lba,Lbi->ai", Lvv, Y, optimize=True)                         # Jvv = Lov.t1 + Lvv (:141-142)
+        Z = np.einsum("Ljb,Lbi->ji", Lov, Y, optimize=True)
+        Om += t1.T @ Z
+        Om -= np.einsum("Lji,Laj->ai", Joo, Y, optimize=True)                         # (:143)
+        e1 = Xoo_t1.transpose(0, 2, 1) + X[:, None, None] * t1.T[None, :, :] + Jvo    # (:146)
+        dE = float(np.vdot(e1, Y))
+        upd = Om.T / self.eia
+        res = float(np.linalg.norm(t1 + upd))
+        vec[:nov] = (-upd).reshape(-1)
+        return res, dE, -upd, vec, t2_sumsq
 
     # -- :72-100, :155-160 -------------------------------------------------
     def run_diis(self, t1, t2, adiis):

@@ -5,10 +5,13 @@ Runs ``/root/reference/pyscf/mpcc/dfrmpcc_lowlevel.py`` and
 fake ``pyscf`` / ``pyscf.lib`` package in ``sys.modules`` (real PySCF cannot be
 imported in this image: no h5py, no compiled ``libnp_helper``).
 
-``/root/reference`` exists only in the build container, never on the GPU box:
-only ``tests/golden/generate_golden.py`` (run here, output committed) and the
-``not gpu`` tests that re-validate the oracle (skipped when the tree is absent)
-may call :func:`load_reference`. Nothing under ``pyscf_mpcc_b200/`` imports this.
+``/root/reference`` exists only in the build container, never on the GPU box.
+There the five hot-path files staged by ``oracle/make_ref.py`` under ``oracle/_ref/``
+(git-ignored, shipped with the snapshot) are executed instead — the same bytes.
+Callers: ``tests/golden/generate_golden*.py`` (run here, output committed), the tests
+that re-validate the oracle or drive the reference's solver object through the GPU
+module, and the ``--impl reference`` / ``cpu_baseline`` legs of ``bench.py``.
+Nothing under ``pyscf_mpcc_b200/`` imports this.
 
 The fake helpers restate:
   * ``lib.pack_tril``   — ``pyscf/lib/numpy_helper.py:256-294`` + ``np_helper/pack_tril.c:99-107``
@@ -25,11 +28,30 @@ import types
 
 import numpy as np
 
-REFERENCE_ROOT = os.environ.get("MPCC_REFERENCE_ROOT", "/root/reference")
+_STAGED_ROOT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref")
+
+
+def _pick_root() -> str:
+    """MPCC_REFERENCE_ROOT, else the reference tree of the build container, else the staged copy (oracle/make_ref.py)."""
+    env = os.environ.get("MPCC_REFERENCE_ROOT")
+    if env:
+        return env
+    for root in ("/root/reference", _STAGED_ROOT):
+        if os.path.isfile(os.path.join(root, "pyscf", "mpcc", "dfrmpcc_lowlevel.py")):
+            return root
+    return "/root/reference"
+
+
+REFERENCE_ROOT = _pick_root()
 
 
 def reference_available() -> bool:
     return os.path.isfile(os.path.join(REFERENCE_ROOT, "pyscf", "mpcc", "dfrmpcc_lowlevel.py"))
+
+
+def full_tree_available() -> bool:
+    """True when the whole reference tree is there (build container), not only the staged hot-path files."""
+    return os.path.isfile(os.path.join(REFERENCE_ROOT, "pyscf", "cc", "rmpccsd_slow.py"))
 
 
 def _tril_pack(mat, axis=-1, out=None):
@@ -86,6 +108,17 @@ class _MemFile(dict):
 
 _loaded = None
 _loaded_cc = None
+_loaded_solver = None
+
+
+def load_reference_solver():
+    """The reference's solver-object module ``pyscf/mpcc/mpcc.py`` (class ``MPCC(mf, lowlevel)``, :3-17), executed
+    unmodified. ``MPCC(mf, module)`` instantiates ``module.MPCC_LL(mf)``, pokes ``con_tol``/``max_its`` and runs
+    ``kernel()`` — the plug-in seam the GPU module is a drop-in for."""
+    load_reference()
+    if isinstance(_loaded_solver, Exception) or _loaded_solver is None:
+        raise _loaded_solver if _loaded_solver is not None else RuntimeError("reference solver module not loaded")
+    return _loaded_solver
 
 
 def _direct_sum_general(spec, *ops):
@@ -164,6 +197,11 @@ def load_reference():
     diis = run("pyscf.lib.diis", "lib/diis.py")
     lib.diis = diis
     lowlevel = run("pyscf.mpcc.dfrmpcc_lowlevel", "mpcc/dfrmpcc_lowlevel.py")
+    global _loaded_solver
+    try:
+        _loaded_solver = run("pyscf.mpcc.mpcc", "mpcc/mpcc.py")
+    except Exception as exc:
+        _loaded_solver = exc
     # CCSD-type residual of the high-level stage (rows f1/f2): rintermediates.py and rmpccsd_slow.py, unmodified.
     # Everything they import besides numpy is faked: lib.einsum/direct_sum/dot, an empty ao2mo, a stub ccsd.CCSD.
     global _loaded_cc

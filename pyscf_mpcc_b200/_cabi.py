@@ -69,6 +69,7 @@ SIGNATURES = {
                                   c_double_p]),
     "mpccb_class_overwrite": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, ctypes.c_uint]),
     "mpccb_dot": (c_int, [c_void_p, c_void_p, c_void_p, c_ll, c_void_p]),
+    "mpccb_test_fast_div": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_ll]),
     "mpccb_gemm_nt": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int]),
 }
 

@@ -69,6 +69,9 @@ struct mpccb_ctx {
   int profile;
   std::vector<cudaEvent_t>* prof_ev;   // [stage] -> start/stop pairs
   int prof_used[16];
+  // kernels whose dynamic-shared-memory opt-in was already set for THIS context's device. The attribute is per
+  // device, so a process-wide flag would leave a second GPU of the same process without it.
+  std::vector<const void*>* attr_set;
 };
 
 enum Stage { ST_DRESS = 0, ST_DRESS_POST, ST_ERIS_T2, ST_YVO, ST_SINGLES_FROM_Y, ST_FINISH, ST_DIIS_PUSH, ST_DIIS_COMBINE, ST_COUNT };
@@ -85,6 +88,28 @@ int fail(mpccb_ctx* c, const char* fmt, ...) {
     va_end(ap);
   }
   return 1;
+}
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize (and optionally the carve-out preference) once per context and kernel
+cudaError_t ensure_smem_attr(mpccb_ctx* c, const void* func, size_t smem, bool prefer_smem) {
+  for (const void* f : *c->attr_set)
+    if (f == func) return cudaSuccess;
+  cudaError_t e = cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  if (prefer_smem) {
+    e = cudaFuncSetAttribute(func, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+    if (e != cudaSuccess) return e;
+  }
+  c->attr_set->push_back(func);
+  return cudaSuccess;
+}
+
+// every entry point that launches work runs on the context's device, whatever the caller's current device is
+cudaError_t enter_device(const mpccb_ctx* c) {
+  int cur = -1;
+  cudaError_t e = cudaGetDevice(&cur);
+  if (e != cudaSuccess) return e;
+  return cur == c->device ? cudaSuccess : cudaSetDevice(c->device);
 }
 
 struct StageTimer {
@@ -168,12 +193,7 @@ int launch_gemm(mpccb_ctx* c, const char* what, const Operand& A, const Operand&
     C = flat_output(partial, N, 1);
     C.split_stride = (i64)M * N;
   }
-  static bool attr_done = false;
-  if (!attr_done) {
-    CUDA_OK(c, cudaFuncSetAttribute(gemm_store_kernel<Cfg>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    (int)Cfg::MAIN_SMEM));
-    attr_done = true;
-  }
+  CUDA_OK(c, ensure_smem_attr(c, reinterpret_cast<const void*>(&gemm_store_kernel<Cfg>), Cfg::MAIN_SMEM, false));
   dim3 grid(d.tiles_m * d.tiles_n, 1, splits);
   gemm_store_kernel<Cfg><<<grid, Cfg::NTH, Cfg::MAIN_SMEM, c->stream>>>(A, B, C, d);
   LAUNCH_OK(c, what);
@@ -405,7 +425,15 @@ int mpccb_create(mpccb_ctx** out, int nocc, int nvir, int naux, int a_begin, int
   *out = c;   // returned even on failure so the caller can read the message
   if (nocc <= 0 || nvir <= 0 || naux <= 0) return fail(c, "sizes must be positive");
   if (a_begin < 0 || a_end > nvir || a_begin >= a_end) return fail(c, "bad slab [%d,%d) of %d", a_begin, a_end, nvir);
-  if ((i64)nocc * nvir * (i64)nocc * nvir / nocc > (i64)INT_MAX) return fail(c, "problem too large for 32-bit row indices");
+  // explicit limits of the index arithmetic (rows and tile ids are 32-bit, element offsets 64-bit):
+  //   nov <= 2^21            residual-norm scratch of mpccb_finish (8000 blocks of 256) and 32-bit GEMM row indices
+  //   nocc <= 2^15           umulhi index split of the fused epilogue
+  //   nov * ldk, nov * nov   < 2^62 as byte counts (always true under the nov limit; kept for the record)
+  //   (na*nvir) block count and (tiles_m * tiles_n) tile count of the eris launch < 2^31 (checked after the geometry)
+  const i64 nov64 = (i64)nocc * nvir;
+  if (nov64 > ((i64)1 << 21)) return fail(c, "nocc*nvir = %lld exceeds the supported 2^21", (long long)nov64);
+  if (nocc > (1 << 15)) return fail(c, "nocc = %d exceeds the supported 2^15", nocc);
+  if ((i64)naux > ((i64)1 << 24)) return fail(c, "naux = %d exceeds the supported 2^24", naux);
   c->o = nocc; c->v = nvir; c->L = naux; c->device = device;
   c->a_begin = a_begin; c->a_end = a_end; c->na = a_end - a_begin;
   c->nov = (i64)nocc * nvir;
@@ -413,7 +441,10 @@ int mpccb_create(mpccb_ctx** out, int nocc, int nvir, int naux, int a_begin, int
   c->use_tma = 1;
   c->profile = 0;
   c->prof_ev = new std::vector<cudaEvent_t>[ST_COUNT];
+  c->attr_set = new std::vector<const void*>();
   set_t2_geometry(c, 0);
+  if ((i64)c->t2_tiles_m * c->t2_tiles_n > (i64)INT_MAX || (i64)c->na * nvir > (i64)INT_MAX)
+    return fail(c, "eris launch would exceed 2^31 tiles");
   CUDA_OK(c, cudaSetDevice(device));
   c->ws_bytes = 0;
   return 0;
@@ -426,6 +457,7 @@ void mpccb_destroy(mpccb_ctx* ctx) {
       for (cudaEvent_t e : ctx->prof_ev[s]) cudaEventDestroy(e);
     delete[] ctx->prof_ev;
   }
+  delete ctx->attr_set;
   if (ctx->side) {
     cudaStreamDestroy(ctx->side);
     cudaEventDestroy(ctx->ev_fork);
@@ -439,6 +471,7 @@ const char* mpccb_profile_stage_name(int stage) { return (stage >= 0 && stage < 
 
 // synchronises, then returns per-stage summed milliseconds and launch-group counts since the last read
 int mpccb_profile_read(mpccb_ctx* c, double* ms_out, long long* count_out) {
+  CUDA_OK(c, enter_device(c));
   CUDA_OK(c, cudaStreamSynchronize(c->stream));
   for (int s = 0; s < ST_COUNT; ++s) {
     double tot = 0.0;
@@ -499,6 +532,7 @@ size_t mpccb_workspace_bytes(const mpccb_ctx* c) {
 }
 
 int mpccb_bind_workspace(mpccb_ctx* c, void* ws, size_t bytes) {
+  CUDA_OK(c, enter_device(c));
   const size_t need = mpccb_workspace_bytes(c);
   if (bytes < need) return fail(c, "workspace too small: %zu < %zu", bytes, need);
   if ((reinterpret_cast<uintptr_t>(ws) & 255) != 0) return fail(c, "workspace must be 256-byte aligned");
@@ -513,6 +547,7 @@ int mpccb_bind_workspace(mpccb_ctx* c, void* ws, size_t bytes) {
 
 int mpccb_bind_integrals(mpccb_ctx* c, const double* Loo, const double* Lov, const double* Lvv,
                          const double* foo, const double* fvv, const double* eo, const double* ev) {
+  CUDA_OK(c, enter_device(c));
   if (!c->ws) return fail(c, "bind the workspace first");
   c->Loo = Loo; c->Lov = Lov; c->Lvv = Lvv; c->foo = foo; c->fvv = fvv; c->eo = eo; c->ev = ev;
   // Lvo[L][b][j] = Lov[L][j][b]
@@ -574,6 +609,7 @@ extern "C" int mpccb_dress_post(mpccb_ctx* c);
 // replicated (2 x 2 L o^2 v flop). With several ranks the caller all-gathers the JK rows and then
 // calls mpccb_dress_post; on one rank mpccb_dress runs the post part itself.
 extern "C" int mpccb_dress(mpccb_ctx* c, const double* t1_dev) {
+  CUDA_OK(c, enter_device(c));
   if (!c->ws || !c->Lov) return fail(c, "workspace/integrals not bound");
   const int o = c->o, v = c->v, L = c->L, a0 = c->a_begin, na = c->na;
   const i64 nov = c->nov;
@@ -654,6 +690,7 @@ extern "C" int mpccb_dress(mpccb_ctx* c, const double* t1_dev) {
 
 // Needs every row of JK (all-gathered over the ranks): w = Jvo.X for all (b,j), Fvo = w - F2.
 extern "C" int mpccb_dress_post(mpccb_ctx* c) {
+  CUDA_OK(c, enter_device(c));
   if (!c->ws || !c->Lov) return fail(c, "workspace/integrals not bound");
   StageTimer timer(c, ST_DRESS_POST);
   const i64 nov = c->nov;
@@ -713,12 +750,7 @@ int launch_tma(mpccb_ctx* c, const char* what, const CUtensorMap& mA, const CUte
                const TmaGemmParams& p, const T2Params& t2p) {
   typedef TmaCfg<WN> Cfg;
   const size_t smem = (EPI == 1 ? (size_t)Cfg::AREA_EPI1 : (size_t)Cfg::RING_BYTES) + TMA_BAR_BYTES;
-  static bool attr_done = false;
-  if (!attr_done) {
-    CUDA_OK(c, cudaFuncSetAttribute(gemm_tma_kernel<EPI, WN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    CUDA_OK(c, cudaFuncSetAttribute(gemm_tma_kernel<EPI, WN>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
-    attr_done = true;
-  }
+  CUDA_OK(c, ensure_smem_attr(c, reinterpret_cast<const void*>(&gemm_tma_kernel<EPI, WN>), smem, true));
   SymInfo sym;
   memset(&sym, 0, sizeof(sym));
   int grid = p.tiles_total > 0 ? p.tiles_total : p.tiles_m * p.tiles_n;
@@ -890,12 +922,7 @@ int launch_eris_t2(mpccb_ctx* c) {
   d.tm_eff = c->t2_na * o; d.tn_eff = c->t2_nb * o;
   d.tiles_m = c->t2_tiles_m; d.tiles_n = c->t2_tiles_n;
   d.kchunk = L;
-  static bool attr_done = false;
-  if (!attr_done) {
-    CUDA_OK(c, cudaFuncSetAttribute(gemm_t2_kernel<Cfg>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    (int)T2Smem<Cfg>::BYTES));
-    attr_done = true;
-  }
+  CUDA_OK(c, ensure_smem_attr(c, reinterpret_cast<const void*>(&gemm_t2_kernel<Cfg>), T2Smem<Cfg>::BYTES, false));
   gemm_t2_kernel<Cfg><<<d.tiles_m * d.tiles_n, Cfg::NTH, T2Smem<Cfg>::BYTES, c->stream>>>(A, B, p, d);
   LAUNCH_OK(c, "gemm_t2_kernel");
   return 0;
@@ -919,6 +946,7 @@ int launch_yvo(mpccb_ctx* c) {
 }  // namespace
 
 extern "C" int mpccb_doubles_begin(mpccb_ctx* c, double* red_dev) {
+  CUDA_OK(c, enter_device(c));
   if (!c->T) return fail(c, "t2 buffer not bound");
   const int o = c->o, na = c->na;
   const i64 nov = c->nov;
@@ -953,6 +981,7 @@ extern "C" int mpccb_doubles(mpccb_ctx* c, double* red_dev) {
 }
 
 extern "C" int mpccb_doubles_end(mpccb_ctx* c, double* red_dev) {
+  CUDA_OK(c, enter_device(c));
   if (!c->T) return fail(c, "t2 buffer not bound");
   const int o = c->o, v = c->v, L = c->L, na = c->na;
   const i64 nov = c->nov;
@@ -1002,6 +1031,7 @@ extern "C" int mpccb_doubles_end(mpccb_ctx* c, double* red_dev) {
 // phase 3: T1 update (reference :128-131, :149-151)
 // ===========================================================================
 extern "C" int mpccb_finish(mpccb_ctx* c, const double* red_dev, double* t1_new_dev, double* scal_dev) {
+  CUDA_OK(c, enter_device(c));
   StageTimer timer(c, ST_FINISH);
   const i64 nov = c->nov;
   const int nb = cdiv(nov, 256);
@@ -1017,6 +1047,7 @@ extern "C" int mpccb_finish(mpccb_ctx* c, const double* red_dev, double* t1_new_
 
 extern "C" int mpccb_updated_amps_host(mpccb_ctx* c, const double* t1_host, double* t1_new_host,
                                        double* res_host, double* dE_host) {
+  CUDA_OK(c, enter_device(c));
   const i64 nov = c->nov;
   CUDA_OK(c, cudaMemcpyAsync(c->t1, t1_host, sizeof(double) * nov, cudaMemcpyHostToDevice, c->stream));
   if (c->na != c->v) return fail(c, "mpccb_updated_amps_host works on a whole-range context (one rank)");
@@ -1037,6 +1068,7 @@ extern "C" int mpccb_updated_amps_host(mpccb_ctx* c, const double* t1_host, doub
 // amplitude <-> vector layouts, DIIS algebra
 // ===========================================================================
 extern "C" int mpccb_t2_to_aibj(mpccb_ctx* c, double* out_dev) {
+  CUDA_OK(c, enter_device(c));
   if (!c->T) return fail(c, "t2 buffer not bound");
   const i64 total = (i64)c->na * c->v * c->o * c->o;
   const int nb = (int)std::min<i64>(cdiv(total, 256), 148 * 16);
@@ -1067,6 +1099,7 @@ extern "C" int mpccb_bind_diis_columns(mpccb_ctx* c, const long long* prefix_dev
 }
 
 extern "C" int mpccb_pack_tril_rows(mpccb_ctx* c, double* seg_dev) {
+  CUDA_OK(c, enter_device(c));
   if (!c->T) return fail(c, "t2 buffer not bound");
   if (c->diis_prefix) {                      // column-owned order; seg_dev is the t2 part (vector + nov)
     DiisPtrs ep = {};
@@ -1078,12 +1111,14 @@ extern "C" int mpccb_pack_tril_rows(mpccb_ctx* c, double* seg_dev) {
 }
 
 extern "C" int mpccb_diis_scatter_tril(mpccb_ctx* c, const double* seg_dev, double* full_packed_dev) {
+  CUDA_OK(c, enter_device(c));
   if (!c->diis_prefix) return fail(c, "the DIIS vector is row-owned: its segments are contiguous, no scatter needed");
   DiisPtrs ep = {};
   return launch_diis_cols(c, nullptr, seg_dev - c->nov, nullptr, nullptr, ep, 0, 0, 0, 0, full_packed_dev, nullptr);
 }
 
 extern "C" int mpccb_unpack_oovv(mpccb_ctx* c, const double* packed_dev, double* out_dev) {
+  CUDA_OK(c, enter_device(c));
   const i64 total = c->nov * c->nov;
   const int nb = (int)std::min<i64>(cdiv(total, 256), 148 * 16);
   k_unpack_oovv<<<nb, 256, 0, c->stream>>>(packed_dev, out_dev, c->o, c->v);
@@ -1094,6 +1129,7 @@ extern "C" int mpccb_unpack_oovv(mpccb_ctx* c, const double* packed_dev, double*
 extern "C" int mpccb_diis_push(mpccb_ctx* c, const double* t1_new_dev, const double* xprev_dev,
                                double* x_slot_dev, double* e_slot_dev, const double* const* e_list_dev,
                                int nd, int slot, int first_call, int count_t1, double* dots_dev) {
+  CUDA_OK(c, enter_device(c));
   if (!c->T) return fail(c, "t2 buffer not bound");
   if (nd < 0 || nd > 6 || slot < 0 || slot > 5) return fail(c, "bad DIIS slot/nd");
   StageTimer timer(c, ST_DIIS_PUSH);
@@ -1128,6 +1164,7 @@ extern "C" int mpccb_diis_push(mpccb_ctx* c, const double* t1_new_dev, const dou
 
 extern "C" int mpccb_diis_combine(mpccb_ctx* c, const double* const* x_list_dev, const double* coeff_host,
                                   int nd, double* xnew_dev, long long n) {
+  CUDA_OK(c, enter_device(c));
   if (nd < 1 || nd > 6) return fail(c, "bad DIIS nd");
   StageTimer timer(c, ST_DIIS_COMBINE);
   DiisComb cb;
@@ -1156,6 +1193,7 @@ extern "C" size_t mpccb_ao2mo_scratch_bytes(const mpccb_ctx* c, int nb) {
 extern "C" int mpccb_ao2mo_block(mpccb_ctx* c, const double* packed_dev, int nb, int l0, const double* C_dev,
                                  double* Loo_dev, double* Lov_dev, double* Lvv_dev, void* scratch_dev,
                                  size_t scratch_bytes) {
+  CUDA_OK(c, enter_device(c));
   const int o = c->o, v = c->v, nao = o + v;
   if (nb <= 0 || l0 < 0 || l0 + nb > c->L) return fail(c, "bad auxiliary block [%d,%d)", l0, l0 + nb);
   if (scratch_bytes < mpccb_ao2mo_scratch_bytes(c, nb)) return fail(c, "ao2mo scratch too small");
@@ -1227,12 +1265,14 @@ extern "C" int mpccb_get_buffer(mpccb_ctx* c, const char* name, double** ptr, lo
 }
 
 extern "C" int mpccb_copy_to_host(mpccb_ctx* c, const double* src, double* dst, long long count) {
+  CUDA_OK(c, enter_device(c));
   CUDA_OK(c, cudaMemcpyAsync(dst, src, sizeof(double) * count, cudaMemcpyDeviceToHost, c->stream));
   CUDA_OK(c, cudaStreamSynchronize(c->stream));
   return 0;
 }
 
 extern "C" int mpccb_copy_to_device(mpccb_ctx* c, const double* src, double* dst, long long count) {
+  CUDA_OK(c, enter_device(c));
   CUDA_OK(c, cudaMemcpyAsync(dst, src, sizeof(double) * count, cudaMemcpyHostToDevice, c->stream));
   CUDA_OK(c, cudaStreamSynchronize(c->stream));
   return 0;
@@ -1242,6 +1282,7 @@ extern "C" int mpccb_copy_to_device(mpccb_ctx* c, const double* src, double* dst
 // through the TMA-fed kernel (same code as the Yvo GEMM), everything else through the generic DMMA kernel.
 extern "C" int mpccb_gemm_nt(mpccb_ctx* c, const double* A_dev, const double* B_dev, double* C_dev,
                              int M, int N, int K) {
+  CUDA_OK(c, enter_device(c));
   if (M <= 0 || N <= 0 || K <= 0) return fail(c, "gemm_nt: empty product");
   const bool aligned = (K % 2 == 0) && ((reinterpret_cast<uintptr_t>(A_dev) | reinterpret_cast<uintptr_t>(B_dev)) & 15) == 0;
   if (c->use_tma && aligned && K >= 64 && (double)M * N * K >= 5e8 && M >= 64 && N >= 64) {
@@ -1291,6 +1332,7 @@ extern "C" int mpccb_gemm_nt(mpccb_ctx* c, const double* A_dev, const double* B_
 // out = alpha * transpose(in, perm) + beta * out   (numpy semantics: out axis d = in axis perm[d])
 extern "C" int mpccb_permute_axpby(mpccb_ctx* c, const double* in_dev, double* out_dev, int rank,
                                    const int* in_dims, const int* perm, double alpha, double beta) {
+  CUDA_OK(c, enter_device(c));
   if (rank < 1 || rank > MAX_RANK) return fail(c, "permute: rank must be 1..%d", MAX_RANK);
   i64 istr[MAX_RANK], total = 1;
   int seen = 0;
@@ -1337,6 +1379,7 @@ extern "C" int mpccb_permute_axpby(mpccb_ctx* c, const double* in_dev, double* o
 
 // rank 2: t1[i,a] /= eo[i]-ev[a];  rank 4: t2[i,j,a,b] /= eo[i]+eo[j]-ev[a]-ev[b]   (the context's eps_o / eps_v)
 extern "C" int mpccb_div_denominators(mpccb_ctx* c, double* t_dev, int rank) {
+  CUDA_OK(c, enter_device(c));
   if (!c->eo || !c->ev) return fail(c, "orbital energies not bound");
   if (rank != 2 && rank != 4) return fail(c, "div_denominators: rank 2 or 4");
   const i64 total = rank == 2 ? c->nov : c->nov * c->nov;
@@ -1349,6 +1392,7 @@ extern "C" int mpccb_div_denominators(mpccb_ctx* c, double* t_dev, int rank) {
 // t[x0..] /= sum_d sign[d] * e_dev[d][x_d]  (rank <= 4; e_dev[d] has dims[d] entries)
 extern "C" int mpccb_div_general(mpccb_ctx* c, double* t_dev, int rank, const int* dims,
                                  const double* const* e_dev, const double* signs) {
+  CUDA_OK(c, enter_device(c));
   if (rank < 1 || rank > 4) return fail(c, "div_general: rank 1..4");
   DenomDesc d;
   memset(&d, 0, sizeof(d));
@@ -1364,6 +1408,7 @@ extern "C" int mpccb_div_general(mpccb_ctx* c, double* t_dev, int rank, const in
 // tnew[idx] = told[idx] for the active/inactive index classes in class_mask (see k_class_overwrite)
 extern "C" int mpccb_class_overwrite(mpccb_ctx* c, double* tnew_dev, const double* told_dev, int rank,
                                      const int* act_h_dev, const int* act_p_dev, unsigned class_mask) {
+  CUDA_OK(c, enter_device(c));
   if (rank != 2 && rank != 4) return fail(c, "class_overwrite: rank 2 or 4");
   const i64 total = rank == 2 ? c->nov : c->nov * c->nov;
   const int nb = (int)std::min<i64>(cdiv(total, 256), NSM * 16);
@@ -1372,8 +1417,36 @@ extern "C" int mpccb_class_overwrite(mpccb_ctx* c, double* tnew_dev, const doubl
   return 0;
 }
 
+// Test hook: q[i] = fast_div(x[i], y[i]) — the branch-free quotient the fused t2 epilogue uses instead of the
+// compiler's IEEE division sequence (gemm_tma.cuh). tests/test_gpu_parity.py sweeps it against x / y.
+namespace {
+__global__ void __launch_bounds__(256) k_test_fast_div(const double* __restrict__ x, const double* __restrict__ y,
+                                                       double* __restrict__ q, i64 n) {
+  const i64 stride = (i64)gridDim.x * blockDim.x * 8;
+  for (i64 i0 = ((i64)blockIdx.x * blockDim.x + threadIdx.x) * 8; i0 < n; i0 += stride) {
+    double xs[8], ys[8], qs[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) { xs[u] = i0 + u < n ? x[i0 + u] : 1.0; ys[u] = i0 + u < n ? y[i0 + u] : 1.0; }
+    fast_div_batch<8>(xs, ys, qs);                    // the batched form the epilogue calls
+#pragma unroll
+    for (int u = 0; u < 8; ++u)
+      if (i0 + u < n) q[i0 + u] = (u & 1) ? qs[u] : fast_div(xs[u], ys[u]);   // and the scalar form, alternating
+  }
+}
+}  // namespace
+
+extern "C" int mpccb_test_fast_div(mpccb_ctx* c, const double* x_dev, const double* y_dev, double* q_dev, long long n) {
+  CUDA_OK(c, enter_device(c));
+  if (n <= 0) return 0;
+  const int nb = (int)std::min<i64>(cdiv(n, 2048), NSM * 8);
+  k_test_fast_div<<<nb, 256, 0, c->stream>>>(x_dev, y_dev, q_dev, n);
+  LAUNCH_OK(c, "k_test_fast_div");
+  return 0;
+}
+
 // out_dev[0] = sum_i x[i] y[i]  (deterministic two-pass reduction; needs the bound workspace)
 extern "C" int mpccb_dot(mpccb_ctx* c, const double* x_dev, const double* y_dev, long long n, double* out_dev) {
+  CUDA_OK(c, enter_device(c));
   if (!c->ws) return fail(c, "bind the workspace first");
   const int nb = (int)std::min<i64>(std::max<i64>(cdiv(n, 1024), 1), 592);
   k_dot_partial<<<nb, 256, 0, c->stream>>>(x_dev, y_dev, c->scal, n);

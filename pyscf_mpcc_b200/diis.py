@@ -54,6 +54,7 @@ class DIIS:
         self._e = {}
         self.last_coeff = None
         self._pool = []
+        self.generation = 0         # bumped whenever the extrapolation buffer (xprev) is overwritten in place
 
     def get_num_vec(self):
         return len(self._bookkeep)
@@ -94,7 +95,8 @@ class DIIS:
             self._xprev = self._alloc(n_local, dev)
             ctx.call("mpccb_diis_push", amps.t1_dev.data_ptr(), None, self._xprev.data_ptr(), None, None,
                      0, 0, 1, int(ll._count_t1), None)
-            return AmplitudeVector(ll, vec=self._xprev, t1_dev=self._xprev[:ll.nov])
+            self.generation += 1
+            return AmplitudeVector(ll, vec=self._xprev, t1_dev=self._xprev[:ll.nov], owner=self, serial=self.generation)
 
         if self._head >= self.space:
             self._head = 0
@@ -137,7 +139,8 @@ class DIIS:
             x_list[k] = self._x[k].data_ptr()
             coeff[k] = float(c[k + 1])
         ctx.call("mpccb_diis_combine", x_list, coeff, nd, self._xprev.data_ptr(), n_local)
-        return AmplitudeVector(ll, vec=self._xprev, t1_dev=self._xprev[:ll.nov])
+        self.generation += 1
+        return AmplitudeVector(ll, vec=self._xprev, t1_dev=self._xprev[:ll.nov], owner=self, serial=self.generation)
 
 
 class AmplitudeVector:
@@ -146,14 +149,23 @@ class AmplitudeVector:
     bound t2 buffer) or a packed device vector ``[t1 | tril rows]``.
     ``numpy()`` materialises the reference's flat vector on the host."""
 
-    def __init__(self, solver, vec=None, t1_dev=None):
+    def __init__(self, solver, vec=None, t1_dev=None, owner=None, serial=0):
         self.solver = solver
         self.vec = vec
         self.t1_dev = t1_dev
+        # vectors returned by DIIS.update alias its extrapolation buffer: `owner.generation` moves on when the next
+        # update overwrites it (the reference returns a fresh array, diis.py:268-275)
+        self.owner = owner
+        self.serial = serial
+
+    def _check_fresh(self):
+        if self.owner is not None and self.serial != self.owner.generation:
+            raise RuntimeError("this amplitude vector is stale: a later DIIS update overwrote the extrapolated vector")
 
     def packed_device(self):
         ll = self.solver
         if self.vec is not None:
+            self._check_fresh()
             return self.vec
         out = torch.empty(ll._vec_len_local, dtype=torch.float64, device=ll.device)
         out[:ll.nov].copy_(self.t1_dev.reshape(-1))

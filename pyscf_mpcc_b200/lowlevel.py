@@ -43,11 +43,16 @@ class DeviceT2:
     ``numpy()`` / ``np.asarray`` materialise it; nothing on the hot path does.
     """
 
-    def __init__(self, solver, layout, packed=None, serial=0):
+    def __init__(self, solver, layout, packed=None, serial=0, packed_is_full=False, owner=None):
         self.solver = solver
         self.layout = layout
         self.packed = packed
         self.serial = serial
+        # "oovv": `packed` is either this rank's local part of a DIIS vector (row segment or column-owned order) or,
+        # when it came from a host vector, the whole reference-order packed triangle (no gather needed).
+        self.packed_is_full = packed_is_full
+        # the DIIS object whose extrapolation buffer `packed` aliases (None: an own buffer, never stale)
+        self.owner = owner
         o, v = solver.nocc, solver.nvir
         self.shape = (v, o, v, o) if layout == "aibj" else (o, o, v, v)
         self.dtype = np.dtype(np.float64)
@@ -63,12 +68,20 @@ class DeviceT2:
         if self.layout == "aibj":
             slab = self._local_device()                      # (na, o, v, o)
             return ll._gather_rows(slab.reshape(ll._na, -1), v).reshape(v, o, v, o).cpu().numpy()
+        self._check_fresh()
         seg = self.packed                                    # local packed rows of the lower triangle
-        full = ll._gather_packed(seg)
+        full = seg if self.packed_is_full else ll._gather_packed(seg)
         out = torch.empty((o, o, v, v), dtype=torch.float64, device=ll.device)
         ll._ctx.call("mpccb_unpack_oovv", full.data_ptr(), out.data_ptr())
         ll._sync()
         return out.cpu().numpy()
+
+    def _check_fresh(self):
+        """An "oovv" handle from ``run_diis`` aliases the DIIS object's extrapolation buffer, which the next
+        ``update`` overwrites in place (the reference returns a fresh array each time, diis.py:268-275)."""
+        if self.owner is not None and self.serial != self.owner.generation:
+            raise RuntimeError("this t2 handle is stale: a later DIIS update overwrote the extrapolated vector; "
+                               "materialise it (np.asarray) before the next run_diis()")
 
     def _local_device(self):
         ll = self.solver
@@ -86,9 +99,10 @@ class DeviceT2:
         o, v = ll.nocc, ll.nvir
         if self.layout == "aibj":
             return self._local_device().cpu().numpy()
-        if ll.world_size > 1:
+        self._check_fresh()
+        if ll.world_size > 1 and not self.packed_is_full:
             raise RuntimeError("the (o,o,v,v) form of a sharded vector needs the collective numpy()")
-        packed = ll._gather_packed(self.packed) if ll._diis_columns else self.packed
+        packed = ll._gather_packed(self.packed) if (ll._diis_columns and not self.packed_is_full) else self.packed
         out = torch.empty((o, o, v, v), dtype=torch.float64, device=ll.device)
         ll._ctx.call("mpccb_unpack_oovv", packed.data_ptr(), out.data_ptr())
         ll._sync()
@@ -140,7 +154,12 @@ class MPCC_LL:
         else:
             self.group, self.world_size, self.rank = None, 1, 0
         if device is None:
-            device = torch.device("cuda", torch.cuda.current_device())
+            # one process per GPU under torchrun: cuda:<LOCAL_RANK>; otherwise the current device
+            local = os.environ.get("LOCAL_RANK")
+            if local is not None and self.world_size > 1 and int(local) < torch.cuda.device_count():
+                device = torch.device("cuda", int(local))
+            else:
+                device = torch.device("cuda", torch.cuda.current_device())
         self.device = torch.device(device)
         if self.device.index is None:
             self.device = torch.device("cuda", torch.cuda.current_device())
@@ -383,7 +402,7 @@ class MPCC_LL:
         if mode not in ("auto", "multicast", "p2p", "nccl"):
             raise ValueError(f"jk_exchange={mode!r}")
         ok, hdl, buf = 0, None, None
-        if mode != "nccl":
+        if mode != "nccl" and self._symm_agreed():
             try:
                 import torch.distributed._symmetric_memory as symm
                 buf = symm.empty(count, dtype=torch.float64, device=self.device)
@@ -413,6 +432,24 @@ class MPCC_LL:
         self._equal_slabs = len({hi - lo for lo, hi in self._jk_rows}) == 1
         self._jk_mode = "nccl"
 
+    def _symm_agreed(self):
+        """All ranks agree, BEFORE anyone enters the collective rendezvous, that symmetric memory can be tried: a
+        local probe (module importable, allocation works) reduced with MIN over the group. A rank that cannot even
+        allocate would otherwise leave the others blocked inside ``rendezvous``."""
+        if getattr(self, "_symm_ok", None) is None:
+            ok = 1
+            try:
+                import torch.distributed._symmetric_memory as symm
+                probe = symm.empty(16, dtype=torch.float64, device=self.device)
+                del probe
+            except Exception as e:
+                ok = 0
+                self._symm_probe_error = repr(e)
+            flag = torch.tensor([ok], device=self.device)
+            torch.distributed.all_reduce(flag, op=torch.distributed.ReduceOp.MIN, group=self.group)
+            self._symm_ok = int(flag.item()) == 1
+        return self._symm_ok
+
     def _setup_t2_peers(self):
         """Cross-rank half of the mirror scheme (include/mpcc_b200.h, mpccb_bind_t2_peers): the t2 slabs live in
         symmetric memory so that the rank computing block (a,b) can store the mirror block t2[b,a] straight into
@@ -422,6 +459,8 @@ class MPCC_LL:
         bounds = self._bounds
         n_max = max(bounds[r + 1] - bounds[r] for r in range(self.world_size)) * v * o * o
         ok, buf, hdl = 0, None, None
+        if not self._symm_agreed():
+            return
         try:
             import torch.distributed._symmetric_memory as symm
             buf = symm.empty(n_max, dtype=torch.float64, device=self.device)
@@ -591,15 +630,25 @@ class MPCC_LL:
 
     def vector_to_amplitudes(self, vector):
         """(:170-176) t1 (o,v) host copy; t2 (o,o,v,v) lazy handle."""
+        full, owner, serial = False, None, 0
         if isinstance(vector, AmplitudeVector):
             vec = vector.packed_device()
+            owner, serial = vector.owner, vector.serial
         else:
-            vec = self._to_dev(np.asarray(vector))
+            # a host vector is the reference-order flat vector (what AmplitudeVector.numpy() returns): the whole
+            # packed triangle, whatever the device-side sharding / ownership of DIIS vectors is
+            host = np.asarray(vector, dtype=np.float64).reshape(-1)
+            if host.size != self.nov + self.nov * (self.nov + 1) // 2:
+                raise ValueError(f"vector has {host.size} elements, expected nov + nov(nov+1)/2 = "
+                                 f"{self.nov + self.nov * (self.nov + 1) // 2}")
+            vec = self._to_dev(host)
+            self.h2d_bytes += host.size * 8
+            full = True
         self._t1n_host.copy_(vec[:self.nov], non_blocking=True)
         self._sync()
         self.d2h_bytes += self.nov * 8
         t1 = self._t1n_host.numpy().reshape(self.nocc, self.nvir).copy()
-        return t1, DeviceT2(self, "oovv", packed=vec[self.nov:])
+        return t1, DeviceT2(self, "oovv", packed=vec[self.nov:], packed_is_full=full, owner=owner, serial=serial)
 
     def run_diis(self, t1, t2, adiis):
         vec = self.amplitudes_to_vector(t1, t2)

@@ -82,6 +82,32 @@ class SyntheticMF:
                 np.ascontiguousarray(f[:, o:, o:]))
 
 
+def host_blocks(nocc: int, nvir: int, naux: int, seed: int = 0, scale: float | None = None, chunk: int = 64):
+    """(Loo, Lov, Lvv, eps_o, eps_v) of ``SyntheticMF(nocc, nvir, naux, seed, scale)`` — the same random stream, hence
+    bit-identical MO blocks (``mo_coeff`` = identity) — drawn ``chunk`` auxiliary rows at a time, so that the full
+    (naux, nao, nao) tensor and its packed copy never exist: at (64, 512, 1536) the peak is the 3.6 GB of the blocks
+    instead of 12 GB. ``numpy.random.Generator.standard_normal`` fills its output sequentially, so chunked draws
+    continue the stream exactly (``tests/test_host_logic.py::test_host_blocks_equal_synthetic_mf``). These are the
+    inputs of ``bench.py`` and of the full-size trace fixture: reproducible on the CPU (oracle) and on every rank."""
+    if scale is None:
+        scale = default_scale(nocc, nvir)
+    rng = np.random.default_rng(seed)
+    nao = nocc + nvir
+    Loo = np.empty((naux, nocc, nocc))
+    Lov = np.empty((naux, nocc, nvir))
+    Lvv = np.empty((naux, nvir, nvir))
+    for lo in range(0, naux, chunk):
+        hi = min(lo + chunk, naux)
+        full = rng.standard_normal((hi - lo, nao, nao)) * scale / np.sqrt(naux)      # same rounding as SyntheticMF
+        full = full + full.transpose(0, 2, 1)
+        Loo[lo:hi] = full[:, :nocc, :nocc]
+        Lov[lo:hi] = full[:, :nocc, nocc:]
+        Lvv[lo:hi] = full[:, nocc:, nocc:]
+    e_occ = np.sort(rng.uniform(-2.0, -0.5, nocc))
+    e_vir = np.sort(rng.uniform(0.3, 3.0, nvir))
+    return Loo, Lov, Lvv, e_occ, e_vir
+
+
 def default_scale(nocc: int, nvir: int) -> float:
     """Scale that keeps |dE| O(1) for large shapes."""
     return 0.1 * float(np.sqrt(76.0 / (nocc + nvir)))

@@ -1,7 +1,12 @@
-"""Full-size (BASELINE.json configs[2]: nocc=64, nvir=512, naux=1536) checks through size-independent
-properties plus an oracle comparison on a slab of rows (the oracle finishes those in seconds)."""
+"""Full-size (BASELINE.json configs[2]: nocc=64, nvir=512, naux=1536) checks: the iteration trace against the
+fixture the oracle produced on the same inputs (tests/golden/generate_trace_config3.py), size-independent
+properties, and an oracle comparison on a slab of rows (the oracle finishes those in seconds)."""
+import os
+
 import numpy as np
 import pytest
+
+from conftest import GOLDEN
 
 pytestmark = pytest.mark.gpu
 
@@ -10,12 +15,52 @@ pytestmark = pytest.mark.gpu
 def big():
     import torch
     from pyscf_mpcc_b200.lowlevel import MPCC_LL
-    from pyscf_mpcc_b200.synthetic import device_blocks, default_scale
+    from pyscf_mpcc_b200.synthetic import host_blocks, default_scale
     o, v, L = 64, 512, 1536
-    Loo, Lov, Lvv, eo, ev = device_blocks(o, v, L, seed=0, scale=default_scale(o, v), device="cuda")
-    ll = MPCC_LL(blocks=(Loo, Lov, Lvv, torch.diag(eo), torch.diag(ev), torch.cat([eo, ev])))
+    # the inputs of the trace fixture and of bench.py: SyntheticMF's stream, drawn in chunks on the host
+    Loo, Lov, Lvv, eo, ev = host_blocks(o, v, L, seed=0, scale=default_scale(o, v))
+    ll = MPCC_LL(blocks=(Loo, Lov, Lvv, np.diag(eo), np.diag(ev), np.concatenate([eo, ev])))
     ll.verbose_print = False
     return ll
+
+
+def test_fullsize_trace_against_oracle_fixture(big):
+    """kernel()'s loop at the shape the metric is quoted on, iteration by iteration against the oracle's trace:
+    identical iteration count, |dE| <= 1e-8 Eh, res to 1e-6 relative, amplitude and DIIS-vector norms, final t1 to
+    1e-10 (north_star's tolerances)."""
+    import torch
+    from pyscf_mpcc_b200.diis import DIIS
+    g = np.load(os.path.join(GOLDEN, "trace_64_512_1536.npz"))
+    ll = big
+    o, v = ll.nocc, ll.nvir
+    assert tuple(int(x) for x in g["shape"]) == (o, v, ll.naux)
+    ll.t1 = np.zeros((o, v))
+    ad = DIIS()
+    err, count = np.inf, 0
+    while err > 1e-6 and count < 50:
+        res, dE, t1n, t2 = ll.updated_amps()
+        assert count < len(g["trace_dE"]), "more iterations than the oracle needed"
+        assert abs(dE - g["trace_dE"][count]) <= 1e-8
+        assert abs(res - g["trace_res"][count]) <= 1e-6 * g["trace_res"][count] + 1e-12
+        assert abs(np.linalg.norm(t1n) - g["trace_t1_new_norm"][count]) <= 1e-10
+        t2n = float(torch.linalg.vector_norm(ll._T).item())
+        assert abs(t2n - g["trace_t2_norm"][count]) <= 1e-9 * g["trace_t2_norm"][count]
+        vec = ll.amplitudes_to_vector(t1n, t2)
+        vn = float(torch.linalg.vector_norm(vec.packed_device()).item())
+        assert abs(vn - g["trace_vec_norm"][count]) <= 1e-9 * g["trace_vec_norm"][count]
+        if count == 0:
+            assert np.abs(t1n - g["it1_t1_new"]).max() <= 1e-10
+        ll.t1, ll.t2 = ll.vector_to_amplitudes(ad.update(vec))
+        assert abs(np.linalg.norm(ll.t1) - g["trace_t1_next_norm"][count]) <= 1e-10
+        if ad.last_coeff is not None:
+            c = g["diis_coeff"][count][:len(ad.last_coeff)]
+            np.testing.assert_allclose(ad.last_coeff[1:], c[1:], rtol=0, atol=1e-6)
+        count += 1
+        err = res
+    assert count == int(g["iterations"]) and bool(g["converged"])
+    assert np.abs(ll.t1 - g["final_t1"]).max() <= 1e-10
+    del ad
+    torch.cuda.empty_cache()
 
 
 def test_fullsize_slab_against_oracle_and_symmetry(big):

@@ -332,3 +332,156 @@ def test_column_owned_vector_equals_row_owned_vector(shape):
         vecs.append(ll.amplitudes_to_vector(t1n, t2h).numpy())
     assert vecs[0].shape == vecs[1].shape == (o * v + (o * v) * (o * v + 1) // 2,)
     assert np.array_equal(vecs[0], vecs[1])
+
+
+def test_config2_kernel_against_the_references_own_run():
+    """BASELINE.json configs[1]'s shape (benzene/cc-pVTZ: 21, 243, 654): iteration count, per-iteration dE / res,
+    final t1 and t2 samples against the fixture the REFERENCE's files produced (generate_golden_config2.py)."""
+    from conftest import GOLDEN
+    g = np.load(os.path.join(GOLDEN, "config2_mpcc_21_243_654.npz"))
+    o, v, L = (int(x) for x in g["shape"])
+    mf, ll = _solver(o, v, L, float(g["scale"]))
+    ll.con_tol, ll.max_its = 1e-6, 50
+    e = ll.kernel()
+    assert ll.iterations == int(g["iterations"])
+    tr = np.array(ll.history)
+    assert np.abs(tr[:, 1] - g["trace_dE"]).max() <= E_TOL
+    np.testing.assert_allclose(tr[:, 2], g["trace_res"], rtol=1e-6, atol=1e-12)
+    assert abs(e - g["trace_dE"][-1]) <= E_TOL
+    assert np.abs(ll.t1 - g["final_t1"]).max() <= AMP_TOL
+    t2 = np.asarray(ll.t2)
+    s = int(g["sample_stride"])
+    assert np.abs(t2.reshape(-1)[::s] - g["final_t2_samples"]).max() <= AMP_TOL
+    assert abs(np.linalg.norm(t2) - g["final_t2_norm"]) <= 1e-9
+    assert abs(t2.sum() - g["final_t2_sum"]) <= 1e-8
+    # first iteration from t1 = 0: t1_new, (v,o,v,o) t2 and the DIIS vector
+    ll.t1 = np.zeros((o, v))
+    res, dE, t1n, t2a = ll.updated_amps()
+    assert np.abs(t1n - g["it1_t1_new"]).max() <= AMP_TOL
+    t2h = np.asarray(t2a)
+    assert np.abs(t2h.reshape(-1)[::s] - g["it1_t2_samples"]).max() <= AMP_TOL
+    vec = ll.amplitudes_to_vector(t1n, t2a).numpy()
+    assert np.abs(vec[::s] - g["it1_vec_samples"]).max() <= AMP_TOL
+    assert abs(np.linalg.norm(vec) - g["it1_vec_norm"]) <= 1e-9
+
+
+def test_the_references_solver_object_drives_this_module(capsys):
+    """pyscf/mpcc/mpcc.py:5-17 executed UNMODIFIED (staged copy, oracle/make_ref.py): ``MPCC(mf, module)`` builds
+    ``module.MPCC_LL(mf)``, sets con_tol / max_its from outside and calls ``kernel()``. Passing
+    ``pyscf_mpcc_b200.lowlevel`` makes the reference's own solver object run on the GPU."""
+    from oracle import ref_shim
+    if not ref_shim.reference_available():
+        pytest.skip("no reference files (neither /root/reference nor oracle/_ref)")
+    import pyscf_mpcc_b200.lowlevel as b200_lowlevel
+    from pyscf_mpcc_b200.synthetic import SyntheticMF
+    ref_mpcc = ref_shim.load_reference_solver()
+    g, o, v, L, scale = _load([p for p in golden_cases() if "8_40_120" in p][0])
+    mf = SyntheticMF(o, v, L, seed=0, scale=scale)
+    obj = ref_mpcc.MPCC(mf, b200_lowlevel)                      # the reference's class, our module
+    assert type(obj).__module__ == "pyscf.mpcc.mpcc"
+    ll = obj.lowlevel
+    assert isinstance(ll, b200_lowlevel.MPCC_LL)
+    assert ll.con_tol == 1e-6 and ll.max_its == 50 and obj._scf is mf
+    assert ll.iterations == int(g["iterations"])
+    assert abs(ll.history[-1][1] - g["trace_dE"][-1]) <= E_TOL
+    assert np.abs(ll.t1 - g["final_t1"]).max() <= AMP_TOL
+    lines = [x for x in capsys.readouterr().out.splitlines() if x.startswith("It ")]
+    assert len(lines) == ll.iterations
+    # and the reference's own low-level module behind the same object gives the same numbers
+    ref_ll, _ = ref_shim.load_reference()
+    obj_ref = ref_mpcc.MPCC(mf, ref_ll)
+    assert abs(obj_ref.lowlevel.t1 - ll.t1).max() <= AMP_TOL
+
+
+@pytest.mark.parametrize("layout", ["rows", "columns"])
+def test_host_vector_round_trip(layout):
+    """vector_to_amplitudes(amplitudes_to_vector(t1, t2).numpy()): a HOST vector is the reference-order flat vector,
+    whatever the device-side ownership of DIIS vectors is (:162-176)."""
+    from oracle.mpcc_oracle import vector_to_amps
+    o, v, L = 6, 11, 20
+    mf, ll = _solver(o, v, L, 0.1, seed=2, diis_layout=layout)
+    ll.t1 = 0.05 * np.random.default_rng(3).standard_normal((o, v))
+    res, dE, t1n, t2 = ll.updated_amps()
+    flat = ll.amplitudes_to_vector(t1n, t2).numpy()
+    assert flat.shape == (o * v + o * v * (o * v + 1) // 2,)
+    t1b, t2b = ll.vector_to_amplitudes(flat)
+    t1o, t2o = vector_to_amps(flat, o, v)
+    assert np.array_equal(t1b, t1o)
+    assert np.array_equal(np.asarray(t2b), t2o)
+    with pytest.raises(ValueError):
+        ll.vector_to_amplitudes(flat[:-1])
+
+
+def test_extrapolated_t2_handle_goes_stale_instead_of_changing():
+    """run_diis returns a t2 that aliases the DIIS extrapolation buffer; the next update overwrites it in place. The
+    reference returns a fresh array (diis.py:268-275), so an old handle must raise, not silently show new values."""
+    from pyscf_mpcc_b200.diis import DIIS
+    o, v, L = 5, 9, 16
+    mf, ll = _solver(o, v, L, 0.1, seed=1)
+    ll.t1 = np.zeros((o, v))
+    ad = DIIS()
+    handles = []
+    for _ in range(3):
+        res, dE, t1n, t2 = ll.updated_amps()
+        ll.t1, t2x = ll.run_diis(t1n, t2, ad)
+        handles.append(t2x)
+    assert np.asarray(handles[-1]).shape == (o, o, v, v)
+    with pytest.raises(RuntimeError, match="stale"):
+        np.asarray(handles[0])
+    with pytest.raises(RuntimeError, match="stale"):
+        np.asarray(handles[1])
+
+
+def test_fast_div_within_one_ulp_of_ieee_division():
+    """The fused t2 epilogue replaces the IEEE division of :137 by MUFU.RCP64H + Newton + residual correction
+    (gemm_tma.cuh fast_div / fast_div_batch). Swept against numpy's x / y over the denominator range of the
+    fixtures (eo+eo-ev-ev in [-10, -1.6]), near-degenerate denominators, and a wide exponent range."""
+    import torch
+    mf, ll = _solver(4, 6, 8, 0.1)
+    rng = np.random.default_rng(0)
+    n = 1 << 21
+    dens = [-(1.6 + 8.4 * rng.random(n)),                             # fixture range
+            -(10.0 ** rng.uniform(-9, -1, n)),                        # near-degenerate orbital energies
+            np.ldexp(1.0 + rng.random(n), rng.integers(-300, 300, n)) * rng.choice([-1.0, 1.0], n)]
+    nums = [rng.standard_normal(n) * 10.0 ** rng.uniform(-12, 2, n),
+            rng.standard_normal(n) * 1e-3,
+            np.ldexp(1.0 + rng.random(n), rng.integers(-300, 300, n)) * rng.choice([-1.0, 1.0], n)]
+    worst = 0
+    for x, y in zip(nums, dens):
+        ok = np.isfinite(x / y) & (np.abs(x / y) > 1e-290) & (np.abs(x / y) < 1e290)
+        x, y = x[ok], y[ok]
+        xd, yd = torch.from_numpy(x).cuda(), torch.from_numpy(y).cuda()
+        qd = torch.empty_like(xd)
+        ll._ctx.call("mpccb_test_fast_div", xd.data_ptr(), yd.data_ptr(), qd.data_ptr(), x.size)
+        torch.cuda.synchronize()
+        q = qd.cpu().numpy()
+        want = x / y
+        ulps = np.abs(q.view(np.int64) - want.view(np.int64))
+        assert np.all(np.sign(q) == np.sign(want))
+        worst = max(worst, int(ulps.max()))
+    assert worst <= 1, f"fast_div is {worst} ulp away from IEEE division"
+
+
+def test_near_degenerate_orbital_energies():
+    """HOMO-LUMO gap of 1e-3 Eh: denominators down to 2e-3, amplitudes ~500x larger; one residual evaluation
+    against the oracle to 1e-10 relative to the largest amplitude."""
+    from oracle.mpcc_oracle import LowLevelOracle
+    from pyscf_mpcc_b200.lowlevel import MPCC_LL
+    from pyscf_mpcc_b200.synthetic import SyntheticMF
+    o, v, L = 16, 40, 64
+    mf = SyntheticMF(o, v, L, seed=6, scale=0.02)
+    Loo, Lov, Lvv = mf.mo_blocks()
+    eo = np.sort(np.concatenate([np.linspace(-1.0, -0.6, o - 2), [-0.5005, -0.5]]))
+    ev = np.sort(np.concatenate([[-0.499, -0.4985], np.linspace(0.3, 2.0, v - 2)]))
+    blocks = (Loo, Lov, Lvv, np.diag(eo), np.diag(ev), np.concatenate([eo, ev]))
+    ll = MPCC_LL(blocks=blocks)
+    orc = LowLevelOracle(blocks=blocks, mode="blas")
+    t1 = 0.01 * np.random.default_rng(1).standard_normal((o, v))
+    ll.t1 = t1
+    res, dE, t1n, t2 = ll.updated_amps()
+    res_o, dE_o, t1n_o, t2_o = orc.updated_amps(t1)
+    scale = np.abs(t2_o).max()
+    assert scale > 1.0
+    assert np.abs(np.asarray(t2) - t2_o).max() <= 1e-10 * scale
+    assert np.abs(t1n - t1n_o).max() <= 1e-10 * max(1.0, np.abs(t1n_o).max())
+    assert abs(dE - dE_o) <= 1e-8 * max(1.0, abs(dE_o))

@@ -232,3 +232,28 @@ def test_column_owned_shares_are_balanced_at_the_target_shape():
         assert max(sizes) / (sum(sizes) / p) < 1.003
         rows = [sharding.local_vector_length(o, v, *sharding.slab_bounds(v, p, r)) - o * v for r in range(p)]
         assert max(rows) / (sum(rows) / p) > 1.4                 # what the row-owned split costs
+
+
+def test_host_blocks_equal_synthetic_mf():
+    """The chunked generator behind bench.py and the full-size trace fixture draws the same stream as SyntheticMF."""
+    from pyscf_mpcc_b200.synthetic import SyntheticMF, host_blocks
+    o, v, L = 6, 21, 50
+    mf = SyntheticMF(o, v, L, seed=5, scale=0.07)
+    for chunk in (1, 7, 64):
+        Loo, Lov, Lvv, eo, ev = host_blocks(o, v, L, seed=5, scale=0.07, chunk=chunk)
+        for got, want in zip((Loo, Lov, Lvv), mf.mo_blocks()):
+            assert np.array_equal(got, want)
+        assert np.array_equal(np.concatenate([eo, ev]), mf.mo_energy)
+
+
+def test_staged_reference_files_match_the_reference_tree():
+    """oracle/make_ref.py stages the five hot-path files byte for byte (build container only)."""
+    import hashlib
+    from oracle import make_ref
+    if not os.path.isdir(make_ref.SOURCE_ROOT):
+        pytest.skip("reference tree not present")
+    manifest = make_ref.stage()
+    for rel, digest in manifest.items():
+        with open(os.path.join(make_ref.SOURCE_ROOT, rel), "rb") as f:
+            assert hashlib.sha256(f.read()).hexdigest() == digest
+    assert make_ref.staged()

@@ -110,3 +110,52 @@ def test_flop_formula_target_shape():
     assert abs(flops_per_updated_amps(64, 512, 1536) - 6.799e12) < 2e9
     from pyscf_mpcc_b200.flops import updated_amps_flops
     assert updated_amps_flops(21, 243, 654) == flops_per_updated_amps(21, 243, 654)
+
+
+def test_config2_fixture_from_the_reference_itself():
+    """BASELINE.json configs[1]'s shape (21, 243, 654): the fixture was produced by the reference's own files
+    (tests/golden/generate_golden_config2.py, about 40 s of np.einsum per call); the GEMM-shaped oracle reproduces
+    its iteration count, trace and amplitudes."""
+    from pyscf_mpcc_b200.synthetic import default_scale
+    g = np.load(os.path.join(GOLDEN, "config2_mpcc_21_243_654.npz"))
+    o, v, L = (int(x) for x in g["shape"])
+    assert (o, v, L) == (21, 243, 654) and float(g["scale"]) == default_scale(o, v)
+    orc = LowLevelOracle(SyntheticMF(o, v, L, seed=0, scale=float(g["scale"])), mode="blas")
+    e = orc.kernel()
+    assert orc.iterations == int(g["iterations"]) == 5
+    tr = np.array(orc.history)
+    np.testing.assert_allclose(tr[:, 1], g["trace_dE"], rtol=0, atol=1e-11)
+    np.testing.assert_allclose(tr[:, 2], g["trace_res"], rtol=1e-8, atol=1e-13)
+    np.testing.assert_allclose(orc.t1, g["final_t1"], rtol=0, atol=1e-12)
+    s = int(g["sample_stride"])
+    np.testing.assert_allclose(orc.t2.reshape(-1)[::s], g["final_t2_samples"], rtol=0, atol=1e-12)
+    assert abs(np.linalg.norm(orc.t2) - g["final_t2_norm"]) < 1e-10
+    assert abs(e - g["trace_dE"][-1]) < 1e-11
+
+
+@pytest.mark.parametrize("shape", [(5, 19, 116, 0.1, 4), (12, 64, 192, 0.1, 7), (21, 30, 70, 0.1, 32)])
+def test_packed_form_equals_plain(shape):
+    """``updated_amps_packed`` (slab by slab, DIIS vector written directly — the form that produced the full-size
+    trace fixture) against ``updated_amps`` + ``amps_to_vector``, and a whole solve through it against the fixture
+    the reference produced."""
+    o, v, L, scale, slab = shape
+    mf = SyntheticMF(o, v, L, seed=0, scale=scale)
+    orc = LowLevelOracle(mf, mode="blas")
+    t1 = 0.05 * np.random.default_rng(2).standard_normal((o, v))
+    res, dE, t1n, t2 = orc.updated_amps(t1)
+    res2, dE2, t1n2, vec2, ss = orc.updated_amps_packed(t1, slab=slab)
+    assert abs(res - res2) < 1e-14 and abs(dE - dE2) < 1e-13
+    np.testing.assert_allclose(t1n2, t1n, rtol=0, atol=1e-14)
+    np.testing.assert_allclose(vec2, amps_to_vector(t1n, t2, o, v), rtol=0, atol=1e-14)
+    assert abs(ss - float(np.vdot(t2, t2))) < 1e-12 * max(1.0, ss)
+    g = np.load(os.path.join(GOLDEN, f"mpcc_{o}_{v}_{L}.npz"))
+    t1, ad, err, count, tr = np.zeros((o, v)), PulayDIIS(), np.inf, 0, []
+    while err > 1e-6 and count < 50:
+        res, dE, t1n, vec, _ = orc.updated_amps_packed(t1, slab=slab)
+        t1 = np.array(ad.update(vec)[:o * v]).reshape(o, v)
+        count += 1
+        err = res
+        tr.append((dE, res))
+    assert count == int(g["iterations"])
+    np.testing.assert_allclose(np.array(tr)[:, 0], g["trace_dE"], rtol=0, atol=1e-12)
+    np.testing.assert_allclose(t1, g["final_t1"], rtol=0, atol=1e-12)

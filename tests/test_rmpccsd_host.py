@@ -15,7 +15,7 @@ from oracle import ref_shim
 from pyscf_mpcc_b200 import rmpccsd
 from pyscf_mpcc_b200.tensor_engine import Engine
 
-needs_ref = pytest.mark.skipif(not ref_shim.reference_available(), reason="reference tree not present")
+needs_ref = pytest.mark.skipif(not ref_shim.full_tree_available(), reason="full reference tree not present")
 
 
 def _ours(p, act_h, act_p, idx_s, idx_d):

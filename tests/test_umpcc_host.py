@@ -16,7 +16,7 @@ from pyscf_mpcc_b200 import umpcc_lowlevel as U
 from pyscf_mpcc_b200.tensor_engine import Engine
 from u_problem import make_u_problem, reference_state
 
-needs_ref = pytest.mark.skipif(not ref_shim.reference_available(), reason="reference tree not present")
+needs_ref = pytest.mark.skipif(not ref_shim.full_tree_available(), reason="full reference tree not present")
 
 
 def ours(p, steps=1, eng=None):
