@@ -469,7 +469,7 @@ def test_near_degenerate_orbital_energies():
     from pyscf_mpcc_b200.lowlevel import MPCC_LL
     from pyscf_mpcc_b200.synthetic import SyntheticMF
     o, v, L = 16, 40, 64
-    mf = SyntheticMF(o, v, L, seed=6, scale=0.02)
+    mf = SyntheticMF(o, v, L, seed=6, scale=0.05)
     Loo, Lov, Lvv = mf.mo_blocks()
     eo = np.sort(np.concatenate([np.linspace(-1.0, -0.6, o - 2), [-0.5005, -0.5]]))
     ev = np.sort(np.concatenate([[-0.499, -0.4985], np.linspace(0.3, 2.0, v - 2)]))
@@ -481,7 +481,7 @@ def test_near_degenerate_orbital_energies():
     res, dE, t1n, t2 = ll.updated_amps()
     res_o, dE_o, t1n_o, t2_o = orc.updated_amps(t1)
     scale = np.abs(t2_o).max()
-    assert scale > 1.0
+    assert scale > 0.5                                     # dominated by the 2e-3 denominators
     assert np.abs(np.asarray(t2) - t2_o).max() <= 1e-10 * scale
     assert np.abs(t1n - t1n_o).max() <= 1e-10 * max(1.0, np.abs(t1n_o).max())
     assert abs(dE - dE_o) <= 1e-8 * max(1.0, abs(dE_o))
