@@ -119,8 +119,13 @@ int mpccb_unpack_oovv(mpccb_ctx* ctx, const double* packed_dev, double* out_dev)
 /* x_slot = [t1_new | packed local rows of the bound t2]; unless first_call:
  * e_slot = x_slot - xprev and dots_dev[k] = e_slot . e_k for k < nd (e_list[slot] is ignored:
  * e_slot itself is used). count_t1 = 0 leaves the (replicated) t1 part out of the dots.
- * first_call != 0: only x_slot is written (it is the DIIS `xprev`). */
+ * first_call != 0: only x_slot is written (it is the DIIS `xprev`).
+ * xprev, the previous extrapolated vector (diis.py:268-275), is either the explicit vector xprev_dev (n_prev == 0)
+ * or — never stored — the combination sum_{k<n_prev} coeff_prev_host[k] * x_prev_list_dev[k] of the stored trial
+ * vectors in slot order, recomputed per element with the arithmetic of mpccb_diis_combine: one write and one read
+ * of the whole vector less per iteration. x_prev_list_dev[slot] may be x_slot_dev (the slot being replaced). */
 int mpccb_diis_push(mpccb_ctx* ctx, const double* t1_new_dev, const double* xprev_dev,
+                    const double* const* x_prev_list_dev, const double* coeff_prev_host, int n_prev,
                     double* x_slot_dev, double* e_slot_dev, const double* const* e_list_dev,
                     int nd, int slot, int first_call, int count_t1, double* dots_dev);
 /* xnew = sum_{k<nd} coeff[k] * x_list[k]  (n doubles each) */

@@ -177,12 +177,28 @@ k_t1_update(const double* __restrict__ OmRep, const double* __restrict__ w, cons
     const int i = (int)(idx / v), a = (int)(idx % v);   // lanes along a: t1/t1n/fvv coalesced
     const i64 ai = (i64)a * o + i;
     double om = (OmRep ? OmRep[ai] : 0.0) + w[ai] + OmLoc[ai];
-    double s = 0.0;
-    for (int b = 0; b < v; ++b) s += t1[(i64)i * v + b] * fvv[(i64)b * v + a];
-    om += s;
-    s = 0.0;
-    for (int k = 0; k < o; ++k) s += t1[(i64)k * v + a] * foo[(i64)i * o + k];
-    om -= s;
+    // four independent accumulation chains per sum (fixed order): the loads of a chain no longer wait for the
+    // previous FMA — this kernel is replicated on every rank, its latency is serial time at 8 GPUs
+    double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+    int b = 0;
+    for (; b + 4 <= v; b += 4) {
+      s0 = fma(t1[(i64)i * v + b], fvv[(i64)b * v + a], s0);
+      s1 = fma(t1[(i64)i * v + b + 1], fvv[(i64)(b + 1) * v + a], s1);
+      s2 = fma(t1[(i64)i * v + b + 2], fvv[(i64)(b + 2) * v + a], s2);
+      s3 = fma(t1[(i64)i * v + b + 3], fvv[(i64)(b + 3) * v + a], s3);
+    }
+    for (; b < v; ++b) s0 = fma(t1[(i64)i * v + b], fvv[(i64)b * v + a], s0);
+    om += (s0 + s1) + (s2 + s3);
+    s0 = s1 = s2 = s3 = 0.0;
+    int k = 0;
+    for (; k + 4 <= o; k += 4) {
+      s0 = fma(t1[(i64)k * v + a], foo[(i64)i * o + k], s0);
+      s1 = fma(t1[(i64)(k + 1) * v + a], foo[(i64)i * o + k + 1], s1);
+      s2 = fma(t1[(i64)(k + 2) * v + a], foo[(i64)i * o + k + 2], s2);
+      s3 = fma(t1[(i64)(k + 3) * v + a], foo[(i64)i * o + k + 3], s3);
+    }
+    for (; k < o; ++k) s0 = fma(t1[(i64)k * v + a], foo[(i64)i * o + k], s0);
+    om -= (s0 + s1) + (s2 + s3);
     const double q = om / (ev[a] - eo[i]);
     t1n[idx] = -q;
     OmOut[ai] = om;
@@ -204,49 +220,88 @@ struct DiisPtrs {
   const double* e[6];
 };
 
-// Row blocks: blockIdx.x = local row (r - r0) for the t2 part, one extra block
-// (blockIdx.x == nrows) for the t1 part (skipped when t1 == nullptr).
-//   xs[...] = value;  es[...] = value - xprev[...];  dots[k] += es . e_k  (k < nd; e_slot is `es` itself)
-// partial layout: [gridDim.x][7] (slot k -> column k; column 6 unused)
+// The previous extrapolated vector, never stored: xprev = sum_k c[k] * x[k] over the n stored trial vectors in slot
+// order — the arithmetic of k_diis_combine (diis.py:268-275), recomputed per element inside the push. n == 0: the
+// explicit `xprev` pointer is used (second call of a solve: xprev is the first vector). Folding the combination into
+// the push removes one write and one read of the whole vector per iteration.
+struct DiisPrev {
+  const double* x[6];
+  double c[6];
+  int n;
+};
+
+__device__ __forceinline__ double diis_prev_value(const DiisPrev& pv, const double* xprev, i64 p) {
+  if (pv.n == 0) return xprev[p];
+  double s = 0.0;
+#pragma unroll
+  for (int k = 0; k < 6; ++k)
+    if (k < pv.n) s = fma(pv.x[k][p], pv.c[k], s);
+  return s;
+}
+
+// Chunked push. The t2 part of the local vector (packed rows r0 .. r0+nrows of the (nov x nov) view of T) is cut into
+// G equal contiguous chunks of the PACKED index; CTA b streams chunk b with all vector streams (x_k, e_k, the new x
+// and e) contiguous and coalesced, and the matching T row prefixes contiguous up to the row breaks. A thread finds
+// (row, column) of its first element with one square root and then walks: column += 256, carrying into the next rows.
+// CTA G handles the t1 part (skipped when t1new == nullptr).
+//   xs[p] = value;  es[p] = value - xprev[p];  dots[k] += es . e_k  (k < nd; e_slot is `es` itself)
+// xs / es may alias pv.x[slot] / eptr.e[slot] (the slot being replaced): every element is read before it is
+// written, by the same thread — hence no __restrict__ on them.
+// partial layout: [G + 1][7] (slot k -> column k; column 6 unused)
 __global__ void __launch_bounds__(256)
 k_diis_push(const double* __restrict__ T, const double* __restrict__ t1new,
-            const double* __restrict__ xprev, double* __restrict__ xs, double* __restrict__ es,
+            const double* xprev, DiisPrev pv, double* xs, double* es,
             DiisPtrs eptr, int nd, int slot, int first_call, int count_t1,
-            i64 nov, i64 r0, int nrows, double* __restrict__ partial) {
+            i64 nov, i64 r0, int nrows, i64 chunk, int G, double* __restrict__ partial) {
   __shared__ double scratch[32];
   const int blk = blockIdx.x;
-  i64 len, src_off, dst_off;
-  const double* src;
-  if (blk < nrows) {
-    const i64 r = r0 + blk;
-    len = r + 1;
-    src = T + (i64)blk * nov;          // T holds local rows only
-    src_off = 0;
-    dst_off = nov + (r * (r + 1)) / 2 - (r0 * (r0 + 1)) / 2;   // t1 part first, then local packed rows
-  } else {
-    if (t1new == nullptr) { len = 0; src = nullptr; src_off = 0; dst_off = 0; }
-    else { len = nov; src = t1new; src_off = 0; dst_off = 0; }
-  }
   double d[6] = {0, 0, 0, 0, 0, 0};
-  for (i64 c = threadIdx.x; c < len; c += blockDim.x) {
-    const double val = src[src_off + c];
+  auto one = [&](double val, i64 p) {
     if (first_call) {
-      xs[dst_off + c] = val;           // becomes xprev
+      xs[p] = val;                       // becomes xprev
     } else {
-      const double e = val - xprev[dst_off + c];
-      xs[dst_off + c] = val;
-      es[dst_off + c] = e;
+      const double e = val - diis_prev_value(pv, xprev, p);
+      double other[6];
+#pragma unroll
+      for (int k = 0; k < 6; ++k) other[k] = (k < nd && k != slot) ? eptr.e[k][p] : 0.0;
+      xs[p] = val;
+      es[p] = e;
 #pragma unroll
       for (int k = 0; k < 6; ++k)
-        if (k < nd) d[k] += e * ((k == slot) ? e : eptr.e[k][dst_off + c]);
+        if (k < nd) d[k] = fma(e, (k == slot) ? e : other[k], d[k]);
+    }
+  };
+  if (blk < G) {
+    const i64 tri0 = (r0 * (r0 + 1)) / 2;
+    const i64 total = ((r0 + nrows) * (r0 + nrows + 1)) / 2 - tri0;      // local packed t2 elements
+    const i64 q0 = (i64)blk * chunk;
+    const i64 q1 = q0 + chunk < total ? q0 + chunk : total;
+    i64 q = q0 + threadIdx.x;
+    if (q < q1) {
+      // global packed position -> (r, c): r = floor((sqrt(8P + 1) - 1) / 2), fixed up for rounding
+      const i64 P = tri0 + q;
+      i64 r = (i64)((sqrt(8.0 * (double)P + 1.0) - 1.0) * 0.5);
+      while ((r * (r + 1)) / 2 > P) --r;
+      while (((r + 1) * (r + 2)) / 2 <= P) ++r;
+      i64 c = P - (r * (r + 1)) / 2;
+      for (; q < q1; q += 256) {
+        one(T[(r - r0) * nov + c], nov + q);
+        c += 256;
+        while (c > r) { c -= r + 1; ++r; }
+      }
+    }
+  } else if (t1new != nullptr) {
+    for (i64 c = threadIdx.x; c < nov; c += blockDim.x) one(t1new[c], c);
+    if (!count_t1) {                     // replicated t1 part counted by one rank only
+#pragma unroll
+      for (int k = 0; k < 6; ++k) d[k] = 0.0;
     }
   }
   if (!first_call) {
-    const double wgt = (blk < nrows || count_t1) ? 1.0 : 0.0;   // replicated t1 part counted by one rank only
 #pragma unroll
     for (int k = 0; k < 6; ++k) {
       if (k < nd) {
-        const double s = wgt * block_sum(d[k], scratch);
+        const double s = block_sum(d[k], scratch);
         if (threadIdx.x == 0) partial[(i64)blk * 7 + k] = s;
       }
     }
@@ -277,7 +332,7 @@ __device__ __forceinline__ i64 tril_below(i64 r, i64 c) { return (r * (r + 1)) /
 // packed vector (host-facing gathers; the caller all-reduces the zero-initialised targets).
 __global__ void __launch_bounds__(256)
 k_diis_push_cols(const double* __restrict__ T, const double* __restrict__ t1new,
-                 const double* __restrict__ xprev, double* __restrict__ xs, double* __restrict__ es,
+                 const double* xprev, DiisPrev pv, double* xs, double* es,
                  DiisPtrs eptr, int nd, int slot, int first_call, int count_t1,
                  int o, int v, int a0, int na, const i64* __restrict__ prefix, int G,
                  double* __restrict__ partial, double* __restrict__ scatter_to) {
@@ -325,7 +380,7 @@ k_diis_push_cols(const double* __restrict__ T, const double* __restrict__ t1new,
         } else {
           double e[U];
 #pragma unroll
-          for (int u = 0; u < U; ++u) e[u] = ok[u] ? val[u] - xprev[pos[u]] : 0.0;
+          for (int u = 0; u < U; ++u) e[u] = ok[u] ? val[u] - diis_prev_value(pv, xprev, pos[u]) : 0.0;
 #pragma unroll
           for (int q = 0; q < 6; ++q) {
             if (q < nd) {
@@ -347,12 +402,15 @@ k_diis_push_cols(const double* __restrict__ T, const double* __restrict__ t1new,
       if (first_call) {
         xs[c] = val;
       } else {
-        const double e = val - xprev[c];
+        const double e = val - diis_prev_value(pv, xprev, c);
+        double other[6];
+#pragma unroll
+        for (int q = 0; q < 6; ++q) other[q] = (q < nd && q != slot) ? eptr.e[q][c] : 0.0;
         xs[c] = val;
         es[c] = e;
 #pragma unroll
         for (int q = 0; q < 6; ++q)
-          if (q < nd) d[q] += e * ((q == slot) ? e : eptr.e[q][c]);
+          if (q < nd) d[q] += e * ((q == slot) ? e : other[q]);
       }
     }
     if (!count_t1) {
@@ -383,7 +441,7 @@ k_diis_combine(DiisComb cb, int nd, double* __restrict__ xnew, i64 n) {
     double s = 0.0;
 #pragma unroll
     for (int k = 0; k < 6; ++k)
-      if (k < nd) s += cb.x[k][i] * cb.c[k];
+      if (k < nd) s = fma(cb.x[k][i], cb.c[k], s);     // same arithmetic as diis_prev_value
     xnew[i] = s;
   }
 }

@@ -35,6 +35,7 @@ typedef GemmCfg<2, 4, 4, 4, false, false> CfgM64RR;   // 64 x 128
 }  // namespace
 
 constexpr int DIIS_COLS_GRID = 148 * 16;
+constexpr int DIIS_ROWS_GRID = 148 * 8;      // chunks of the packed vector (k_diis_push): 8 resident CTAs per SM
 
 struct mpccb_ctx {
   int o, v, L, device, a_begin, a_end, na, ldk;
@@ -370,7 +371,7 @@ i64 carve_workspace(mpccb_ctx* c, unsigned char* base) {
   mx(splitk_scratch((int)na, (int)o, (int)(o * L), 128, 64));  // S7
   mx(splitk_scratch((int)v, (int)o, (int)(na * L), 128, 64));  // G2
   mx(splitk_scratch((int)o, (int)o, (int)(na * L), 128, 64));  // S8
-  mx((na * o + 1) * 7);                                        // DIIS dot partials (row-owned vector)
+  mx((DIIS_ROWS_GRID + 1) * 7);                                // DIIS dot partials (row-owned vector)
   mx((DIIS_COLS_GRID + 1) * 7);                                //   "   (column-owned vector)
   c->P_count = p;
   c->P = w.take(p);
@@ -1078,13 +1079,13 @@ extern "C" int mpccb_t2_to_aibj(mpccb_ctx* c, double* out_dev) {
 }
 
 namespace {
-int launch_diis_cols(mpccb_ctx* c, const double* t1_new_dev, const double* xprev_dev, double* x_slot_dev,
-                     double* e_slot_dev, const DiisPtrs& ep, int nd, int slot, int first_call, int count_t1,
-                     double* scatter_to, int* grid_out) {
+int launch_diis_cols(mpccb_ctx* c, const double* t1_new_dev, const double* xprev_dev, const DiisPrev& pv,
+                     double* x_slot_dev, double* e_slot_dev, const DiisPtrs& ep, int nd, int slot, int first_call,
+                     int count_t1, double* scatter_to, int* grid_out) {
   const i64 nblocks = (i64)c->na * c->v;
   const int G = (int)std::min<i64>(nblocks, DIIS_COLS_GRID);
   if ((i64)(G + 1) * 7 > c->P_count) return fail(c, "DIIS partial scratch too small");
-  k_diis_push_cols<<<G + 1, 256, 0, c->stream>>>(c->T, t1_new_dev, xprev_dev, x_slot_dev, e_slot_dev, ep, nd, slot,
+  k_diis_push_cols<<<G + 1, 256, 0, c->stream>>>(c->T, t1_new_dev, xprev_dev, pv, x_slot_dev, e_slot_dev, ep, nd, slot,
                                                  first_call, count_t1, c->o, c->v, c->a_begin, c->na,
                                                  reinterpret_cast<const i64*>(c->diis_prefix), G, c->P, scatter_to);
   LAUNCH_OK(c, "k_diis_push_cols");
@@ -1103,7 +1104,8 @@ extern "C" int mpccb_pack_tril_rows(mpccb_ctx* c, double* seg_dev) {
   if (!c->T) return fail(c, "t2 buffer not bound");
   if (c->diis_prefix) {                      // column-owned order; seg_dev is the t2 part (vector + nov)
     DiisPtrs ep = {};
-    return launch_diis_cols(c, nullptr, nullptr, seg_dev - c->nov, nullptr, ep, 0, 0, 1, 0, nullptr, nullptr);
+    DiisPrev pv = {};
+    return launch_diis_cols(c, nullptr, nullptr, pv, seg_dev - c->nov, nullptr, ep, 0, 0, 1, 0, nullptr, nullptr);
   }
   k_pack_rows<<<c->na * c->o, 256, 0, c->stream>>>(c->T, seg_dev, c->nov, (i64)c->a_begin * c->o);
   LAUNCH_OK(c, "k_pack_rows");
@@ -1114,7 +1116,8 @@ extern "C" int mpccb_diis_scatter_tril(mpccb_ctx* c, const double* seg_dev, doub
   CUDA_OK(c, enter_device(c));
   if (!c->diis_prefix) return fail(c, "the DIIS vector is row-owned: its segments are contiguous, no scatter needed");
   DiisPtrs ep = {};
-  return launch_diis_cols(c, nullptr, seg_dev - c->nov, nullptr, nullptr, ep, 0, 0, 0, 0, full_packed_dev, nullptr);
+  DiisPrev pv = {};
+  return launch_diis_cols(c, nullptr, seg_dev - c->nov, pv, nullptr, nullptr, ep, 0, 0, 0, 0, full_packed_dev, nullptr);
 }
 
 extern "C" int mpccb_unpack_oovv(mpccb_ctx* c, const double* packed_dev, double* out_dev) {
@@ -1127,36 +1130,41 @@ extern "C" int mpccb_unpack_oovv(mpccb_ctx* c, const double* packed_dev, double*
 }
 
 extern "C" int mpccb_diis_push(mpccb_ctx* c, const double* t1_new_dev, const double* xprev_dev,
+                               const double* const* x_prev_list_dev, const double* coeff_prev_host, int n_prev,
                                double* x_slot_dev, double* e_slot_dev, const double* const* e_list_dev,
                                int nd, int slot, int first_call, int count_t1, double* dots_dev) {
   CUDA_OK(c, enter_device(c));
   if (!c->T) return fail(c, "t2 buffer not bound");
   if (nd < 0 || nd > 6 || slot < 0 || slot > 5) return fail(c, "bad DIIS slot/nd");
+  if (n_prev < 0 || n_prev > 6) return fail(c, "bad DIIS n_prev");
+  if (!first_call && n_prev == 0 && !xprev_dev) return fail(c, "DIIS push needs xprev (explicit or as a combination)");
   StageTimer timer(c, ST_DIIS_PUSH);
-  if (c->diis_prefix) {
-    DiisPtrs ep;
-    for (int k = 0; k < 6; ++k) ep.e[k] = (k < nd && e_list_dev) ? e_list_dev[k] : nullptr;
-    int grid = 0;
-    if (launch_diis_cols(c, t1_new_dev, xprev_dev, x_slot_dev, e_slot_dev, ep, nd, slot, first_call, count_t1,
-                         nullptr, &grid)) return 1;
-    if (!first_call) {
-      k_final_sums_strided<<<1, 256, 0, c->stream>>>(c->P, dots_dev, grid, 7, nd);
-      LAUNCH_OK(c, "k_final_sums_strided");
-    }
-    return 0;
-  }
-  const int nrows = c->na * c->o;
-  const int nblk = nrows + 1;
-  // partial sums live in the (idle) split-K scratch
-  if ((i64)nblk * 7 > c->P_count) return fail(c, "DIIS partial scratch too small");
   DiisPtrs ep;
   for (int k = 0; k < 6; ++k) ep.e[k] = (k < nd && e_list_dev) ? e_list_dev[k] : nullptr;
-  double* partial = c->P;
-  k_diis_push<<<nblk, 256, 0, c->stream>>>(c->T, t1_new_dev, xprev_dev, x_slot_dev, e_slot_dev, ep, nd, slot,
-                                           first_call, count_t1, c->nov, (i64)c->a_begin * c->o, nrows, partial);
-  LAUNCH_OK(c, "k_diis_push");
+  DiisPrev pv;
+  pv.n = n_prev;
+  for (int k = 0; k < 6; ++k) {
+    pv.x[k] = k < n_prev ? x_prev_list_dev[k] : nullptr;
+    pv.c[k] = k < n_prev ? coeff_prev_host[k] : 0.0;
+  }
+  int grid = 0;
+  if (c->diis_prefix) {
+    if (launch_diis_cols(c, t1_new_dev, xprev_dev, pv, x_slot_dev, e_slot_dev, ep, nd, slot, first_call, count_t1,
+                         nullptr, &grid)) return 1;
+  } else {
+    const i64 r0 = (i64)c->a_begin * c->o;
+    const int nrows = c->na * c->o;
+    const i64 total = ((r0 + nrows) * (r0 + nrows + 1)) / 2 - (r0 * (r0 + 1)) / 2;
+    const int G = (int)std::min<i64>(DIIS_ROWS_GRID, std::max<i64>(1, cdiv(total, 2048)));
+    const i64 chunk = align_up(cdiv(total, G) > 0 ? (total + G - 1) / G : 1, 256);
+    grid = G + 1;
+    if ((i64)grid * 7 > c->P_count) return fail(c, "DIIS partial scratch too small");
+    k_diis_push<<<grid, 256, 0, c->stream>>>(c->T, t1_new_dev, xprev_dev, pv, x_slot_dev, e_slot_dev, ep, nd, slot,
+                                             first_call, count_t1, c->nov, r0, nrows, chunk, G, c->P);
+    LAUNCH_OK(c, "k_diis_push");
+  }
   if (!first_call) {
-    k_final_sums_strided<<<1, 256, 0, c->stream>>>(partial, dots_dev, nblk, 7, nd);
+    k_final_sums_strided<<<1, 256, 0, c->stream>>>(c->P, dots_dev, grid, 7, nd);
     LAUNCH_OK(c, "k_final_sums_strided");
   }
   return 0;

@@ -10,7 +10,11 @@ only by the kernels behind ``mpccb_diis_push`` / ``mpccb_diis_combine``:
 * push: one pass that packs the new amplitudes into slot ``s``, forms
   ``e_s = x_s - xprev`` and accumulates all ``e_s . e_k`` (deterministic reduction);
 * the (nd+1) x (nd+1) system is solved on the host with the reference's calls;
-* combine: ``xprev = sum_k c_k x_k`` in slot order (``diis.py:268-275``).
+* combine: ``xprev = sum_k c_k x_k`` in slot order (``diis.py:268-275``) — only its first
+  nov elements (the t1 the next iteration starts from) are formed right away. The rest of
+  ``xprev`` is never stored: the next push recomputes it per element from the stored
+  trial vectors and the coefficients (one write and one read of the vector less per
+  iteration), and a host-facing access (``.t2`` after ``run_diis``) materialises it on demand.
 
 Unlike the reference there is no HDF5 spill (``diis.py:123-139``): 13 vectors of
 4.3 GB fit in 180 GB of HBM at the target shape.
@@ -49,7 +53,10 @@ class DIIS:
         self._bookkeep = []
         self._head = 0
         self._H = None
-        self._xprev = None          # torch tensor (device)
+        self._xprev_buf = None      # torch tensor (device): the first vector; later the on-demand materialisation
+        self._prev = None           # (coefficients, slots): xprev as a combination of the stored trial vectors
+        self._prev_stored = False   # does _xprev_buf hold the current xprev?
+        self._t1_next = None
         self._x = {}
         self._e = {}
         self.last_coeff = None
@@ -75,7 +82,7 @@ class DIIS:
         """Allocate the whole history (xprev + ``space`` x/e pairs) up front, so that no cudaMalloc —
         slow once NCCL has mapped peer memory — lands inside the iteration loop. Optional: without it
         the vectors are allocated on first use, as the reference's ``push_vec`` does (diis.py:148-185)."""
-        need = 1 + 2 * self.space - (0 if self._xprev is None else 1) - 2 * len(self._x) - len(self._pool)
+        need = 1 + 2 * self.space - (0 if self._xprev_buf is None else 1) - 2 * len(self._x) - len(self._pool)
         for _ in range(max(need, 0)):
             self._pool.append(torch.empty(solver._vec_len_local, dtype=torch.float64, device=solver.device))
         return self
@@ -90,13 +97,16 @@ class DIIS:
         if len(self._bookkeep) >= self.space:
             self._bookkeep = self._bookkeep[1 - self.space:]
 
-        if self._xprev is None:
+        if self._xprev_buf is None:
             # first trial vector only becomes xprev (diis.py:160-167); returned unchanged
-            self._xprev = self._alloc(n_local, dev)
-            ctx.call("mpccb_diis_push", amps.t1_dev.data_ptr(), None, self._xprev.data_ptr(), None, None,
-                     0, 0, 1, int(ll._count_t1), None)
+            self._xprev_buf = self._alloc(n_local, dev)
+            self._solver = ll
+            ctx.call("mpccb_diis_push", amps.t1_dev.data_ptr(), None, None, None, 0, self._xprev_buf.data_ptr(), None,
+                     None, 0, 0, 1, int(ll._count_t1), None)
+            self._prev_stored = True
             self.generation += 1
-            return AmplitudeVector(ll, vec=self._xprev, t1_dev=self._xprev[:ll.nov], owner=self, serial=self.generation)
+            return AmplitudeVector(ll, vec=self._xprev_buf, t1_dev=self._xprev_buf[:ll.nov], owner=self,
+                                   serial=self.generation)
 
         if self._head >= self.space:
             self._head = 0
@@ -111,8 +121,17 @@ class DIIS:
         e_list = (ctypes.c_void_p * 6)()
         for k in range(6):
             e_list[k] = self._e[k].data_ptr() if (k < nd and k in self._e) else None
+        xp_list = (ctypes.c_void_p * 6)()
+        xp_coeff = (ctypes.c_double * 6)()
+        n_prev = 0
+        if self._prev is not None:
+            coeffs, slots = self._prev
+            n_prev = len(slots)
+            for k, sl in enumerate(slots):
+                xp_list[k] = self._x[sl].data_ptr()
+                xp_coeff[k] = coeffs[k]
         dots = ll._dots_dev
-        ctx.call("mpccb_diis_push", amps.t1_dev.data_ptr(), self._xprev.data_ptr(),
+        ctx.call("mpccb_diis_push", amps.t1_dev.data_ptr(), self._xprev_buf.data_ptr(), xp_list, xp_coeff, n_prev,
                  self._x[slot].data_ptr(), self._e[slot].data_ptr(), e_list, nd, slot, 0,
                  int(ll._count_t1), dots.data_ptr())
         if ll.world_size > 1:
@@ -133,14 +152,33 @@ class DIIS:
 
         c = solve_diis_system(self._H[:nd + 1, :nd + 1])
         self.last_coeff = c
+        # xprev = sum_k c[k+1] x_k (diis.py:268-275): kept as a recipe; only the t1 part is formed now
+        self._prev = ([float(c[k + 1]) for k in range(nd)], list(range(nd)))
+        self._prev_stored = False
+        self.generation += 1
+        if self._t1_next is None:
+            self._t1_next = torch.empty(ll.nov, dtype=torch.float64, device=dev)
+        self._combine_into(self._t1_next, ll.nov)
+        return AmplitudeVector(ll, vec=None, t1_dev=self._t1_next, owner=self, serial=self.generation, lazy=True)
+
+    def _combine_into(self, out, n):
+        coeffs, slots = self._prev
         x_list = (ctypes.c_void_p * 6)()
         coeff = (ctypes.c_double * 6)()
-        for k in range(nd):
-            x_list[k] = self._x[k].data_ptr()
-            coeff[k] = float(c[k + 1])
-        ctx.call("mpccb_diis_combine", x_list, coeff, nd, self._xprev.data_ptr(), n_local)
-        self.generation += 1
-        return AmplitudeVector(ll, vec=self._xprev, t1_dev=self._xprev[:ll.nov], owner=self, serial=self.generation)
+        for k, sl in enumerate(slots):
+            x_list[k] = self._x[sl].data_ptr()
+            coeff[k] = coeffs[k]
+        self._solver._ctx.call("mpccb_diis_combine", x_list, coeff, len(slots), out.data_ptr(), n)
+
+    @property
+    def _xprev(self):
+        """The current extrapolated vector as a device tensor (materialised on demand; host-facing paths only)."""
+        if self._xprev_buf is None:
+            return None
+        if not self._prev_stored:
+            self._combine_into(self._xprev_buf, self._xprev_buf.numel())
+            self._prev_stored = True
+        return self._xprev_buf
 
 
 class AmplitudeVector:
@@ -149,10 +187,11 @@ class AmplitudeVector:
     bound t2 buffer) or a packed device vector ``[t1 | tril rows]``.
     ``numpy()`` materialises the reference's flat vector on the host."""
 
-    def __init__(self, solver, vec=None, t1_dev=None, owner=None, serial=0):
+    def __init__(self, solver, vec=None, t1_dev=None, owner=None, serial=0, lazy=False):
         self.solver = solver
         self.vec = vec
         self.t1_dev = t1_dev
+        self.lazy = lazy            # the extrapolated vector of `owner`, not materialised yet
         # vectors returned by DIIS.update alias its extrapolation buffer: `owner.generation` moves on when the next
         # update overwrites it (the reference returns a fresh array, diis.py:268-275)
         self.owner = owner
@@ -166,6 +205,10 @@ class AmplitudeVector:
         ll = self.solver
         if self.vec is not None:
             self._check_fresh()
+            return self.vec
+        if self.lazy:
+            self._check_fresh()
+            self.vec = self.owner._xprev
             return self.vec
         out = torch.empty(ll._vec_len_local, dtype=torch.float64, device=ll.device)
         out[:ll.nov].copy_(self.t1_dev.reshape(-1))

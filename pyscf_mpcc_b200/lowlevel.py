@@ -43,10 +43,11 @@ class DeviceT2:
     ``numpy()`` / ``np.asarray`` materialise it; nothing on the hot path does.
     """
 
-    def __init__(self, solver, layout, packed=None, serial=0, packed_is_full=False, owner=None):
+    def __init__(self, solver, layout, packed=None, serial=0, packed_is_full=False, owner=None, source=None):
         self.solver = solver
         self.layout = layout
         self.packed = packed
+        self.source = source        # "oovv": the AmplitudeVector to take the packed t2 part from, on first use
         self.serial = serial
         # "oovv": `packed` is either this rank's local part of a DIIS vector (row segment or column-owned order) or,
         # when it came from a host vector, the whole reference-order packed triangle (no gather needed).
@@ -69,12 +70,19 @@ class DeviceT2:
             slab = self._local_device()                      # (na, o, v, o)
             return ll._gather_rows(slab.reshape(ll._na, -1), v).reshape(v, o, v, o).cpu().numpy()
         self._check_fresh()
-        seg = self.packed                                    # local packed rows of the lower triangle
+        seg = self._packed()                                 # local packed rows of the lower triangle
         full = seg if self.packed_is_full else ll._gather_packed(seg)
         out = torch.empty((o, o, v, v), dtype=torch.float64, device=ll.device)
         ll._ctx.call("mpccb_unpack_oovv", full.data_ptr(), out.data_ptr())
         ll._sync()
         return out.cpu().numpy()
+
+    def _packed(self):
+        """The packed t2 part. An extrapolated vector is materialised only here — nothing on the hot path reads the
+        t2 part of the DIIS extrapolation (the next iteration rebuilds t2 from t1, :135-137)."""
+        if self.packed is None:
+            self.packed = self.source.packed_device()[self.solver.nov:]
+        return self.packed
 
     def _check_fresh(self):
         """An "oovv" handle from ``run_diis`` aliases the DIIS object's extrapolation buffer, which the next
@@ -102,7 +110,7 @@ class DeviceT2:
         self._check_fresh()
         if ll.world_size > 1 and not self.packed_is_full:
             raise RuntimeError("the (o,o,v,v) form of a sharded vector needs the collective numpy()")
-        packed = ll._gather_packed(self.packed) if (ll._diis_columns and not self.packed_is_full) else self.packed
+        packed = ll._gather_packed(self._packed()) if (ll._diis_columns and not self.packed_is_full) else self._packed()
         out = torch.empty((o, o, v, v), dtype=torch.float64, device=ll.device)
         ll._ctx.call("mpccb_unpack_oovv", packed.data_ptr(), out.data_ptr())
         ll._sync()
@@ -555,7 +563,7 @@ class MPCC_LL:
         ctx.call("mpccb_finish", self._red.data_ptr(), self._t1n_dev.data_ptr(), self._scal_dev.data_ptr())
         self._scal_host.copy_(self._scal_dev, non_blocking=True)
         if adiis is not None:
-            nxt = adiis.update(AmplitudeVector(self, vec=None, t1_dev=self._t1n_dev)).vec[:self.nov]
+            nxt = adiis.update(AmplitudeVector(self, vec=None, t1_dev=self._t1n_dev)).t1_dev
         else:
             nxt = self._t1n_dev
         self._sync()
@@ -630,6 +638,14 @@ class MPCC_LL:
 
     def vector_to_amplitudes(self, vector):
         """(:170-176) t1 (o,v) host copy; t2 (o,o,v,v) lazy handle."""
+        if isinstance(vector, AmplitudeVector) and vector.t1_dev is not None:
+            # device-side vector: t1 from its first nov elements; the t2 part stays where it is (for an extrapolated
+            # vector: un-materialised) until somebody reads the (o,o,v,v) tensor
+            self._t1n_host.copy_(vector.t1_dev.reshape(-1), non_blocking=True)
+            self._sync()
+            self.d2h_bytes += self.nov * 8
+            t1 = self._t1n_host.numpy().reshape(self.nocc, self.nvir).copy()
+            return t1, DeviceT2(self, "oovv", source=vector, owner=vector.owner, serial=vector.serial)
         full, owner, serial = False, None, 0
         if isinstance(vector, AmplitudeVector):
             vec = vector.packed_device()

@@ -87,11 +87,18 @@ class _FakeCtx:
 
     def call(self, name, *a):
         if name == "mpccb_diis_push":
-            t1p, xprev, xs, es, elist, nd, slot, first, count_t1, dots = a
+            t1p, xprev, xpl, xpc, n_prev, xs, es, elist, nd, slot, first, count_t1, dots = a
             x = self.mem[t1p]
+            if not first:
+                if n_prev:                       # xprev as a combination of the stored vectors (read before xs is written)
+                    prev = np.zeros(len(x))
+                    for k in range(n_prev):
+                        prev += self.mem[xpl[k]] * xpc[k]
+                else:
+                    prev = self.mem[xprev].copy()
             self.mem[xs][:] = x
             if not first:
-                self.mem[es][:] = x - self.mem[xprev]
+                self.mem[es][:] = x - prev
                 d = self.mem[dots]
                 for k in range(nd):
                     ek = self.mem[es] if k == slot else self.mem[elist[k]]
@@ -117,6 +124,9 @@ class _FakeTensor:
     def __getitem__(self, s):
         return self
 
+    def numel(self):
+        return self.arr.size
+
     def numpy(self):
         return self.arr
 
@@ -135,9 +145,12 @@ def test_device_diis_bookkeeping_against_reference_fixture(monkeypatch):
     ll._dots_host = _FakeTensor(ctx, np.zeros(7))
     d = DIIS()
     monkeypatch.setattr(DIIS, "_alloc", lambda self, k, dev: _FakeTensor(ctx, np.zeros(k)))
+    import pyscf_mpcc_b200.diis as diis_mod
+    monkeypatch.setattr(diis_mod.torch, "empty", lambda k, dtype=None, device=None: _FakeTensor(ctx, np.zeros(k)))
     for x, want in zip(g["inputs"], g["outputs"]):
         out = d.update(AmplitudeVector(ll, vec=None, t1_dev=_FakeTensor(ctx, x.copy())))
-        np.testing.assert_allclose(out.vec.arr, want, rtol=1e-9, atol=1e-11)
+        np.testing.assert_allclose(out.packed_device().arr, want, rtol=1e-9, atol=1e-11)
+        np.testing.assert_allclose(out.t1_dev.arr, want, rtol=1e-9, atol=1e-11)      # nov == n in this stand-in
     np.testing.assert_allclose(d._H, g["H"], rtol=1e-10, atol=1e-14)
     assert d._head == 3 and d.get_num_vec() == 6          # 9 pushes into a ring of 6 wrapped once
 
