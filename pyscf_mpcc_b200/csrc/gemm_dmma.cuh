@@ -274,6 +274,7 @@ struct T2Params {
   const double* Fvo;    // [b, j]
   double* OmP;          // [tiles_n][(a - a_begin) * o + i]
   int o, v, a_begin, a_end, n_a, n_b;
+  int jp;               // pitch of j in T (nocc rounded up to even)
 };
 
 // Symmetry of the dressed integrals: e[(a,i),(b,j)] = e[(b,j),(a,i)] (a Gram matrix), hence
@@ -357,7 +358,7 @@ __device__ __forceinline__ void t2_epilogue(double (&acc)[Cfg::MT][Cfg::NT][2], 
       const int b = tn * p.n_b + bl;
       if (b >= p.v) break;
       const double evb = p.ev[b];
-      double* trow = p.T + (((i64)(a - p.a_begin) * p.v + b) * o + i) * o;
+      double* trow = p.T + (((i64)(a - p.a_begin) * p.v + b) * o + i) * p.jp;
       const double* frow = p.Fvo + (i64)b * o;
       for (int j = lane; j < o; j += 32) {
         const double e1 = S[r * PITCH + bl * o + j];

@@ -350,7 +350,7 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
       cok[cc] = in && b < t2p.v;
       cbl[cc] = bl; cj[cc] = j;
       cden[cc] = t2p.ev[cok[cc] ? b : 0] - t2p.eo[j];
-      coloff[cc] = (i64)b * o * o + j;
+      coloff[cc] = (i64)b * o * t2p.jp + j;
       cfvo[cc] = cok[cc] ? t2p.Fvo[(i64)b * o + j] : 0.0;
     }
     double tv[RPW][CPL];
@@ -370,7 +370,7 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
         const int a = t2p.a_begin + tm * t2p.n_a + al;
         const bool rok = in && a < t2p.a_end;
         const double dai = t2p.ev[rok ? a : t2p.a_begin] - t2p.eo[i];
-        rowoff[u] = ((i64)(a - t2p.a_begin) * t2p.v * o + i) * o;
+        rowoff[u] = ((i64)(a - t2p.a_begin) * t2p.v * o + i) * t2p.jp;
         omp[u] = rok ? (a - t2p.a_begin) * o + i : -1;
 #pragma unroll
         for (int cc = 0; cc < CPL; ++cc) {
@@ -426,7 +426,7 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
         const int a = t2p.a_begin + tm * t2p.n_a + al;
         mok[m] = in && a < t2p.a_end;
         mal[m] = al;
-        mcol[m] = (i64)a * o * o + i;
+        mcol[m] = (i64)a * o * t2p.jp + i;
         mfvo[m] = mok[m] ? t2p.Fvo[(i64)a * o + i] : 0.0;
       }
 #pragma unroll
@@ -438,7 +438,7 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
         const int b = tn * t2p.n_b + bl;
         const bool rok = in && b < t2p.v;
         const int s = sym_owner(sym, rok ? b : 0);
-        double* tgt = sym.Tp[s] + ((i64)(b - sym.bounds[s]) * t2p.v * o + j) * o;
+        double* tgt = sym.Tp[s] + ((i64)(b - sym.bounds[s]) * t2p.v * o + j) * t2p.jp;
         double fsum = 0.0;
         bool any = false;
 #pragma unroll

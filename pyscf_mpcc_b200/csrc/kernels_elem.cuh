@@ -10,10 +10,15 @@
 namespace mpccb {
 
 // out[b][c][r] = in[b][r][c]      (Lov -> Lvo, t1 -> t1T)
+// Address of flat element f of the LOGICAL [a][b][i][j] t2 tensor in the stored buffer, whose j pitch is nocc rounded
+// up to even (pad = 0 or 1): every row of nocc elements is followed by `pad` unused ones.
+__device__ __forceinline__ i64 t2_addr(i64 f, int o, int pad) { return pad ? f + (f / o) * pad : f; }
+
 __global__ void __launch_bounds__(256)
-k_transpose_batched(const double* __restrict__ in, double* __restrict__ out, int R, int C) {
+k_transpose_batched(const double* __restrict__ in, double* __restrict__ out, int R, int C, int ldo) {
+  // ldo >= R: pitch of the output rows (Lvo keeps its j index on an even pitch)
   __shared__ double tile[32][33];
-  const i64 boff = (i64)blockIdx.z * R * C;
+  const i64 boff = (i64)blockIdx.z * R * C, boff_out = (i64)blockIdx.z * ldo * C;
   const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
   for (int dy = threadIdx.y; dy < 32; dy += 8) {
     const int r = r0 + dy, c = c0 + threadIdx.x;
@@ -22,7 +27,7 @@ k_transpose_batched(const double* __restrict__ in, double* __restrict__ out, int
   __syncthreads();
   for (int dy = threadIdx.y; dy < 32; dy += 8) {
     const int c = c0 + dy, r = r0 + threadIdx.x;
-    if (r < R && c < C) out[boff + (i64)c * R + r] = tile[threadIdx.x][dy];
+    if (r < R && c < C) out[boff_out + (i64)c * ldo + r] = tile[threadIdx.x][dy];
   }
 }
 
@@ -252,7 +257,7 @@ __global__ void __launch_bounds__(256)
 k_diis_push(const double* __restrict__ T, const double* __restrict__ t1new,
             const double* xprev, DiisPrev pv, double* xs, double* es,
             DiisPtrs eptr, int nd, int slot, int first_call, int count_t1,
-            i64 nov, i64 r0, int nrows, i64 chunk, int G, double* __restrict__ partial) {
+            i64 nov, i64 r0, int nrows, i64 chunk, int G, int o, int pad, double* __restrict__ partial) {
   __shared__ double scratch[32];
   const int blk = blockIdx.x;
   double d[6] = {0, 0, 0, 0, 0, 0};
@@ -285,7 +290,7 @@ k_diis_push(const double* __restrict__ T, const double* __restrict__ t1new,
       while (((r + 1) * (r + 2)) / 2 <= P) ++r;
       i64 c = P - (r * (r + 1)) / 2;
       for (; q < q1; q += 256) {
-        one(T[(r - r0) * nov + c], nov + q);
+        one(T[t2_addr((r - r0) * nov + c, o, pad)], nov + q);
         c += 256;
         while (c > r) { c -= r + 1; ++r; }
       }
@@ -334,7 +339,7 @@ __global__ void __launch_bounds__(256)
 k_diis_push_cols(const double* __restrict__ T, const double* __restrict__ t1new,
                  const double* xprev, DiisPrev pv, double* xs, double* es,
                  DiisPtrs eptr, int nd, int slot, int first_call, int count_t1,
-                 int o, int v, int a0, int na, const i64* __restrict__ prefix, int G,
+                 int o, int jp, int v, int a0, int na, const i64* __restrict__ prefix, int G,
                  double* __restrict__ partial, double* __restrict__ scatter_to) {
   __shared__ double scratch[32];
   constexpr int U = 4;
@@ -350,7 +355,7 @@ k_diis_push_cols(const double* __restrict__ T, const double* __restrict__ t1new,
       const i64 F0 = ((i64)b * v + (a0 + al)) * oo;
       const i64 R0 = F0 / nov, C0 = F0 - R0 * nov;
       const i64 base = nov + prefix[k] - tril_below(R0, C0);
-      const double* blk = T + k * oo;
+      const double* blk = T + k * o * jp;
       for (int t0 = threadIdx.x; t0 < oo; t0 += 256 * U) {
         i64 pos[U], ref[U];
         double val[U];
@@ -367,7 +372,7 @@ k_diis_push_cols(const double* __restrict__ T, const double* __restrict__ t1new,
               ok[u] = true;
               ref[u] = (r * (r + 1)) / 2 + c;
               pos[u] = base + ref[u];
-              val[u] = blk[i * o + j];
+              val[u] = blk[i * jp + j];
             }
           }
         }
@@ -467,7 +472,7 @@ k_unpack_oovv(const double* __restrict__ packed, double* __restrict__ out, int o
 
 // out[a][i][b][j] = T[a][b][i][j]   (the (v,o,v,o) tensor updated_amps returns, reference :137,:152)
 __global__ void __launch_bounds__(256)
-k_abij_to_aibj(const double* __restrict__ T, double* __restrict__ out, int o, int v, int na) {
+k_abij_to_aibj(const double* __restrict__ T, double* __restrict__ out, int o, int jp, int v, int na) {
   const i64 total = (i64)na * v * o * o;
   const i64 stride = (i64)gridDim.x * blockDim.x;
   for (i64 idx = (i64)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += stride) {
@@ -476,17 +481,17 @@ k_abij_to_aibj(const double* __restrict__ T, double* __restrict__ out, int o, in
     const int b = (int)(q % v); q /= v;
     const int i = (int)(q % o);
     const int a = (int)(q / o);
-    out[idx] = T[(((i64)a * v + b) * o + i) * o + j];
+    out[idx] = T[(((i64)a * v + b) * o + i) * jp + j];
   }
 }
 
 // plain row-prefix pack (amplitudes_to_vector without the DIIS bookkeeping)
 __global__ void __launch_bounds__(256)
-k_pack_rows(const double* __restrict__ T, double* __restrict__ seg, i64 nov, i64 r0) {
+k_pack_rows(const double* __restrict__ T, double* __restrict__ seg, i64 nov, i64 r0, int o, int pad) {
   const i64 r = r0 + blockIdx.x;
-  const double* src = T + (i64)blockIdx.x * nov;
+  const i64 f0 = (i64)blockIdx.x * nov;
   double* dst = seg + (r * (r + 1)) / 2 - (r0 * (r0 + 1)) / 2;
-  for (i64 c = threadIdx.x; c <= r; c += blockDim.x) dst[c] = src[c];
+  for (i64 c = threadIdx.x; c <= r; c += blockDim.x) dst[c] = T[t2_addr(f0 + c, o, pad)];
 }
 
 }  // namespace mpccb
@@ -515,7 +520,7 @@ namespace mpccb {
 // fixed order) from the block's own freshly written (L1/L2-hot) values.
 __global__ void __launch_bounds__(256)
 k_t2_finalize(double* __restrict__ T, const double* __restrict__ eo, const double* __restrict__ ev,
-              const double* __restrict__ Fvo, double* __restrict__ OmP, int o, int v, int a_begin, int na,
+              const double* __restrict__ Fvo, double* __restrict__ OmP, int o, int jp, int v, int a_begin, int na,
               SymInfo sym, const unsigned char* __restrict__ flags) {
   // Mirror scheme (flags != nullptr; one byte per (a,b) block of the slab: bit 0 = this rank computes the block,
   // bit 1 = it also writes t2[b,a,:,:] = t2[a,b,:,:]^T, bits 4.. = rank that owns b): blocks without bit 0 were
@@ -525,9 +530,9 @@ k_t2_finalize(double* __restrict__ T, const double* __restrict__ eo, const doubl
   const int b = blockIdx.x, al = blockIdx.y, a = a_begin + al;
   const unsigned char f = flags ? flags[(i64)al * v + b] : (unsigned char)1;
   if (!(f & 1)) return;
-  double* blk = T + ((i64)al * v + b) * o * o;
+  double* blk = T + ((i64)al * v + b) * o * jp;
   const int s = f >> 4;
-  double* mir = (f & 2) ? sym.Tp[s] + ((i64)(b - sym.bounds[s]) * v + a) * o * o : nullptr;
+  double* mir = (f & 2) ? sym.Tp[s] + ((i64)(b - sym.bounds[s]) * v + a) * o * jp : nullptr;
   const bool diag = flags && b == a;
   const double dab = ev[a] + ev[b];
   const int npair = o * (o + 1) / 2;
@@ -537,15 +542,15 @@ k_t2_finalize(double* __restrict__ T, const double* __restrict__ eo, const doubl
     while (j * (j + 1) / 2 > p) --j;
     while ((j + 1) * (j + 2) / 2 <= p) ++j;
     const int i = p - j * (j + 1) / 2;
-    const double eij = blk[i * o + j];
-    const double eji = diag ? eij : blk[j * o + i];
+    const double eij = blk[i * jp + j];
+    const double eji = diag ? eij : blk[j * jp + i];
     const double den = eo[i] + eo[j] - dab;
     const double tij = (2.0 * eij - eji) / den, tji = (2.0 * eji - eij) / den;
-    blk[i * o + j] = tij;
-    if (i != j) blk[j * o + i] = tji;
+    blk[i * jp + j] = tij;
+    if (i != j) blk[j * jp + i] = tji;
     if (mir) {
-      mir[j * o + i] = tij;
-      if (i != j) mir[i * o + j] = tji;
+      mir[j * jp + i] = tij;
+      if (i != j) mir[i * jp + j] = tji;
     }
   }
   __threadfence_block();
@@ -554,7 +559,7 @@ k_t2_finalize(double* __restrict__ T, const double* __restrict__ eo, const doubl
   const double* f_b = Fvo + (i64)b * o;
   for (int i = warp; i < o; i += nw) {
     double sum = 0.0;
-    for (int j = lane; j < o; j += 32) sum += blk[i * o + j] * f_b[j];
+    for (int j = lane; j < o; j += 32) sum += blk[i * jp + j] * f_b[j];
     sum = warp_sum(sum);
     if (lane == 0) OmP[((i64)b * na + al) * o + i] = sum;
   }
@@ -563,7 +568,7 @@ k_t2_finalize(double* __restrict__ T, const double* __restrict__ eo, const doubl
     const i64 nov = (i64)o * v;
     for (int j = warp; j < o; j += nw) {
       double sum = 0.0;
-      for (int i = lane; i < o; i += 32) sum += blk[i * o + j] * f_a[i];
+      for (int i = lane; i < o; i += 32) sum += blk[i * jp + j] * f_a[i];
       sum = warp_sum(sum);
       if (lane == 0) sym.OmPm[(i64)al * nov + (i64)b * o + j] = sum;
     }

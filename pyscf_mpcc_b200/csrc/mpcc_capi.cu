@@ -35,10 +35,12 @@ typedef GemmCfg<2, 4, 4, 4, false, false> CfgM64RR;   // 64 x 128
 }  // namespace
 
 constexpr int DIIS_COLS_GRID = 148 * 16;
-constexpr int DIIS_ROWS_GRID = 148 * 8;      // chunks of the packed vector (k_diis_push): 8 resident CTAs per SM
+constexpr int DIIS_ROWS_GRID = 148 * 32;     // chunks of the packed vector (k_diis_push): 5 CTAs resident per SM (48 registers), 6-7 waves
 
 struct mpccb_ctx {
   int o, v, L, device, a_begin, a_end, na, ldk;
+  int jp;                          // pitch of the innermost (j) index of T[a][b][i][j] and Lvo[L][b][j]: nocc rounded up
+                                   // to even, so that the 4-D / 2-D tensor maps have 16-byte strides for odd nocc too
   i64 nov;
   cudaStream_t stream;
   long long launches;
@@ -315,7 +317,7 @@ int build_tile_list(mpccb_ctx* c) {
 
 // Yvo through one TMA launch whose 128-row tiles hold 128/nocc whole values of a: when those fill >= 85 % of the
 // tile (nocc = 64, 32, 22, 42, 110..128, ...). Other even nocc: power-of-two pieces (launch_yvo_tma_pieces).
-bool yvo_single_launch(int o) { return o % 2 == 0 && o <= 128 && (128 / o) * o >= 109; }
+bool yvo_single_launch(int o) { return o <= 128 && (128 / o) * o >= 109; }
 
 // Split-K factor of the TMA Yvo GEMM: with few output tiles per SM (a-slab sharding) the last wave is
 // mostly idle; s K-slices turn T tiles into T*s shorter CTAs. Pick s <= 8 minimising ceil(T*s/148)/s.
@@ -340,7 +342,7 @@ int choose_yvo_splits(const mpccb_ctx* c) {
 i64 carve_workspace(mpccb_ctx* c, unsigned char* base) {
   const i64 o = c->o, v = c->v, L = c->L, nov = c->nov, ldk = c->ldk, na = c->na;
   Carve w{base, 0};
-  c->Lvo = w.take(L * v * o);
+  c->Lvo = w.take(L * v * c->jp);
   c->t1 = w.take(nov);
   c->t1T = w.take(nov);
   c->t1n = w.take(nov);
@@ -439,6 +441,7 @@ int mpccb_create(mpccb_ctx** out, int nocc, int nvir, int naux, int a_begin, int
   c->a_begin = a_begin; c->a_end = a_end; c->na = a_end - a_begin;
   c->nov = (i64)nocc * nvir;
   c->ldk = (int)align_up(naux, 2);
+  c->jp = (int)align_up(nocc, 2);
   c->use_tma = 1;
   c->profile = 0;
   c->prof_ev = new std::vector<cudaEvent_t>[ST_COUNT];
@@ -551,9 +554,10 @@ int mpccb_bind_integrals(mpccb_ctx* c, const double* Loo, const double* Lov, con
   CUDA_OK(c, enter_device(c));
   if (!c->ws) return fail(c, "bind the workspace first");
   c->Loo = Loo; c->Lov = Lov; c->Lvv = Lvv; c->foo = foo; c->fvv = fvv; c->eo = eo; c->ev = ev;
-  // Lvo[L][b][j] = Lov[L][j][b]
+  // Lvo[L][b][j] = Lov[L][j][b], j pitch jp (the pad column, odd nocc only, stays zero)
+  if (c->jp != c->o) CUDA_OK(c, cudaMemsetAsync(c->Lvo, 0, sizeof(double) * c->L * c->v * c->jp, c->stream));
   dim3 grid(cdiv(c->v, 32), cdiv(c->o, 32), c->L), block(32, 8);
-  k_transpose_batched<<<grid, block, 0, c->stream>>>(Lov, c->Lvo, c->o, c->v);
+  k_transpose_batched<<<grid, block, 0, c->stream>>>(Lov, c->Lvo, c->o, c->v, c->jp);
   LAUNCH_OK(c, "k_transpose_batched(Lov)");
   return 0;
 }
@@ -620,7 +624,7 @@ extern "C" int mpccb_dress(mpccb_ctx* c, const double* t1_dev) {
     CUDA_OK(c, cudaMemcpyAsync(c->t1, t1_dev, sizeof(double) * nov, cudaMemcpyDeviceToDevice, c->stream));
   {  // t1T[a][i] = t1[i][a]
     dim3 grid(cdiv(v, 32), cdiv(o, 32), 1), block(32, 8);
-    k_transpose_batched<<<grid, block, 0, c->stream>>>(c->t1, c->t1T, o, v);
+    k_transpose_batched<<<grid, block, 0, c->stream>>>(c->t1, c->t1T, o, v, o);
     LAUNCH_OK(c, "k_transpose_batched(t1)");
   }
   {  // :119  Xov[L][i][a] = sum_b Lvv[L][a][b] t1[i][b]      M=(L, a in slab) N=i K=b
@@ -772,7 +776,7 @@ int launch_eris_t2_tma_wn(mpccb_ctx* c) {
   if (make_map_2d(c, &mB, c->JK, L, (i64)v * o, c->ldk, Cfg::TN)) return 1;
   T2Params t;
   t.T = c->T; t.eo = c->eo; t.ev = c->ev; t.Fvo = c->Fvo; t.OmP = c->OmP;
-  t.o = o; t.v = v; t.a_begin = c->a_begin; t.a_end = c->a_end; t.n_a = c->t2_na; t.n_b = c->t2_nb;
+  t.o = o; t.v = v; t.a_begin = c->a_begin; t.a_end = c->a_end; t.n_a = c->t2_na; t.n_b = c->t2_nb; t.jp = c->jp;
   TmaGemmParams p;
   memset(&p, 0, sizeof(p));
   p.M = c->na * o; p.N = v * o;
@@ -790,23 +794,24 @@ int launch_eris_t2_tma(mpccb_ctx* c) {
 
 int launch_yvo_tma(mpccb_ctx* c) {
   constexpr int TN = TmaCfg<4>::TN;
-  const int o = c->o, v = c->v, L = c->L;
+  const int o = c->o, v = c->v, L = c->L, jp = c->jp;
   const int n_a = 128 / o;
   CUtensorMap mA, mB;
   {  // T[a][b][i][j], box = (16 j, o i, 1 b, n_a a) -> smem rows (a,i) x 16 k
+    // the j extent of the map is the LOGICAL nocc (columns past it are zero-filled by TMA); only the pitch is padded
     cuuint64_t dims[4] = {(cuuint64_t)o, (cuuint64_t)o, (cuuint64_t)v, (cuuint64_t)c->na};
-    cuuint64_t strides[3] = {(cuuint64_t)o * 8, (cuuint64_t)o * o * 8, (cuuint64_t)v * o * o * 8};
+    cuuint64_t strides[3] = {(cuuint64_t)jp * 8, (cuuint64_t)o * jp * 8, (cuuint64_t)v * o * jp * 8};
     cuuint32_t box[4] = {(cuuint32_t)TMA_TK, (cuuint32_t)o, 1, (cuuint32_t)n_a};
     if (make_tensor_map(c, &mA, c->T, 4, dims, strides, box)) return 1;
   }
-  if (make_map_2d(c, &mB, c->Lvo, (i64)v * o, L, (i64)v * o, TN)) return 1;
+  if (make_map_2d(c, &mB, c->Lvo, (i64)v * jp, L, (i64)v * jp, TN)) return 1;
   TmaGemmParams p;
   memset(&p, 0, sizeof(p));
   p.M = c->na * o; p.N = L;
   p.tm_eff = n_a * o; p.tn_eff = TN;
   p.tiles_m = cdiv(c->na, n_a); p.tiles_n = cdiv(L, TN);
   p.nk = v * cdiv(o, TMA_TK);
-  p.a_mode = 1; p.jsteps = cdiv(o, TMA_TK); p.o = o; p.n_a = n_a;
+  p.a_mode = 1; p.jsteps = cdiv(o, TMA_TK); p.o = jp; p.n_a = n_a;      // p.o: K columns of Lvo per b (the j pitch)
   p.a_bytes = (uint32_t)(TMA_TK * o * n_a * 8); p.b_bytes = TN * TMA_TK * 8;
   double* Yslab = c->Y + (i64)c->a_begin * o * L;
   p.C = Yslab; p.ldc = L;
@@ -836,17 +841,17 @@ int launch_yvo_tma(mpccb_ctx* c) {
 // kernel.
 int launch_yvo_tma_pieces(mpccb_ctx* c) {
   constexpr int TN = TmaCfg<4>::TN;
-  const int o = c->o, v = c->v, L = c->L;
+  const int o = c->o, v = c->v, L = c->L, jp = c->jp;
   double* Yslab = c->Y + (i64)c->a_begin * o * L;
   CUtensorMap mB;
-  if (make_map_2d(c, &mB, c->Lvo, (i64)v * o, L, (i64)v * o, TN)) return 1;
+  if (make_map_2d(c, &mB, c->Lvo, (i64)v * jp, L, (i64)v * jp, TN)) return 1;
   int i0 = 0;
-  for (int w = 128; w >= 2; w >>= 1) {
+  for (int w = 128; w >= 1; w >>= 1) {
     while (o - i0 >= w) {
       const int n_a = 128 / w;
       CUtensorMap mA;
       cuuint64_t dims[4] = {(cuuint64_t)o, (cuuint64_t)o, (cuuint64_t)v, (cuuint64_t)c->na};
-      cuuint64_t strides[3] = {(cuuint64_t)o * 8, (cuuint64_t)o * o * 8, (cuuint64_t)v * o * o * 8};
+      cuuint64_t strides[3] = {(cuuint64_t)jp * 8, (cuuint64_t)o * jp * 8, (cuuint64_t)v * o * jp * 8};
       cuuint32_t box[4] = {(cuuint32_t)TMA_TK, (cuuint32_t)w, 1, (cuuint32_t)n_a};
       if (make_tensor_map(c, &mA, c->T, 4, dims, strides, box)) return 1;
       TmaGemmParams p;
@@ -855,7 +860,7 @@ int launch_yvo_tma_pieces(mpccb_ctx* c) {
       p.tm_eff = TMA_TM; p.tn_eff = TN;
       p.tiles_m = cdiv(c->na, n_a); p.tiles_n = cdiv(L, TN);
       p.nk = v * cdiv(o, TMA_TK);
-      p.a_mode = 1; p.jsteps = cdiv(o, TMA_TK); p.o = o; p.n_a = n_a; p.i0 = i0;
+      p.a_mode = 1; p.jsteps = cdiv(o, TMA_TK); p.o = jp; p.n_a = n_a; p.i0 = i0;
       p.a_bytes = TMA_TM * TMA_TK * 8; p.b_bytes = TN * TMA_TK * 8;
       p.ksplit = 1;
       p.out = flat_output(Yslab + (i64)i0 * L, 0, 1);
@@ -874,8 +879,8 @@ int launch_eris_t2_unfused(mpccb_ctx* c) {
   Operand A = flat_operand(c->JK + (i64)c->a_begin * o * c->ldk, c->na * o, c->ldk, 1);
   Operand B = flat_operand(c->JK, v * o, c->ldk, 1);
   Output C = flat_output(c->T, 0, 0);
-  C.mdiv = o; C.m_hi = (i64)v * o * o; C.m_lo = o;      // m = (a_l, i)
-  C.ndiv = o; C.n_hi = (i64)o * o;     C.n_lo = 1;      // n = (b, j)
+  C.mdiv = o; C.m_hi = (i64)v * o * c->jp; C.m_lo = c->jp;   // m = (a_l, i)
+  C.ndiv = o; C.n_hi = (i64)o * c->jp;     C.n_lo = 1;       // n = (b, j)
   const unsigned char* flags = c->sym.enabled ? c->blkflags : nullptr;     // mirror scheme (build_tile_list)
   C.keep = flags; C.keep_ld = v;
   if (c->use_tma) {
@@ -903,7 +908,7 @@ int launch_eris_t2_unfused(mpccb_ctx* c) {
   dim3 grid(v, c->na);
   SymInfo sym = c->sym;
   sym.Tp[sym.rank] = c->T;
-  k_t2_finalize<<<grid, 256, 0, c->stream>>>(c->T, c->eo, c->ev, c->Fvo, c->OmP, o, v, c->a_begin, c->na, sym, flags);
+  k_t2_finalize<<<grid, 256, 0, c->stream>>>(c->T, c->eo, c->ev, c->Fvo, c->OmP, o, c->jp, v, c->a_begin, c->na, sym, flags);
   LAUNCH_OK(c, "k_t2_finalize");
   return 0;
 }
@@ -917,7 +922,7 @@ int launch_eris_t2(mpccb_ctx* c) {
   Operand B = flat_operand(c->JK, v * o, c->ldk, 1);
   T2Params p;
   p.T = c->T; p.eo = c->eo; p.ev = c->ev; p.Fvo = c->Fvo; p.OmP = c->OmP;
-  p.o = o; p.v = v; p.a_begin = c->a_begin; p.a_end = c->a_end; p.n_a = c->t2_na; p.n_b = c->t2_nb;
+  p.o = o; p.v = v; p.a_begin = c->a_begin; p.a_end = c->a_end; p.n_a = c->t2_na; p.n_b = c->t2_nb; p.jp = c->jp;
   GemmDims d;
   d.M = c->na * o; d.N = v * o; d.K = L;
   d.tm_eff = c->t2_na * o; d.tn_eff = c->t2_nb * o;
@@ -931,15 +936,16 @@ int launch_eris_t2(mpccb_ctx* c) {
 
 int launch_yvo(mpccb_ctx* c) {
   const int o = c->o, v = c->v, L = c->L;
-  // TMA strides must be multiples of 16 bytes: even nocc
+  // TMA strides must be multiples of 16 bytes: the j pitch of T and Lvo is nocc rounded up to even
   if (c->use_tma && yvo_single_launch(o)) return launch_yvo_tma(c);
-  if (c->use_tma && o % 2 == 0) return launch_yvo_tma_pieces(c);
+  if (c->use_tma) return launch_yvo_tma_pieces(c);
   // :138  Y[(a,i)][L] = sum_{(b,j)} T[a][b][i][j] Lvo[L][(b,j)]
   Operand A;
   A.base = c->T; A.rows = c->na * o;
-  A.rdiv = o; A.r_hi = (i64)v * o * o; A.r_lo = o;
-  A.kdiv = o; A.k_hi = (i64)o * o; A.k_lo = 1;
-  Operand B = flat_operand(c->Lvo, L, (i64)v * o, 1);
+  A.rdiv = o; A.r_hi = (i64)v * o * c->jp; A.r_lo = c->jp;
+  A.kdiv = o; A.k_hi = (i64)o * c->jp; A.k_lo = 1;
+  Operand B = flat_operand(c->Lvo, L, (i64)v * c->jp, 1);
+  B.kdiv = o; B.k_hi = c->jp; B.k_lo = 1;
   Output C = flat_output(c->Y + (i64)c->a_begin * o * L, L, 1);
   return launch_gemm<CfgBigKK>(c, "Yvo", A, B, C, c->na * o, L, v * o, 1, nullptr);
 }
@@ -1011,8 +1017,8 @@ extern "C" int mpccb_doubles_end(mpccb_ctx* c, double* red_dev) {
   }
   {  // :141-142 (Lov.t1 part)  Z[j][i] = sum_{(b,L)} Lvo[L][b][j] Y[(b,i)][L];  Om[a][i] += sum_j t1[j][a] Z[j][i]
     Operand A;
-    A.base = c->Lvo + (i64)c->a_begin * o; A.rows = o; A.rdiv = BIG; A.r_hi = 0; A.r_lo = 1;
-    A.kdiv = L; A.k_hi = o; A.k_lo = (i64)v * o;
+    A.base = c->Lvo + (i64)c->a_begin * c->jp; A.rows = o; A.rdiv = BIG; A.r_hi = 0; A.r_lo = 1;
+    A.kdiv = L; A.k_hi = c->jp; A.k_lo = (i64)v * c->jp;
     if (splitk_gemm<CfgN64RK>(c, "Lov.Yvo", A, By, c->Z, o, o, na * L, 1.0, 0.0)) return 1;
     k_add_t1T_Z<<<cdiv(nov, 256), 256, 0, c->stream>>>(Om, c->t1, c->Z, o, v);
     LAUNCH_OK(c, "k_add_t1T_Z");
@@ -1073,7 +1079,7 @@ extern "C" int mpccb_t2_to_aibj(mpccb_ctx* c, double* out_dev) {
   if (!c->T) return fail(c, "t2 buffer not bound");
   const i64 total = (i64)c->na * c->v * c->o * c->o;
   const int nb = (int)std::min<i64>(cdiv(total, 256), 148 * 16);
-  k_abij_to_aibj<<<nb, 256, 0, c->stream>>>(c->T, out_dev, c->o, c->v, c->na);
+  k_abij_to_aibj<<<nb, 256, 0, c->stream>>>(c->T, out_dev, c->o, c->jp, c->v, c->na);
   LAUNCH_OK(c, "k_abij_to_aibj");
   return 0;
 }
@@ -1086,7 +1092,7 @@ int launch_diis_cols(mpccb_ctx* c, const double* t1_new_dev, const double* xprev
   const int G = (int)std::min<i64>(nblocks, DIIS_COLS_GRID);
   if ((i64)(G + 1) * 7 > c->P_count) return fail(c, "DIIS partial scratch too small");
   k_diis_push_cols<<<G + 1, 256, 0, c->stream>>>(c->T, t1_new_dev, xprev_dev, pv, x_slot_dev, e_slot_dev, ep, nd, slot,
-                                                 first_call, count_t1, c->o, c->v, c->a_begin, c->na,
+                                                 first_call, count_t1, c->o, c->jp, c->v, c->a_begin, c->na,
                                                  reinterpret_cast<const i64*>(c->diis_prefix), G, c->P, scatter_to);
   LAUNCH_OK(c, "k_diis_push_cols");
   if (grid_out) *grid_out = G + 1;
@@ -1107,7 +1113,7 @@ extern "C" int mpccb_pack_tril_rows(mpccb_ctx* c, double* seg_dev) {
     DiisPrev pv = {};
     return launch_diis_cols(c, nullptr, nullptr, pv, seg_dev - c->nov, nullptr, ep, 0, 0, 1, 0, nullptr, nullptr);
   }
-  k_pack_rows<<<c->na * c->o, 256, 0, c->stream>>>(c->T, seg_dev, c->nov, (i64)c->a_begin * c->o);
+  k_pack_rows<<<c->na * c->o, 256, 0, c->stream>>>(c->T, seg_dev, c->nov, (i64)c->a_begin * c->o, c->o, c->jp - c->o);
   LAUNCH_OK(c, "k_pack_rows");
   return 0;
 }
@@ -1160,7 +1166,7 @@ extern "C" int mpccb_diis_push(mpccb_ctx* c, const double* t1_new_dev, const dou
     grid = G + 1;
     if ((i64)grid * 7 > c->P_count) return fail(c, "DIIS partial scratch too small");
     k_diis_push<<<grid, 256, 0, c->stream>>>(c->T, t1_new_dev, xprev_dev, pv, x_slot_dev, e_slot_dev, ep, nd, slot,
-                                             first_call, count_t1, c->nov, r0, nrows, chunk, G, c->P);
+                                             first_call, count_t1, c->nov, r0, nrows, chunk, G, c->o, c->jp - c->o, c->P);
     LAUNCH_OK(c, "k_diis_push");
   }
   if (!first_call) {
@@ -1259,13 +1265,13 @@ extern "C" int mpccb_get_buffer(mpccb_ctx* c, const char* name, double** ptr, lo
   const i64 o = c->o, v = c->v, L = c->L, nov = c->nov;
   struct Ent { const char* n; double* p; i64 cnt; };
   const Ent tab[] = {
-      {"Lvo", c->Lvo, L * v * o},   {"t1", c->t1, nov},          {"t1n", c->t1n, nov},
+      {"Lvo", c->Lvo, L * v * c->jp},   {"t1", c->t1, nov},          {"t1n", c->t1n, nov},
       {"Xov", c->Xov, L * o * v},   {"Xoo", c->Xoo, L * o * o},   {"Joo", c->Joo, L * o * o},
       {"X", c->X, L},               {"XT", c->XT, L * o * v},     {"JT", c->JT, L * o * v},
       {"JK", c->JK, nov * c->ldk},  {"E1K", c->E1K, nov * c->ldk}, {"Wov", c->Wov, L * o * v},
       {"w", c->w, nov},             {"Fvo", c->Fvo, nov},         {"Y", c->Y, nov * L},
       {"OmRep", c->OmRep, nov},     {"OmTot", c->OmTot, nov},     {"Z", c->Z, o * o},
-      {"red", c->red, nov + 1},     {"T", c->T, (i64)c->na * v * o * o},
+      {"red", c->red, nov + 1},     {"T", c->T, (i64)c->na * v * o * c->jp},
   };
   for (const Ent& e : tab)
     if (!strcmp(e.n, name)) { *ptr = e.p; *count = e.cnt; return 0; }

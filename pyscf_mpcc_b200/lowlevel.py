@@ -188,6 +188,9 @@ class MPCC_LL:
             self.mo_coeff = None
         self.nvir_pair = self.nvir * (self.nvir + 1) // 2
         self.nov = self.nocc * self.nvir
+        # pitch of the innermost index of the device t2 buffer T[a][b][i][j] (and of Lvo[L][b][j]): nocc rounded up to
+        # even, so the TMA tensor maps of the Yvo GEMM are legal for odd nocc as well (16-byte strides)
+        self._jp = self.nocc + (self.nocc & 1)
         o, v, L = self.nocc, self.nvir, self.naux
 
         # --- native context, workspace, device buffers (torch owns the memory) ---
@@ -246,7 +249,8 @@ class MPCC_LL:
         if self.world_size > 1 and self._t2_sym and self._jk_mode in ("multicast", "p2p"):
             self._setup_t2_peers()
         if not self._t2_peers:
-            self._T = torch.empty(self._na * v * o * o, **f64)
+            # odd nocc: the pad column is read by TMA boxes (and multiplied by Lvo's zero column) — it must stay finite
+            self._T = (torch.zeros if self._jp != o else torch.empty)(self._na * v * o * self._jp, **f64)
             self._ctx.call("mpccb_bind_t2", self._T.data_ptr())
         self._t2_serial = 0
         self._red = torch.zeros(self.nov + 1, **f64)
@@ -347,7 +351,7 @@ class MPCC_LL:
         """(L,v,o) transpose of Lov — the reference builds it (:50,:63) and never uses it; here it
         is the K-major operand of the Yvo GEMM."""
         p, n = self._ctx.buffer("Lvo")
-        return self._read_device(p, n).reshape(self.naux, self.nvir, self.nocc)
+        return np.ascontiguousarray(self._read_device(p, n).reshape(self.naux, self.nvir, self._jp)[:, :, :self.nocc])
 
     @property
     def D(self):
@@ -363,7 +367,10 @@ class MPCC_LL:
     def debug_buffer(self, name):
         """Host copy of a named scratch tensor (tests / profiling only)."""
         p, n = self._ctx.buffer(name)
-        return self._read_device(p, n)
+        out = self._read_device(p, n)
+        if name in ("T", "Lvo") and self._jp != self.nocc:        # strip the pad column of the j index
+            out = np.ascontiguousarray(out.reshape(-1, self._jp)[:, :self.nocc]).reshape(-1)
+        return out
 
     # ------------------------------------------------------------------ :46-69
     def compute_three_center_ints(self):
@@ -465,7 +472,7 @@ class MPCC_LL:
         dist = torch.distributed
         o, v = self.nocc, self.nvir
         bounds = self._bounds
-        n_max = max(bounds[r + 1] - bounds[r] for r in range(self.world_size)) * v * o * o
+        n_max = max(bounds[r + 1] - bounds[r] for r in range(self.world_size)) * v * o * self._jp
         ok, buf, hdl = 0, None, None
         if not self._symm_agreed():
             return
@@ -482,7 +489,11 @@ class MPCC_LL:
             return
         peers = (ctypes.c_void_p * self.world_size)(*[int(p) for p in hdl.buffer_ptrs])
         self._ctx.call("mpccb_bind_t2_peers", self.world_size, self.rank, (ctypes.c_int * (self.world_size + 1))(*bounds), peers)
-        self._T = buf[:self._na * v * o * o]
+        if self._jp != o:
+            buf.zero_()
+            self._sync()
+            hdl.barrier(channel=1)
+        self._T = buf[:self._na * v * o * self._jp]
         self._t2_buf, self._t2_hdl = buf, hdl
         self._t2_peers = True
 
@@ -631,8 +642,13 @@ class MPCC_LL:
         if self.world_size > 1:
             raise NotImplementedError("host t2 upload with several ranks")
         m = np.ascontiguousarray(t2.transpose(0, 2, 1, 3)).reshape(-1)
-        if m.size != self._T.numel():
+        o, jp = self.nocc, self._jp
+        if m.size * jp != self._T.numel() * o:
             raise ValueError("t2 has the wrong size")
+        if jp != o:                                    # rows of nocc elements onto the even pitch of the device buffer
+            padded = np.zeros((m.size // o, jp))
+            padded[:, :o] = m.reshape(-1, o)
+            m = padded.reshape(-1)
         self._T.copy_(torch.from_numpy(m))
         self._t2_serial += 1
 
