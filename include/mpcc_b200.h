@@ -128,6 +128,16 @@ int mpccb_diis_push(mpccb_ctx* ctx, const double* t1_new_dev, const double* xpre
                     const double* const* x_prev_list_dev, const double* coeff_prev_host, int n_prev,
                     double* x_slot_dev, double* e_slot_dev, const double* const* e_list_dev,
                     int nd, int slot, int first_call, int count_t1, double* dots_dev);
+/* the same push for a plain device vector of n doubles (the CCSD-type stage packs its own vector,
+ * pyscf/cc/ccsd.py:719-726, and feeds it to lib.diis.DIIS.update, ccsd.py:1269-1276) */
+int mpccb_vec_diis_push(mpccb_ctx* ctx, const double* x_new_dev, long long n, const double* xprev_dev,
+                        const double* const* x_prev_list_dev, const double* coeff_prev_host, int n_prev,
+                        double* x_slot_dev, double* e_slot_dev, const double* const* e_list_dev,
+                        int nd, int slot, int first_call, double* dots_dev);
+/* lib.pack_tril / lib.unpack_tril(filltriu=SYMMETRIC) of one (n,n) row-major matrix
+ * (NPdpack_tril, NPdunpack_tril + NPdsymm_triu: pyscf/lib/np_helper/pack_tril.c:24-37,58-69,99-107) */
+int mpccb_pack_tril(mpccb_ctx* ctx, const double* M_dev, long long n, double* packed_dev);
+int mpccb_unpack_tril(mpccb_ctx* ctx, const double* packed_dev, long long n, double* full_dev);
 /* xnew = sum_{k<nd} coeff[k] * x_list[k]  (n doubles each) */
 int mpccb_diis_combine(mpccb_ctx* ctx, const double* const* x_list_dev, const double* coeff_host,
                        int nd, double* xnew_dev, long long n);

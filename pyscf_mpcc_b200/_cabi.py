@@ -53,6 +53,10 @@ SIGNATURES = {
     "mpccb_unpack_oovv": (c_int, [c_void_p, c_void_p, c_void_p]),
     "mpccb_diis_push": (c_int, [c_void_p, c_void_p, c_void_p, ctypes.POINTER(c_void_p), c_double_p, c_int,
                                 c_void_p, c_void_p, ctypes.POINTER(c_void_p), c_int, c_int, c_int, c_int, c_void_p]),
+    "mpccb_vec_diis_push": (c_int, [c_void_p, c_void_p, c_ll, c_void_p, ctypes.POINTER(c_void_p), c_double_p, c_int,
+                                    c_void_p, c_void_p, ctypes.POINTER(c_void_p), c_int, c_int, c_int, c_void_p]),
+    "mpccb_pack_tril": (c_int, [c_void_p, c_void_p, c_ll, c_void_p]),
+    "mpccb_unpack_tril": (c_int, [c_void_p, c_void_p, c_ll, c_void_p]),
     "mpccb_diis_combine": (c_int, [c_void_p, ctypes.POINTER(c_void_p), c_double_p, c_int, c_void_p, c_ll]),
     "mpccb_get_buffer": (c_int, [c_void_p, ctypes.c_char_p, ctypes.POINTER(c_void_p), ctypes.POINTER(c_ll)]),
     "mpccb_copy_to_host": (c_int, [c_void_p, c_void_p, c_void_p, c_ll]),

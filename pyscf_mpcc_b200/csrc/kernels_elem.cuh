@@ -313,6 +313,51 @@ k_diis_push(const double* __restrict__ T, const double* __restrict__ t1new,
   }
 }
 
+// The same update for a plain device vector of n elements (the CCSD-type stage packs its own vector,
+// ccsd.py:719-726): xs = xnew, es = xnew - xprev, dots[k] += es . e_k. Grid-stride; partial layout [gridDim.x][7].
+__global__ void __launch_bounds__(256)
+k_vec_diis_push(const double* __restrict__ xnew, const double* xprev, DiisPrev pv, double* xs, double* es,
+                DiisPtrs eptr, int nd, int slot, int first_call, i64 n, double* __restrict__ partial) {
+  __shared__ double scratch[32];
+  double d[6] = {0, 0, 0, 0, 0, 0};
+  const i64 stride = (i64)gridDim.x * blockDim.x;
+  for (i64 p = (i64)blockIdx.x * blockDim.x + threadIdx.x; p < n; p += stride) {
+    const double val = xnew[p];
+    if (first_call) {
+      xs[p] = val;
+    } else {
+      const double e = val - diis_prev_value(pv, xprev, p);
+      double other[6];
+#pragma unroll
+      for (int k = 0; k < 6; ++k) other[k] = (k < nd && k != slot) ? eptr.e[k][p] : 0.0;
+      xs[p] = val;
+      es[p] = e;
+#pragma unroll
+      for (int k = 0; k < 6; ++k)
+        if (k < nd) d[k] = fma(e, (k == slot) ? e : other[k], d[k]);
+    }
+  }
+  if (!first_call) {
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+      if (k < nd) {
+        const double s = block_sum(d[k], scratch);
+        if (threadIdx.x == 0) partial[(i64)blockIdx.x * 7 + k] = s;
+      }
+    }
+  }
+}
+
+// packed[r(r+1)/2 + c] = M[r*n + c], c <= r: lib.pack_tril of an (n x n) matrix (NPdpack_tril,
+// pyscf/lib/np_helper/pack_tril.c:99-107). One block per row.
+__global__ void __launch_bounds__(256)
+k_pack_tril(const double* __restrict__ M, double* __restrict__ packed, i64 n) {
+  const i64 r = blockIdx.x;
+  const double* src = M + r * n;
+  double* dst = packed + (r * (r + 1)) / 2;
+  for (i64 c = threadIdx.x; c <= r; c += blockDim.x) dst[c] = src[c];
+}
+
 // ---------------------------------------------------------------------------
 // Column-owned form of the same vector (several ranks). Row r of the packed triangle has r+1 elements, so a
 // row-sharded vector gives the last of P ranks (2P-1) times the bytes of the first one and everybody waits for it at

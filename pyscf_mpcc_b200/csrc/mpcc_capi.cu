@@ -1176,6 +1176,52 @@ extern "C" int mpccb_diis_push(mpccb_ctx* c, const double* t1_new_dev, const dou
   return 0;
 }
 
+// DIIS push for a plain device vector (CCSD-type stage): same arithmetic as mpccb_diis_push without the t2 packing
+extern "C" int mpccb_vec_diis_push(mpccb_ctx* c, const double* x_new_dev, long long n, const double* xprev_dev,
+                                   const double* const* x_prev_list_dev, const double* coeff_prev_host, int n_prev,
+                                   double* x_slot_dev, double* e_slot_dev, const double* const* e_list_dev,
+                                   int nd, int slot, int first_call, double* dots_dev) {
+  CUDA_OK(c, enter_device(c));
+  if (!c->ws) return fail(c, "bind the workspace first");
+  if (nd < 0 || nd > 6 || slot < 0 || slot > 5 || n_prev < 0 || n_prev > 6 || n <= 0) return fail(c, "bad DIIS arguments");
+  if (!first_call && n_prev == 0 && !xprev_dev) return fail(c, "DIIS push needs xprev (explicit or as a combination)");
+  DiisPtrs ep;
+  for (int k = 0; k < 6; ++k) ep.e[k] = (k < nd && e_list_dev) ? e_list_dev[k] : nullptr;
+  DiisPrev pv;
+  pv.n = n_prev;
+  for (int k = 0; k < 6; ++k) {
+    pv.x[k] = k < n_prev ? x_prev_list_dev[k] : nullptr;
+    pv.c[k] = k < n_prev ? coeff_prev_host[k] : 0.0;
+  }
+  const int grid = (int)std::min<i64>(std::max<i64>(cdiv(n, 2048), 1), std::min<i64>(NSM * 8, c->P_count / 7));
+  k_vec_diis_push<<<grid, 256, 0, c->stream>>>(x_new_dev, xprev_dev, pv, x_slot_dev, e_slot_dev, ep, nd, slot,
+                                               first_call, n, c->P);
+  LAUNCH_OK(c, "k_vec_diis_push");
+  if (!first_call) {
+    k_final_sums_strided<<<1, 256, 0, c->stream>>>(c->P, dots_dev, grid, 7, nd);
+    LAUNCH_OK(c, "k_final_sums_strided");
+  }
+  return 0;
+}
+
+// lib.pack_tril / lib.unpack_tril(filltriu=SYMMETRIC) of one (n x n) matrix on the device
+// (pyscf/lib/numpy_helper.py:256-358; the CCSD-type stage's amplitudes_to_vector / vector_to_amplitudes, ccsd.py:719-735)
+extern "C" int mpccb_pack_tril(mpccb_ctx* c, const double* M_dev, long long n, double* packed_dev) {
+  CUDA_OK(c, enter_device(c));
+  if (n <= 0 || n > INT_MAX) return fail(c, "pack_tril: bad n");
+  k_pack_tril<<<(int)n, 256, 0, c->stream>>>(M_dev, packed_dev, n);
+  LAUNCH_OK(c, "k_pack_tril");
+  return 0;
+}
+
+extern "C" int mpccb_unpack_tril(mpccb_ctx* c, const double* packed_dev, long long n, double* full_dev) {
+  CUDA_OK(c, enter_device(c));
+  if (n <= 0 || n > INT_MAX) return fail(c, "unpack_tril: bad n");
+  k_unpack_tril_sym<<<dim3((int)n, 1), 256, 0, c->stream>>>(packed_dev, full_dev, (int)n, n * (n + 1) / 2);
+  LAUNCH_OK(c, "k_unpack_tril_sym");
+  return 0;
+}
+
 extern "C" int mpccb_diis_combine(mpccb_ctx* c, const double* const* x_list_dev, const double* coeff_host,
                                   int nd, double* xnew_dev, long long n) {
   CUDA_OK(c, enter_device(c));

@@ -227,3 +227,66 @@ class AmplitudeVector:
 
     def __array__(self, dtype=None, copy=None):
         return self.numpy()
+
+
+class VectorDIIS:
+    """``lib.diis.DIIS`` (``pyscf/lib/diis.py:100-275``) for plain device vectors, as the CCSD-type stage uses it
+    (``ccsd.kernel`` builds ``lib.diis.DIIS(mycc, ...)`` with ``space = mycc.diis_space`` and ``run_diis`` feeds it
+    ``amplitudes_to_vector(t1, t2)``, ``pyscf/cc/ccsd.py:71-76,1269-1276``). Same ring / B-matrix / solve as
+    :class:`DIIS`; the vectors are flat buffers of a backend (``tensor_engine.CudaBackend`` in the product, a NumPy
+    stand-in in the CPU tests) which provides ``vec_diis_push`` and ``combine``."""
+
+    def __init__(self, backend, space=6, min_space=1):
+        self.be = backend
+        self.space = space
+        self.min_space = min_space
+        self._bookkeep = []
+        self._head = 0
+        self._H = None
+        self._xprev = None
+        self._prev = None
+        self._x = {}
+        self._e = {}
+        self.last_coeff = None
+
+    def get_num_vec(self):
+        return len(self._bookkeep)
+
+    def update(self, x, n):
+        """Push the device vector ``x`` (n doubles) and return a NEW device vector with the extrapolation."""
+        be = self.be
+        if len(self._bookkeep) >= self.space:
+            self._bookkeep = self._bookkeep[1 - self.space:]
+        if self._xprev is None:
+            self._xprev = be.empty(n)
+            be.vec_diis_push(x, n, None, [], [], self._xprev, None, [], 0, 0, True)
+            return be.copy(self._xprev)
+        if self._head >= self.space:
+            self._head = 0
+        slot = self._head
+        self._bookkeep.append(slot)
+        if slot not in self._x:
+            self._x[slot] = be.empty(n)
+            self._e[slot] = be.empty(n)
+        self._head += 1
+        nd = self.get_num_vec()
+        prev_x, prev_c = [], []
+        if self._prev is not None:
+            prev_c, slots = self._prev
+            prev_x = [self._x[s] for s in slots]
+        d = be.vec_diis_push(x, n, self._xprev, prev_x, prev_c, self._x[slot], self._e[slot],
+                             [self._e[k] for k in range(nd)], nd, slot, False)
+        if nd < self.min_space:
+            return be.copy(self._x[slot])
+        if self._H is None:
+            self._H = np.zeros((self.space + 1, self.space + 1))
+            self._H[0, 1:] = self._H[1:, 0] = 1
+        for i in range(nd):
+            self._H[self._head, i + 1] = d[i]
+            self._H[i + 1, self._head] = d[i]
+        c = solve_diis_system(self._H[:nd + 1, :nd + 1])
+        self.last_coeff = c
+        self._prev = ([float(c[k + 1]) for k in range(nd)], list(range(nd)))
+        out = be.empty(n)
+        be.combine([self._x[k] for k in range(nd)], self._prev[0], out, n)
+        return out

@@ -111,7 +111,7 @@ def _rows(t, lo, hi):
     return DTensor(t.buf[lo * inner:hi * inner], (hi - lo,) + t.shape[1:])
 
 
-def _pp_ladder(eng, eris, t1, tau, t2new, slab_bytes=4 << 30):
+def _pp_ladder(eng, eris, t1, tau, t2new, slab_bytes=4 << 30, group=None):
     """t2new[i,j,a,b] += sum_cd W[a,b,c,d] tau[i,j,c,d]  (:138), W = cc_Wvvvv (rintermediates.py:92-99):
         W[a,b,c,d] = (ac|bd) - sum_k (kd|ac) t1[k,b] - sum_k (kc|bd) t1[k,a]
     evaluated for slabs of the first virtual index a; (ac|bd) = sum_L Lvv[L,a,c] Lvv[L,b,d] is formed per
@@ -127,17 +127,26 @@ def _pp_ladder(eng, eris, t1, tau, t2new, slab_bytes=4 << 30):
     LB = eng.transpose(eris.Lvv, (1, 2, 0))                       # [b, d, L]
     OA = eng.transpose(eris.ovvv, (2, 3, 1, 0))                   # ovvv[k,d,a,c] -> [a, c, d, k]
     R = eng.zeros((v, v) + tau.shape[:2])                         # [a, b, i, j]
-    for a0 in range(0, v, na):
+    # several ranks: the slabs of the first virtual index are dealt round-robin (north_star: "the ladder ... shards
+    # naturally over ab"); every rank fills its rows of R, one all-reduce (sum with zeros) completes it
+    rank, world = (0, 1) if group is None else eng.be.rank_and_size(group)
+    if world > 1:
+        na = max(1, min(na, -(-v // world)))
+    for n_slab, a0 in enumerate(range(0, v, na)):
+        if n_slab % world != rank:
+            continue
         a1 = min(v, a0 + na)
         W = E("acL,bdL->acbd", _rows(LA, a0, a1), LB)             # (ac|bd) - sum_k t1[k,a](kc|bd)
         E("acdk,kb->acbd", _rows(OA, a0, a1), t1, alpha=-1.0, out=W, beta=1.0)   # - sum_k (kd|ac) t1[k,b]
         E("acbd,ijcd->abij", W, tau, out=_rows(R, a0, a1))
         del W
+    if world > 1:
+        eng.be.all_reduce(R.buf, group)
     eng.add(t2new, R, 1.0, (2, 3, 0, 1))
     return t2new
 
 
-def _intermediates(eng, t1, t2, tau, eris, f):
+def _intermediates(eng, t1, t2, tau, eris, f, cc2=False):
     """Foo, Fvv, Fov (rintermediates.py:29-59), Loo, Lvv (:63-79), Woooo, Wvoov, Wvovo (:83-126).
     `f` holds the fock blocks as device tensors (fov, foo, fvv)."""
     E = eng.einsum
@@ -154,6 +163,8 @@ def _intermediates(eng, t1, t2, tau, eris, f):
     Fvv = E("kcld,klad->ac", lov, t2, alpha=-1.0)                 # (:44-45)
     E("kc,ka->ac", dFov, t1, alpha=-1.0, out=Fvv, beta=1.0)       # (:46-47)
     eng.add(Fvv, f["fvv"])
+    if cc2:                      # the CC2 doubles equation (:115-133) uses none of the kappa / W intermediates
+        return dict(Foo=Foo, Fvv=Fvv, Fov=Fov)
     Loo = eng.copy(Foo)                                           # (:63-70)
     E("kc,ic->ki", f["fov"], t1, out=Loo, beta=1.0)
     E("lcki,lc->ki", ovoo, t1, alpha=2.0, out=Loo, beta=1.0)
@@ -203,11 +214,12 @@ def make_tau(eng, t1, t2):
 
 
 def update_amps(cc, t1, t2, eris, act_hole=(), act_particle=(), idx_singles=(), idx_doubles=()):
-    """One RCCSD amplitude update with active-space overwrite — ``rmpccsd_slow.update_amps`` (:73-180, the
-    ``cc.cc2 == False`` branch). ``t1``/``t2`` are :class:`DTensor` (o,v)/(o,o,v,v) or numpy arrays (uploaded;
-    the result then comes back as numpy). ``eris`` is a :class:`DFERIs`."""
-    if getattr(cc, "cc2", False):
-        raise NotImplementedError("the cc2 branch (:122-133) is not built")
+    """One amplitude update with active-space overwrite — ``rmpccsd_slow.update_amps`` (:73-180): the full RCCSD
+    doubles equation (:134-149) or, with ``cc.cc2``, the CC2 one (:115-133). ``t1``/``t2`` are :class:`DTensor`
+    (o,v)/(o,o,v,v) or numpy arrays (uploaded; the result then comes back as numpy). ``eris`` is a :class:`DFERIs`.
+    ``cc.group`` (optional torch.distributed group): the particle-particle ladder is sharded over its ranks."""
+    cc2 = bool(getattr(cc, "cc2", False))
+    group = getattr(cc, "group", None)
     eng = eris.eng
     as_numpy = not isinstance(t1, DTensor)
     if as_numpy:
@@ -217,10 +229,13 @@ def update_amps(cc, t1, t2, eris, act_hole=(), act_particle=(), idx_singles=(), 
     f = _fock_blocks(eng, eris)
     ovvv, ooov, ovvo, oovv, ovov = eris.ovvv, eris.ooov, eris.ovvo, eris.oovv, eris.ovov
     tau = make_tau(eng, t1, t2)
-    im = _intermediates(eng, t1, t2, tau, eris, f)
+    im = _intermediates(eng, t1, t2, tau, eris, f, cc2=cc2)
     Foo, Fvv, Fov = im["Foo"], im["Fvv"], im["Fov"]
     # move energy terms to the other side (:90-91, :135)
-    for x, d in ((Foo, "foo_diag"), (Fvv, "fvv_diag"), (im["Loo"], "foo_diag"), (im["Lvv"], "fvv_diag")):
+    shifted = ((Foo, "foo_diag"), (Fvv, "fvv_diag"))
+    if not cc2:
+        shifted += ((im["Loo"], "foo_diag"), (im["Lvv"], "fvv_diag"))
+    for x, d in shifted:
         eng.add(x, f[d], -1.0)
 
     # ---- T1 equation (:93-111) ----
@@ -250,15 +265,34 @@ def update_amps(cc, t1, t2, eris, act_hole=(), act_particle=(), idx_singles=(), 
 
     # ---- T2 equation (:114-162) ----
     t2new = eng.transpose(ovov, (0, 2, 1, 3))
-    E("klij,klab->ijab", im["Woooo"], tau, out=t2new, beta=1.0)          # hole-hole ladder (:137)
-    _pp_ladder(eng, eris, t1, tau, t2new)                                 # particle-particle ladder (:138)
-    _sym_add(eng, t2new, E("ac,ijcb->ijab", im["Lvv"], t2), 1.0)          # (:139-140)
-    _sym_add(eng, t2new, E("ki,kjab->ijab", im["Loo"], t2), -1.0)         # (:141-142)
-    tmp = E("akic,kjcb->ijab", im["Wvoov"], t2, alpha=2.0)                # ring (:143-145)
-    E("akci,kjcb->ijab", im["Wvovo"], t2, alpha=-1.0, out=tmp, beta=1.0)
-    _sym_add(eng, t2new, tmp, 1.0)
-    _sym_add(eng, t2new, E("akic,kjbc->ijab", im["Wvoov"], t2), -1.0)     # exchange (:146-149)
-    _sym_add(eng, t2new, E("bkci,kjac->ijab", im["Wvovo"], t2), -1.0)
+    if cc2:
+        # CC2 (:115-133): both ladders act on t1 (x) t1 only — Woooo2 / Wvvvv of :116-126 are cc_Woooo / cc_Wvvvv
+        # with t2 = 0, and 'klij,ka,lb->ijab' / 'abcd,ic,jd->ijab' contract them with tau1[i,j,a,b] = t1[i,a] t1[j,b]
+        tau1 = E("ia,jb->ijab", t1, t1)
+        Woooo2 = eng.transpose(eris.oooo, (0, 2, 1, 3))                   # (:116)
+        E("lcki,jc->klij", eris.ovoo, t1, out=Woooo2, beta=1.0)           # (:117)  ooov[k,i,l,c] = ovoo[l,c,k,i]
+        E("kclj,ic->klij", eris.ovoo, t1, out=Woooo2, beta=1.0)           # (:118)
+        E("kcld,ijcd->klij", ovov, tau1, out=Woooo2, beta=1.0)            # (:119)
+        E("klij,klab->ijab", Woooo2, tau1, out=t2new, beta=1.0)           # (:120)
+        _pp_ladder(eng, eris, t1, tau1, t2new, group=group)               # (:121-125)
+        Lvv2 = E("kc,ka->ac", f["fov"], t1, alpha=-1.0)                   # (:126-127)
+        eng.add(Lvv2, f["fvv"])
+        eng.add(Lvv2, f["fvv_diag"], -1.0)
+        _sym_add(eng, t2new, E("ac,ijcb->ijab", Lvv2, t2), 1.0)           # (:128-129)
+        Loo2 = E("kc,ic->ki", f["fov"], t1)                               # (:130-131)
+        eng.add(Loo2, f["foo"])
+        eng.add(Loo2, f["foo_diag"], -1.0)
+        _sym_add(eng, t2new, E("ki,kjab->ijab", Loo2, t2), -1.0)          # (:132-133)
+    else:
+        E("klij,klab->ijab", im["Woooo"], tau, out=t2new, beta=1.0)          # hole-hole ladder (:137)
+        _pp_ladder(eng, eris, t1, tau, t2new, group=group)                    # particle-particle ladder (:138)
+        _sym_add(eng, t2new, E("ac,ijcb->ijab", im["Lvv"], t2), 1.0)          # (:139-140)
+        _sym_add(eng, t2new, E("ki,kjab->ijab", im["Loo"], t2), -1.0)         # (:141-142)
+        tmp = E("akic,kjcb->ijab", im["Wvoov"], t2, alpha=2.0)                # ring (:143-145)
+        E("akci,kjcb->ijab", im["Wvovo"], t2, alpha=-1.0, out=tmp, beta=1.0)
+        _sym_add(eng, t2new, tmp, 1.0)
+        _sym_add(eng, t2new, E("akic,kjbc->ijab", im["Wvoov"], t2), -1.0)     # exchange (:146-149)
+        _sym_add(eng, t2new, E("bkci,kjac->ijab", im["Wvovo"], t2), -1.0)
     tmp2 = eng.transpose(ovvv, (1, 3, 0, 2))                              # (:151-154)
     E("kibc,ka->abic", oovv, t1, alpha=-1.0, out=tmp2, beta=1.0)
     _sym_add(eng, t2new, E("abic,jc->ijab", tmp2, t1), 1.0)
@@ -303,3 +337,175 @@ def init_amps(cc, eris):
     t2 = eng.div_denominators(eng.transpose(eris.ovov, (0, 2, 1, 3)))
     emp2 = 2.0 * eng.dot(t2, eng.transpose(eris.ovov, (0, 2, 1, 3))) - eng.dot(t2, eng.transpose(eris.ovov, (0, 2, 3, 1)))
     return emp2, t1, t2
+
+
+# --------------------------------------------------------------------------------------------------------------
+# driver loop: pyscf/cc/ccsd.py:42-150 (``kernel``) as the fork runs it for ``RMPCCSD.ccsd`` (rmpccsd_slow.py:223-258)
+# --------------------------------------------------------------------------------------------------------------
+def ccsd_kernel(mycc, eris, t1=None, t2=None, max_cycle=50, tol=1e-7, tolnormt=1e-5, act_hole=(), act_particle=(),
+                idx_s=(), idx_d=(), log=None):
+    """The amplitude iteration with every vector resident on the device (``ccsd.kernel``, ccsd.py:42-150, the
+    ``act_particle is not None and not oo_mp2 and not pert_triples`` path):
+
+        eccsd = energy(t1, t2);  each cycle:  t1new, t2new = update_amps(...)
+        normt = |vec(t1new, t2new) - vec(t1, t2)|                    (:99-101)
+        t1, t2 = run_diis(t1new, t2new, istep, normt, eccsd - eold, adiis)   (:121, ccsd.py:1269-1276)
+        eold, eccsd = eccsd, energy(t1, t2);  stop when |dE| < tol and normt < tolnormt   (:130-137)
+
+    ``iterative_damping`` < 1 mixes the old amplitudes in as :107-119. Returns (converged, e_corr, t1, t2) with
+    device tensors. Only scalars (energies, norms, DIIS dots) cross to the host."""
+    from .diis import VectorDIIS
+    eng = eris.eng
+    o, v = eris.nocc, eris.nvir
+    if t1 is None or t2 is None:
+        guess = mycc.init_amps(eris) if callable(getattr(mycc, "init_amps", None)) else init_amps(mycc, eris)
+        g1, g2 = guess[1:]                                      # get_init_guess = init_amps()[1:] (ccsd.py)
+        t1 = g1 if t1 is None else t1
+        t2 = g2 if t2 is None else t2
+    if not isinstance(t1, DTensor):
+        t1 = eng.tensor(t1)
+    if not isinstance(t2, DTensor):
+        t2 = eng.tensor(t2)
+    eold = 0.0
+    eccsd = energy(mycc, t1, t2, eris)
+    diis = getattr(mycc, "diis", True)
+    adiis = None
+    if isinstance(diis, VectorDIIS):
+        adiis = diis
+    elif diis:
+        adiis = VectorDIIS(eng.be, space=getattr(mycc, "diis_space", 6))
+    damping = float(getattr(mycc, "iterative_damping", 1.0))
+    start_cycle = getattr(mycc, "diis_start_cycle", 0)
+    start_de = getattr(mycc, "diis_start_energy_diff", 1e9)
+    n = o * v + (o * v) * (o * v + 1) // 2
+    converged = False
+    mycc.cycles = 0
+    history = []
+    vec_old = eng.amplitudes_to_vector(t1, t2)
+    for istep in range(max_cycle):
+        t1new, t2new = update_amps(mycc, t1, t2, eris, act_hole, act_particle, idx_s, idx_d)
+        vec_new = eng.amplitudes_to_vector(t1new, t2new)
+        diff = DTensor(eng.be.copy(vec_new), (n,))
+        eng.add(diff, DTensor(vec_old, (n,)), -1.0)
+        normt = float(np.sqrt(eng.dot(diff, diff)))
+        del diff
+        if damping < 1.0:                                        # (:107-119)
+            mixed = eng.scale(t1new, damping)
+            eng.add(mixed, t1, 1.0 - damping)
+            t1new = mixed
+            mixed = eng.scale(t2new, damping)
+            eng.add(mixed, t2, 1.0 - damping)
+            t2new = mixed
+            vec_new = eng.amplitudes_to_vector(t1new, t2new)
+        t1, t2 = t1new, t2new
+        if adiis is not None and istep >= start_cycle and abs(eccsd - eold) < start_de:   # run_diis (ccsd.py:1269-1276)
+            vec_new = adiis.update(vec_new, n)
+            t1, t2 = eng.vector_to_amplitudes(vec_new, o, v)
+        vec_old = vec_new
+        eold, eccsd = eccsd, energy(mycc, t1, t2, eris)
+        mycc.cycles = istep + 1
+        history.append((istep + 1, eccsd, eccsd - eold, normt))
+        if log is not None:
+            log(f"cycle = {istep + 1}  E_corr(RMPCCSD) = {eccsd:.15g}  dE = {eccsd - eold:.9g}  norm(t1,t2) = {normt:.6g}")
+        if abs(eccsd - eold) < tol and normt < tolnormt:
+            converged = True
+            break
+    mycc.history = history
+    return converged, eccsd, t1, t2
+
+
+class RMPCCSD:
+    """Device counterpart of ``pyscf.cc.rmpccsd_slow.RMPCCSD`` (:197-271): the high-level solver object whose
+    ``kernel(act_hole, act_particle, idx_s, idx_d, ...)`` runs MBPT2, CC2 or CCSD with the active-space overwrite.
+    Built on a low-level solver (``MPCC_LL``, whose DF tensors provide the integrals) instead of ``ccsd.CCSD``'s
+    AO integrals; option names and defaults are ``ccsd.CCSD``'s (ccsd.py:970-984)."""
+
+    max_cycle = 50
+    conv_tol = 1e-7
+    conv_tol_normt = 1e-5
+    iterative_damping = 1.0
+    diis = True
+    diis_space = 6
+    diis_start_cycle = 0
+    diis_start_energy_diff = 1e9
+
+    def __init__(self, lowlevel=None, eris=None, fock=None, group=None, verbose=False, stdout=None):
+        if eris is None:
+            if lowlevel is None:
+                raise ValueError("RMPCCSD needs a low-level solver (MPCC_LL) or ready-made DFERIs")
+            eris = lowlevel.high_level_eris(fock=fock)
+        self.lowlevel = lowlevel
+        self.eris = eris
+        self.nocc, self.nvir = eris.nocc, eris.nvir
+        self.nmo = self.nocc + self.nvir
+        self.group = group
+        self.cc2 = False
+        self.max_space = 20                       # (:201) kept for attribute parity; EOM is not part of this path
+        self.verbose = verbose
+        self.stdout = stdout
+        self.converged = False
+        self.e_corr = None
+        self.emp2 = None
+        self.t1 = self.t2 = None
+        self.cycles = 0
+
+    def _log(self, msg):
+        if self.verbose:
+            import sys
+            print(msg, file=self.stdout or sys.stdout)
+
+    def ao2mo(self, mo_coeff=None):
+        return self.eris
+
+    def init_amps(self, eris=None):
+        self.emp2, t1, t2 = init_amps(self, eris or self.eris)
+        self._log(f"Init t2, MP2 energy = {self.emp2:.15g}")
+        return self.emp2, t1, t2
+
+    def get_init_guess(self, eris=None):
+        return self.init_amps(eris)[1:]
+
+    def energy(self, t1=None, t2=None, eris=None):
+        return energy(self, self.t1 if t1 is None else t1, self.t2 if t2 is None else t2, eris or self.eris)
+
+    def update_amps(self, t1, t2, eris, act_hole=(), act_particle=(), idx_s=(), idx_d=()):
+        return update_amps(self, t1, t2, eris, act_hole, act_particle, idx_s, idx_d)
+
+    def amplitudes_to_vector(self, t1, t2, out=None):
+        eng = self.eris.eng
+        t1 = t1 if isinstance(t1, DTensor) else eng.tensor(t1)
+        t2 = t2 if isinstance(t2, DTensor) else eng.tensor(t2)
+        return eng.amplitudes_to_vector(t1, t2)
+
+    def vector_to_amplitudes(self, vec, nmo=None, nocc=None):
+        nocc = self.nocc if nocc is None else nocc
+        nmo = self.nmo if nmo is None else nmo
+        return self.eris.eng.vector_to_amplitudes(vec, nocc, nmo - nocc)
+
+    def vector_size(self, nmo=None, nocc=None):
+        nocc = self.nocc if nocc is None else nocc
+        nov = nocc * ((self.nmo if nmo is None else nmo) - nocc)
+        return nov + nov * (nov + 1) // 2
+
+    def kernel(self, act_hole, act_particle, idx_s, idx_d, t1=None, t2=None, eris=None, mbpt2=False, cc2=False):
+        return self.ccsd(act_hole, act_particle, idx_s, idx_d, t1, t2, eris, mbpt2, cc2)
+
+    def ccsd(self, act_hole, act_particle, idx_s, idx_d, t1=None, t2=None, eris=None, mbpt2=False, cc2=False):
+        """(:223-258) MBPT2 (one shot), CC2 or CCSD ground state with the amplitude classes ``idx_s`` / ``idx_d``
+        frozen at their input values. Returns (e_corr, t1, t2); amplitudes stay on the device (``eng.numpy``)."""
+        if mbpt2 and cc2:
+            raise RuntimeError("MBPT2 and CC2 are mutually exclusive approximations to the CCSD ground state.")
+        if eris is None:
+            eris = self.eris
+        self.eris = eris
+        if mbpt2:
+            self.e_corr, self.t1, self.t2 = self.init_amps(eris)
+            return self.e_corr, self.t1, self.t2
+        self.cc2 = bool(cc2)
+        cctyp = "CC2" if cc2 else "CCSD"
+        self.converged, self.e_corr, self.t1, self.t2 = ccsd_kernel(
+            self, eris, t1, t2, max_cycle=self.max_cycle, tol=self.conv_tol, tolnormt=self.conv_tol_normt,
+            act_hole=act_hole, act_particle=act_particle, idx_s=idx_s, idx_d=idx_d, log=self._log)
+        self._log(f"{cctyp} converged" if self.converged else f"{cctyp} not converged")
+        self._log(f"E_corr = {self.e_corr:.16g}")
+        return self.e_corr, self.t1, self.t2

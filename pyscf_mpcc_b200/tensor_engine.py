@@ -99,6 +99,43 @@ class CudaBackend:
         self.ctx.call("mpccb_dot", x.data_ptr(), y.data_ptr(), int(n), out.data_ptr())
         return float(self.download(out)[0])
 
+    # -- vector layouts and DIIS of the CCSD-type stage (ccsd.py:719-735, 1269-1276) ------------------
+    def pack_tril(self, mat, n, out):
+        self.ctx.call("mpccb_pack_tril", mat.data_ptr(), int(n), out.data_ptr())
+
+    def unpack_tril(self, packed, n, out):
+        self.ctx.call("mpccb_unpack_tril", packed.data_ptr(), int(n), out.data_ptr())
+
+    @staticmethod
+    def _ptr_list(bufs):
+        arr = (ctypes.c_void_p * 6)()
+        for k, b in enumerate(bufs):
+            arr[k] = b.data_ptr() if b is not None else None
+        return arr
+
+    def vec_diis_push(self, x, n, xprev, prev_x, prev_c, x_slot, e_slot, e_list, nd, slot, first):
+        """One ``push_vec`` + B-matrix row (diis.py:148-185,221-231) on device vectors; returns the nd dots."""
+        dots = self.empty(8)
+        coeff = (ctypes.c_double * 6)(*([float(c) for c in prev_c] + [0.0] * (6 - len(prev_c))))
+        self.ctx.call("mpccb_vec_diis_push", x.data_ptr(), int(n), xprev.data_ptr() if xprev is not None else None,
+                      self._ptr_list(prev_x), coeff, len(prev_x), x_slot.data_ptr(),
+                      e_slot.data_ptr() if e_slot is not None else None, self._ptr_list(e_list), int(nd), int(slot),
+                      int(bool(first)), dots.data_ptr())
+        return None if first else self.download(dots)[:nd]
+
+    def combine(self, xs, coeffs, out, n):
+        coeff = (ctypes.c_double * 6)(*([float(c) for c in coeffs] + [0.0] * (6 - len(coeffs))))
+        self.ctx.call("mpccb_diis_combine", self._ptr_list(xs), coeff, len(xs), out.data_ptr(), int(n))
+
+    def all_reduce(self, buf, group):
+        """Sum over the ranks of ``group`` (NCCL); used by the a-slab sharded particle-particle ladder."""
+        self.torch.cuda.current_stream(self.device).synchronize()
+        self.torch.distributed.all_reduce(buf, group=group)
+
+    def rank_and_size(self, group):
+        d = self.torch.distributed
+        return d.get_rank(group), d.get_world_size(group)
+
 
 def _prod(xs):
     n = 1
@@ -228,6 +265,25 @@ class Engine:
         if mask:
             self.be.class_overwrite(tnew.buf, told.buf, tnew.ndim, act_h, act_p, mask)
         return tnew
+
+    # -- amplitude <-> vector (ccsd.py:719-735) ------------------------------------------------------
+    def amplitudes_to_vector(self, t1, t2):
+        """[t1 | pack_tril(t2.transpose(0,2,1,3).reshape(nov, nov))] as a flat device buffer."""
+        o, v = t1.shape
+        nov = o * v
+        vec = self.be.empty(nov + nov * (nov + 1) // 2)
+        self.be.permute_axpby(t1.buf, vec, t1.shape, (0, 1), 1.0, 0.0)
+        m = self.transpose(t2, (0, 2, 1, 3))
+        self.be.pack_tril(m.buf, nov, vec[nov:])
+        return vec
+
+    def vector_to_amplitudes(self, vec, o, v):
+        """t1 (o,v) copy; t2 = unpack_tril(SYMMETRIC).reshape(o,v,o,v).transpose(0,2,1,3), contiguous."""
+        nov = o * v
+        t1 = DTensor(self.be.copy(vec[:nov]), (o, v))
+        full = DTensor(self.be.empty(nov * nov), (o, v, o, v))
+        self.be.unpack_tril(vec[nov:], nov, full.buf)
+        return t1, self.transpose(full, (0, 2, 1, 3))
 
 
 def make_cuda_engine(nocc, nvir, naux, device=None):

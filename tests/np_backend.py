@@ -66,3 +66,34 @@ class NumpyBackend:
 
     def dot(self, x, y, n):
         return float(np.dot(x[:n], y[:n]))
+
+    def pack_tril(self, mat, n, out):
+        r, c = np.tril_indices(n)
+        out[:r.size] = mat[:n * n].reshape(n, n)[r, c]
+
+    def unpack_tril(self, packed, n, out):
+        r, c = np.tril_indices(n)
+        full = np.zeros((n, n))
+        full[c, r] = packed[:r.size]
+        full[r, c] = packed[:r.size]
+        out[:n * n] = full.reshape(-1)
+
+    def vec_diis_push(self, x, n, xprev, prev_x, prev_c, x_slot, e_slot, e_list, nd, slot, first):
+        if first:
+            x_slot[:n] = x[:n]
+            return None
+        if prev_x:
+            prev = np.zeros(n)
+            for xk, ck in zip(prev_x, prev_c):
+                prev += xk[:n] * ck
+        else:
+            prev = np.array(xprev[:n])
+        x_slot[:n] = x[:n]
+        e_slot[:n] = x[:n] - prev
+        return np.array([float(np.dot(e_slot[:n], e_slot[:n] if k == slot else e_list[k][:n])) for k in range(nd)])
+
+    def combine(self, xs, coeffs, out, n):
+        acc = np.zeros(n)
+        for xk, ck in zip(xs, coeffs):
+            acc += xk[:n] * ck
+        out[:n] = acc

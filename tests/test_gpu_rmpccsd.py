@@ -21,7 +21,7 @@ def _device_problem(p):
     return ll, ll.high_level_eris(fock=p["fock"])
 
 
-@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(GOLDEN, "rmpccsd_*.npz"))), ids=os.path.basename)
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(GOLDEN, "rmpccsd_[0-9]*.npz"))), ids=os.path.basename)
 def test_update_amps_and_energy_against_reference_fixture(path):
     from pyscf_mpcc_b200 import rmpccsd
     g = np.load(path)
@@ -96,3 +96,58 @@ def test_gemm_nt_dispatch(mnk):
     ref = a @ b.T
     assert torch.isfinite(c).all()
     assert (c - ref).abs().max().item() <= 1e-12 * max(1.0, ref.abs().max().item()) * k ** 0.5
+
+
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(GOLDEN, "rmpccsd_cc2_*.npz"))), ids=os.path.basename)
+def test_cc2_update_amps_against_reference_fixture(path):
+    """cc.cc2 = True (rmpccsd_slow.py:115-133) on the device against the reference's own output."""
+    from pyscf_mpcc_b200 import rmpccsd
+    g = np.load(path)
+    o, v, L = (int(x) for x in g["shape"])
+    p = make_problem(o, v, L, seed=int(g["seed"]))
+    ll, eris = _device_problem(p)
+    t1n, t2n = rmpccsd.update_amps(types.SimpleNamespace(cc2=True), p["t1"], p["t2"], eris, list(g["act_hole"]),
+                                   list(g["act_particle"]), list(g["idx_singles"]), list(g["idx_doubles"]))
+    scale = max(1.0, float(np.abs(g["t2new_samples"]).max()))
+    assert np.abs(t1n - g["t1new"]).max() <= 1e-10 * max(1.0, float(np.abs(g["t1new"]).max()))
+    assert np.abs(t2n.reshape(-1)[::int(g["stride"])] - g["t2new_samples"]).max() <= 1e-10 * scale
+    assert abs(np.linalg.norm(t2n) - float(g["t2new_norm"])) <= 1e-10 * float(g["t2new_norm"])
+
+
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(GOLDEN, "rmpccsd_kernel_*.npz"))), ids=os.path.basename)
+def test_driver_loop_on_device_against_fixture(path):
+    """RMPCCSD.kernel on the GPU (device-resident amplitudes, VectorDIIS on packed device vectors) against the loop of
+    ccsd.py:42-150 run around the reference's update_amps / energy / lib.diis.DIIS: identical cycle counts,
+    |E_corr| <= 1e-8, amplitudes to 1e-10."""
+    from pyscf_mpcc_b200 import rmpccsd
+    g = np.load(path)
+    o, v, L = (int(x) for x in g["shape"])
+    p = make_problem(o, v, L, seed=int(g["seed"]))
+    ll, eris = _device_problem(p)
+    cc = rmpccsd.RMPCCSD(ll, fock=p["fock"])
+    e, t1, t2 = cc.kernel(list(g["act_hole"]), list(g["act_particle"]), list(g["idx_singles"]), list(g["idx_doubles"]),
+                          cc2=bool(g["cc2"]))
+    hist = np.array(cc.history)
+    assert cc.converged == bool(g["converged"]) and cc.cycles == len(g["history"])
+    assert np.abs(hist[:, 1] - g["history"][:, 1]).max() <= 1e-8
+    np.testing.assert_allclose(hist[:, 3], g["history"][:, 3], rtol=1e-5, atol=1e-10)
+    assert abs(e - float(g["e_corr"])) <= 1e-8 and abs(cc.emp2 - float(g["emp2"])) <= 1e-10
+    eng = eris.eng
+    assert np.abs(eng.numpy(t1) - g["t1"]).max() <= 1e-10
+    t2h = eng.numpy(t2)
+    assert np.abs(t2h.reshape(-1)[::int(g["stride"])] - g["t2_samples"]).max() <= 1e-10
+    assert abs(np.linalg.norm(t2h) - float(g["t2_norm"])) <= 1e-9
+
+
+def test_vector_layouts_on_device():
+    """amplitudes_to_vector / vector_to_amplitudes of the CCSD-type stage (ccsd.py:719-735) against the oracle."""
+    from oracle import cc_oracle
+    p = make_problem(5, 9, 12, seed=3)
+    ll, eris = _device_problem(p)
+    eng = eris.eng
+    vec = eng.amplitudes_to_vector(eng.tensor(p["t1"]), eng.tensor(p["t2"]))
+    want = cc_oracle.amplitudes_to_vector(p["t1"], p["t2"])
+    assert np.array_equal(eng.be.download(vec), want)
+    t1, t2 = eng.vector_to_amplitudes(vec, 5, 9)
+    t1o, t2o = cc_oracle.vector_to_amplitudes(want, 14, 5)
+    assert np.array_equal(eng.numpy(t1), t1o) and np.array_equal(eng.numpy(t2), t2o)
