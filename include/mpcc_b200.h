@@ -171,6 +171,17 @@ int mpccb_set_option(mpccb_ctx* ctx, const char* name, long long value);
 /* standalone C[m,n] = sum_k A[m,k] B[n,k] through the generic DMMA kernel (row-major, test hook) */
 int mpccb_gemm_nt(mpccb_ctx* ctx, const double* A_dev, const double* B_dev, double* C_dev,
                   int M, int N, int K);
+/* y = alpha * op(A) x + beta * y: trans 0: A [rows][K]; trans 1: A [K][rows]. The einsums of rmpccsd_slow.py /
+ * rintermediates.py in which one operand is summed away entirely (e.g. 'kdac,kd->ac', rintermediates.py:77) */
+int mpccb_gemv(mpccb_ctx* ctx, const double* A_dev, const double* x_dev, double* y_dev, long long rows, long long K,
+               int trans, double alpha, double beta);
+/* the same product stored through a two-level index map with axpby:
+ *   C[(m/mdiv)*m_hi + (m%mdiv)*m_lo + (n/ndiv)*n_hi + (n%ndiv)*n_lo] = alpha * sum_k A[m][k] B[n][k] + beta * C[..]
+ * — lib.einsum's final transpose (pyscf/lib/numpy_helper.py:246-252) and the "+=" of the residual terms
+ * (rmpccsd_slow.py:93-158) folded into the GEMM's store epilogue */
+int mpccb_gemm_nt_mapped(mpccb_ctx* ctx, const double* A_dev, const double* B_dev, double* C_dev, int M, int N, int K,
+                         int mdiv, long long m_hi, long long m_lo, int ndiv, long long n_hi, long long n_lo,
+                         double alpha, double beta);
 
 /* ---- tensor engine for the CCSD-type residual terms: the reference evaluates
  *      pyscf/cc/rmpccsd_slow.py:73-180 and pyscf/cc/rintermediates.py:29-130 as a list of lib.einsum calls

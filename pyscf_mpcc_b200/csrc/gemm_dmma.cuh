@@ -45,6 +45,9 @@ struct Output {
   // kept block returns before its K loop. nullptr: store everything.
   const unsigned char* keep;
   int keep_ld;
+  // base[off] = alpha * acc + beta * base[off]  (beta == 0: the old value is not read). The tensor engine's
+  // "out = alpha * einsum + beta * out" lands in the permuted result without a separate pass.
+  double alpha, beta;
 };
 
 struct GemmDims {
@@ -249,7 +252,7 @@ gemm_store_kernel(Operand A, Operand B, Output C, GemmDims d) {
         if (C.keep && !(C.keep[(i64)(m / C.mdiv) * C.keep_ld + n / C.ndiv] & 1)) continue;
         const i64 off = moff + (i64)(n / C.ndiv) * C.n_hi + (i64)(n % C.ndiv) * C.n_lo;
         const double v = acc[i][j][c];
-        C.base[off] = v;
+        C.base[off] = (C.alpha == 1.0 && C.beta == 0.0) ? v : fma(C.alpha, v, C.beta != 0.0 ? C.beta * C.base[off] : 0.0);
         if (C.base2) C.base2[off] = v + C.aux[off];
       }
     }

@@ -41,6 +41,8 @@ struct TmaCfg {
   static constexpr int STAGING_BYTES = 8 * TMA_TM * (TN + 1);      // fused-t2 epilogue staging (aliases the ring)
   static constexpr int FLAG_BYTES = TMA_TM * TN;                   // one byte per (a,b) block of the tile (nocc = 1)
   static constexpr int AREA_EPI1 = STAGING_BYTES + FLAG_BYTES > RING_BYTES ? STAGING_BYTES + FLAG_BYTES : RING_BYTES;
+  // plain / index-mapped store epilogues stage the tile through shared memory too (coalesced global stores)
+  static constexpr int AREA_STORE = STAGING_BYTES > RING_BYTES ? STAGING_BYTES : RING_BYTES;
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -143,7 +145,8 @@ struct TmaGemmParams {
   int ksplit, nk_split, tiles_total;
   i64 split_stride;
   // EPI 2: store through a two-level index map with an optional block mask (gemm_dmma.cuh, Output): the unfused
-  // eris GEMM scatters e[(a,i),(b,j)] into T[a][b][i][j] and skips the blocks that arrive as somebody's mirror
+  // eris GEMM scatters e[(a,i),(b,j)] into T[a][b][i][j] and skips the blocks that arrive as somebody's mirror;
+  // the tensor engine's contractions store straight into the permuted result (out.alpha / out.beta: axpby)
   Output out;
 };
 
@@ -158,7 +161,7 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
   typedef TmaCfg<WN> Cfg;
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   double* ring = reinterpret_cast<double*>(smem_raw);
-  constexpr size_t STAGE_AREA = (EPI == 1) ? (size_t)Cfg::AREA_EPI1 : (size_t)Cfg::RING_BYTES;
+  constexpr size_t STAGE_AREA = (EPI == 1) ? (size_t)Cfg::AREA_EPI1 : (size_t)Cfg::AREA_STORE;
   uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + STAGE_AREA);
   uint64_t* empty = full + TMA_STAGES;
 
@@ -258,42 +261,60 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
     if (lane == 0) mbar_arrive(&empty[s]);
   }
 
-  if (EPI == 0) {
-    // C[m][n] row-major; fragment (row g, cols 2*tig, 2*tig+1) sits at tile (rho(g), rho(2*tig + c))
+  if (EPI == 0 || EPI == 2) {
+    // Stage the accumulators through shared memory (the ring is drained: every warp waited on every full barrier,
+    // the block barrier orders the last reads before the overwrite), then store with lanes along the unit-stride
+    // index of the target: 256-byte runs instead of single doubles at rho-permuted columns.
+    __syncthreads();
+    constexpr int PITCH = Cfg::TN + 1;            // odd: row- and column-wise reads are both conflict-free
+    double* S = reinterpret_cast<double*>(smem_raw);
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int ml = wm * 32 + i * 8 + rho(g);
-      const int m = m0 + ml;
-      if (ml >= p.tm_eff || m >= p.M) continue;
+    for (int i = 0; i < 4; ++i)
 #pragma unroll
       for (int j = 0; j < 4; ++j)
 #pragma unroll
-        for (int c = 0; c < 2; ++c) {
-          const int nl = wn * 32 + j * 8 + rho(2 * tig + c);
-          const int n = n0 + nl;
-          if (nl < p.tn_eff && n < p.N) p.C[split * p.split_stride + (i64)m * p.ldc + n] = acc[i][j][c];
+        for (int c = 0; c < 2; ++c)
+          S[(wm * 32 + i * 8 + rho(g)) * PITCH + wn * 32 + j * 8 + rho(2 * tig + c)] = acc[i][j][c];
+    __syncthreads();
+    constexpr int nwarps = Cfg::WARPS;
+    const int rows = min(p.tm_eff, p.M - m0), cols = min(p.tn_eff, p.N - n0);
+    if (EPI == 0) {
+      double* Cb = p.C + split * p.split_stride;
+      for (int r = warp; r < rows; r += nwarps) {
+        double* crow = Cb + (i64)(m0 + r) * p.ldc + n0;
+        for (int cl = lane; cl < cols; cl += 32) crow[cl] = S[r * PITCH + cl];
+      }
+    } else {
+      const Output& C = p.out;
+      const bool axpby = (C.alpha != 1.0) || (C.beta != 0.0);
+      auto put = [&](i64 off, double val) {
+        C.base[off] = axpby ? fma(C.alpha, val, C.beta != 0.0 ? C.beta * C.base[off] : 0.0) : val;
+      };
+      if (C.n_lo == 1 || C.m_lo != 1) {           // lanes along n
+        for (int r = warp; r < rows; r += nwarps) {
+          const int m = m0 + r;
+          const int mq = m / C.mdiv;
+          const i64 moff = (i64)mq * C.m_hi + (i64)(m - mq * C.mdiv) * C.m_lo;
+          for (int cl = lane; cl < cols; cl += 32) {
+            const int n = n0 + cl;
+            const int nq = n / C.ndiv;
+            if (C.keep && !(C.keep[(i64)mq * C.keep_ld + nq] & 1)) continue;
+            put(moff + (i64)nq * C.n_hi + (i64)(n - nq * C.ndiv) * C.n_lo, S[r * PITCH + cl]);
+          }
         }
-    }
-  } else if (EPI == 2) {
-    const Output& C = p.out;
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int ml = wm * 32 + i * 8 + rho(g);
-      const int m = m0 + ml;
-      if (ml >= p.tm_eff || m >= p.M) continue;
-      const int mq = m / C.mdiv;
-      const i64 moff = (i64)mq * C.m_hi + (i64)(m - mq * C.mdiv) * C.m_lo;
-#pragma unroll
-      for (int j = 0; j < 4; ++j)
-#pragma unroll
-        for (int c = 0; c < 2; ++c) {
-          const int nl = wn * 32 + j * 8 + rho(2 * tig + c);
-          const int n = n0 + nl;
-          if (nl >= p.tn_eff || n >= p.N) continue;
+      } else {                                    // the target is contiguous along m: lanes along m
+        for (int cl = warp; cl < cols; cl += nwarps) {
+          const int n = n0 + cl;
           const int nq = n / C.ndiv;
-          if (C.keep && !(C.keep[(i64)mq * C.keep_ld + nq] & 1)) continue;
-          C.base[moff + (i64)nq * C.n_hi + (i64)(n - nq * C.ndiv) * C.n_lo] = acc[i][j][c];
+          const i64 noff = (i64)nq * C.n_hi + (i64)(n - nq * C.ndiv) * C.n_lo;
+          for (int r = lane; r < rows; r += 32) {
+            const int m = m0 + r;
+            const int mq = m / C.mdiv;
+            if (C.keep && !(C.keep[(i64)mq * C.keep_ld + nq] & 1)) continue;
+            put(noff + (i64)mq * C.m_hi + (i64)(m - mq * C.mdiv) * C.m_lo, S[r * PITCH + cl]);
+          }
         }
+      }
     }
   } else {
     // all consumers have drained the ring (every full barrier was waited on) before the staging

@@ -108,6 +108,26 @@ k_gemv_rows(const double* __restrict__ M, const double* __restrict__ x, double* 
   if (lane == 0) y[r] = s;
 }
 
+// partial[s][n] = sum_{k in slice s} A[k*N + n] * x[k]: y = A^T x for a matrix stored [K][N] (lanes along n:
+// coalesced); grid (ceil(N/256), slices), reduced afterwards in fixed order (k_reduce_splits)
+__global__ void __launch_bounds__(256)
+k_gemv_cols_partial(const double* __restrict__ A, const double* __restrict__ x, double* __restrict__ partial,
+                    i64 K, i64 N, i64 kchunk) {
+  const i64 n = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  const i64 k0 = (i64)blockIdx.y * kchunk, k1 = min(K, k0 + kchunk);
+  double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+  i64 k = k0;
+  for (; k + 4 <= k1; k += 4) {
+    s0 = fma(A[k * N + n], x[k], s0);
+    s1 = fma(A[(k + 1) * N + n], x[k + 1], s1);
+    s2 = fma(A[(k + 2) * N + n], x[k + 2], s2);
+    s3 = fma(A[(k + 3) * N + n], x[k + 3], s3);
+  }
+  for (; k < k1; ++k) s0 = fma(A[k * N + n], x[k], s0);
+  partial[(i64)blockIdx.y * N + n] = (s0 + s1) + (s2 + s3);
+}
+
 // dst[i] = beta*dst[i] + alpha * sum_s P[s*stride + i]   (split-K / tile partial reduction, fixed order)
 __global__ void __launch_bounds__(256)
 k_reduce_splits(double* __restrict__ dst, const double* __restrict__ P, int nsplit, i64 n, i64 stride,

@@ -170,6 +170,7 @@ Output flat_output(double* base, i64 m_stride, i64 n_stride) {
   c.n_hi = 0; c.n_lo = n_stride; c.ndiv = BIG;
   c.split_stride = 0;
   c.keep = nullptr; c.keep_ld = 0;
+  c.alpha = 1.0; c.beta = 0.0;
   return c;
 }
 
@@ -374,6 +375,7 @@ i64 carve_workspace(mpccb_ctx* c, unsigned char* base) {
   mx(splitk_scratch((int)v, (int)o, (int)(na * L), 128, 64));  // G2
   mx(splitk_scratch((int)o, (int)o, (int)(na * L), 128, 64));  // S8
   mx((DIIS_ROWS_GRID + 1) * 7);                                // DIIS dot partials (row-owned vector)
+  mx((i64)2 * NSM * 128 * 128);                                // split-K partials of mpccb_gemm_nt (tensor engine): <= 2 waves of tiles
   mx((DIIS_COLS_GRID + 1) * 7);                                //   "   (column-owned vector)
   c->P_count = p;
   c->P = w.take(p);
@@ -754,7 +756,7 @@ template <int EPI, int WN>
 int launch_tma(mpccb_ctx* c, const char* what, const CUtensorMap& mA, const CUtensorMap& mB,
                const TmaGemmParams& p, const T2Params& t2p) {
   typedef TmaCfg<WN> Cfg;
-  const size_t smem = (EPI == 1 ? (size_t)Cfg::AREA_EPI1 : (size_t)Cfg::RING_BYTES) + TMA_BAR_BYTES;
+  const size_t smem = (EPI == 1 ? (size_t)Cfg::AREA_EPI1 : (size_t)Cfg::AREA_STORE) + TMA_BAR_BYTES;
   CUDA_OK(c, ensure_smem_attr(c, reinterpret_cast<const void*>(&gemm_tma_kernel<EPI, WN>), smem, true));
   SymInfo sym;
   memset(&sym, 0, sizeof(sym));
@@ -1345,7 +1347,7 @@ extern "C" int mpccb_gemm_nt(mpccb_ctx* c, const double* A_dev, const double* B_
   CUDA_OK(c, enter_device(c));
   if (M <= 0 || N <= 0 || K <= 0) return fail(c, "gemm_nt: empty product");
   const bool aligned = (K % 2 == 0) && ((reinterpret_cast<uintptr_t>(A_dev) | reinterpret_cast<uintptr_t>(B_dev)) & 15) == 0;
-  if (c->use_tma && aligned && K >= 64 && (double)M * N * K >= 5e8 && M >= 64 && N >= 64) {
+  if (c->use_tma && aligned && K >= 16 && (double)M * N * K >= 5e8 && M >= 64 && N >= 64) {
     constexpr int TN = TmaCfg<4>::TN;
     CUtensorMap mA, mB;
     if (make_map_2d(c, &mA, A_dev, K, M, K, TMA_TM)) return 1;
@@ -1359,8 +1361,29 @@ extern "C" int mpccb_gemm_nt(mpccb_ctx* c, const double* A_dev, const double* B_
     p.a_mode = 0;
     p.a_bytes = TMA_TM * TMA_TK * 8; p.b_bytes = TN * TMA_TK * 8;
     p.C = C_dev; p.ldc = N; p.ksplit = 1;
+    // fewer tiles than two waves and a long contraction index: K slices (fixed-order reduction afterwards), the
+    // factor that minimises ceil(T * s / 148) / s
+    const i64 T = (i64)p.tiles_m * p.tiles_n;
+    int best_s = 1;
+    if (c->P && T < 2 * NSM) {
+      double best = (double)cdiv(T, NSM);
+      const i64 cap = c->P_count / ((i64)M * N);
+      for (int sp = 2; sp <= 64; ++sp) {
+        if (p.nk / sp < 32 || sp > cap) break;
+        const double w = (double)cdiv(T * sp, NSM) / sp + 0.002 * sp;
+        if (w < best * 0.97) { best = w; best_s = sp; }
+      }
+    }
     T2Params t;
     memset(&t, 0, sizeof(t));
+    if (best_s > 1) {
+      p.nk_split = cdiv(p.nk, best_s);
+      p.ksplit = cdiv(p.nk, p.nk_split);
+      p.C = c->P; p.split_stride = (i64)M * N;
+      p.tiles_total = (int)T * p.ksplit;
+      if (launch_tma<0, 4>(c, "gemm_tma_kernel<nt split-K>", mA, mB, p, t)) return 1;
+      return reduce_splits(c, C_dev, c->P, p.ksplit, (i64)M * N, (i64)M * N, 1.0, 0.0);
+    }
     return launch_tma<0, 4>(c, "gemm_tma_kernel<nt>", mA, mB, p, t);
   }
   Operand A = flat_operand(A_dev, M, K, 1);
@@ -1384,6 +1407,71 @@ extern "C" int mpccb_gemm_nt(mpccb_ctx* c, const double* A_dev, const double* B_
   }
   if (N <= 64) return launch_gemm<CfgN64KK>(c, "gemm_nt", A, B, C, M, N, K, 1, nullptr);
   return launch_gemm<CfgBigKK>(c, "gemm_nt", A, B, C, M, N, K, 1, nullptr);
+}
+
+// y = alpha * op(A) x + beta * y for the contractions in which one operand is summed away entirely ("kdac,kd->ac":
+// matrix-vector products, bound by one read of the matrix): trans = 0: A is [rows][K] (one warp per row),
+// trans = 1: A is [K][rows] (lanes along rows, K sliced over the grid, fixed-order reduction).
+extern "C" int mpccb_gemv(mpccb_ctx* c, const double* A_dev, const double* x_dev, double* y_dev, long long rows,
+                          long long K, int trans, double alpha, double beta) {
+  CUDA_OK(c, enter_device(c));
+  if (!c->ws) return fail(c, "bind the workspace first");
+  if (rows <= 0 || K <= 0 || rows > INT_MAX || K > INT_MAX) return fail(c, "gemv: bad sizes");
+  if (!trans) {
+    if (rows > c->P_count) return fail(c, "gemv: scratch too small");
+    k_gemv_rows<<<cdiv(rows, 8), 256, 0, c->stream>>>(A_dev, x_dev, c->P, (int)rows, (int)K, K);
+    LAUNCH_OK(c, "k_gemv_rows");
+    return reduce_splits(c, y_dev, c->P, 1, rows, rows, alpha, beta);
+  }
+  const int nbx = cdiv(rows, 256);
+  int slices = (int)std::min<i64>(std::max<i64>(1, (4 * NSM) / nbx), std::max<i64>(1, K / 64));
+  slices = (int)std::min<i64>(slices, c->P_count / rows);
+  if (slices < 1) return fail(c, "gemv: scratch too small");
+  const i64 kchunk = (K + slices - 1) / slices;
+  slices = (int)((K + kchunk - 1) / kchunk);
+  k_gemv_cols_partial<<<dim3(nbx, slices), 256, 0, c->stream>>>(A_dev, x_dev, c->P, K, rows, kchunk);
+  LAUNCH_OK(c, "k_gemv_cols_partial");
+  return reduce_splits(c, y_dev, c->P, slices, rows, rows, alpha, beta);
+}
+
+// C[map(m, n)] = alpha * sum_k A[m][k] B[n][k] + beta * C[map(m, n)] with the two-level output map
+//   map(m, n) = (m / mdiv) * m_hi + (m % mdiv) * m_lo + (n / ndiv) * n_hi + (n % ndiv) * n_lo
+// so that a contraction lands in its (permuted) result tensor without a separate permute / accumulate pass
+// (lib.einsum's transpose -> dot -> transpose, pyscf/lib/numpy_helper.py:101-252, minus the last transpose).
+// The map must be injective on [0,M) x [0,N) (the engine derives it from a permutation of the output indices).
+extern "C" int mpccb_gemm_nt_mapped(mpccb_ctx* c, const double* A_dev, const double* B_dev, double* C_dev,
+                                    int M, int N, int K, int mdiv, long long m_hi, long long m_lo,
+                                    int ndiv, long long n_hi, long long n_lo, double alpha, double beta) {
+  CUDA_OK(c, enter_device(c));
+  if (M <= 0 || N <= 0 || K <= 0 || mdiv <= 0 || ndiv <= 0) return fail(c, "gemm_nt_mapped: bad sizes");
+  Output C = flat_output(C_dev, 0, 0);
+  C.mdiv = mdiv; C.m_hi = m_hi; C.m_lo = m_lo;
+  C.ndiv = ndiv; C.n_hi = n_hi; C.n_lo = n_lo;
+  C.alpha = alpha; C.beta = beta;
+  const bool aligned = (K % 2 == 0) && ((reinterpret_cast<uintptr_t>(A_dev) | reinterpret_cast<uintptr_t>(B_dev)) & 15) == 0;
+  if (c->use_tma && aligned && K >= 16 && (double)M * N * K >= 5e8 && M >= 64 && N >= 64) {
+    constexpr int TN = TmaCfg<4>::TN;
+    CUtensorMap mA, mB;
+    if (make_map_2d(c, &mA, A_dev, K, M, K, TMA_TM)) return 1;
+    if (make_map_2d(c, &mB, B_dev, K, N, K, TN)) return 1;
+    TmaGemmParams p;
+    memset(&p, 0, sizeof(p));
+    p.M = M; p.N = N;
+    p.tm_eff = TMA_TM; p.tn_eff = TN;
+    p.tiles_m = cdiv(M, TMA_TM); p.tiles_n = cdiv(N, TN);
+    p.nk = cdiv(K, TMA_TK);
+    p.a_mode = 0;
+    p.a_bytes = TMA_TM * TMA_TK * 8; p.b_bytes = TN * TMA_TK * 8;
+    p.ksplit = 1;
+    p.out = C;
+    T2Params t;
+    memset(&t, 0, sizeof(t));
+    return launch_tma<2, 4>(c, "gemm_tma_kernel<mapped>", mA, mB, p, t);
+  }
+  Operand A = flat_operand(A_dev, M, K, 1);
+  Operand B = flat_operand(B_dev, N, K, 1);
+  if (N <= 64) return launch_gemm<CfgN64KK>(c, "gemm_nt_mapped", A, B, C, M, N, K, 1, nullptr);
+  return launch_gemm<CfgBigKK>(c, "gemm_nt_mapped", A, B, C, M, N, K, 1, nullptr);
 }
 
 // ===========================================================================

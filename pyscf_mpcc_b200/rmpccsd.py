@@ -114,35 +114,62 @@ def _rows(t, lo, hi):
 def _pp_ladder(eng, eris, t1, tau, t2new, slab_bytes=4 << 30, group=None):
     """t2new[i,j,a,b] += sum_cd W[a,b,c,d] tau[i,j,c,d]  (:138), W = cc_Wvvvv (rintermediates.py:92-99):
         W[a,b,c,d] = (ac|bd) - sum_k (kd|ac) t1[k,b] - sum_k (kc|bd) t1[k,a]
-    evaluated for slabs of the first virtual index a; (ac|bd) = sum_L Lvv[L,a,c] Lvv[L,b,d] is formed per
-    slab from the DF tensor, so no v^4 array is ever stored. The last term is folded into the DF tensor:
-        sum_k t1[k,a] (kc|bd) = sum_L (sum_k t1[k,a] Lov[L,k,c]) Lvv[L,b,d]."""
+    DF-direct, in slabs of the first virtual index a, so that no v^4 array is ever stored (the blocking idea of
+    ``pyscf/cc/dfccsd.py:54-117``). Both t1 terms fold into the DF tensor: with Lt[L,a,c] = sum_k t1[k,a] Lov[L,k,c]
+    and Leff = Lvv - Lt,
+        W[a,b,c,d] = sum_L Leff[L,a,c] Leff[L,b,d]  -  sum_L Lt[L,a,c] Lt[L,b,d],
+    and the second piece is of rank o^2:  sum_L Lt[L,a,c] Lt[L,b,d] = sum_kl t1[k,a] t1[l,b] (kc|ld), so its ladder
+    contribution is  sum_kl t1[k,a] t1[l,b] X[k,l,i,j],  X = sum_cd (kc|ld) tau[i,j,c,d]  — O(o^4 v^2) flops instead
+    of a pass over every slab of W. Per slab: one GEMM (ac|bd)-shaped product stored straight in [a,b,c,d] order by
+    the index-mapped epilogue, one GEMM against tau. Several ranks: slabs are dealt round-robin, one all-reduce."""
     E = eng.einsum
-    v = eris.nvir
-    na = max(1, min(v, int(slab_bytes // (8 * v * v * v))))
+    be = eng.be
+    v, L = eris.nvir, eris.naux
+    o2 = tau.shape[0] * tau.shape[1]
     Lt = E("ka,Lkc->Lac", t1, eris.Lov)
     Leff = eng.copy(eris.Lvv)
     eng.add(Leff, Lt, -1.0)                                       # (Lvv - t1^T Lov)[L,a,c]
     LA = eng.transpose(Leff, (1, 2, 0))                           # [a, c, L]   rows of a slab are contiguous
-    LB = eng.transpose(eris.Lvv, (1, 2, 0))                       # [b, d, L]
-    OA = eng.transpose(eris.ovvv, (2, 3, 1, 0))                   # ovvv[k,d,a,c] -> [a, c, d, k]
+    del Leff, Lt
     R = eng.zeros((v, v) + tau.shape[:2])                         # [a, b, i, j]
-    # several ranks: the slabs of the first virtual index are dealt round-robin (north_star: "the ladder ... shards
-    # naturally over ab"); every rank fills its rows of R, one all-reduce (sum with zeros) completes it
-    rank, world = (0, 1) if group is None else eng.be.rank_and_size(group)
-    if world > 1:
-        na = max(1, min(na, -(-v // world)))
+    # W[a,b,c,d] = W[b,a,d,c] and tau[i,j,c,d] = tau[j,i,d,c], hence R[a,b,i,j] = R[b,a,j,i]: per slab [a0,a1) only
+    # the blocks b >= a0 are formed (the triangle pyscf's _add_vvvv keeps, ccsd.py / dfccsd.py:54-117); the square
+    # diagonal slab block holds both members of a pair and enters with weight 1/2, and the final
+    # t2new += R^T(2,3,0,1) + R^T(3,2,1,0) restores everything. About (1 + 1/nslabs)/2 of the ladder flops.
+    na = max(1, min(v, int(slab_bytes // (8 * v * v * v)), -(-v // 6)))
+    # several ranks: the slabs are dealt round-robin (north_star: "the ladder ... shards naturally over ab"); every
+    # rank fills its blocks of R, one all-reduce (sum with zeros) completes it
+    rank, world = (0, 1) if group is None else be.rank_and_size(group)
+    BIG = 1 << 30
     for n_slab, a0 in enumerate(range(0, v, na)):
         if n_slab % world != rank:
             continue
         a1 = min(v, a0 + na)
-        W = E("acL,bdL->acbd", _rows(LA, a0, a1), LB)             # (ac|bd) - sum_k t1[k,a](kc|bd)
-        E("acdk,kb->acbd", _rows(OA, a0, a1), t1, alpha=-1.0, out=W, beta=1.0)   # - sum_k (kd|ac) t1[k,b]
-        E("acbd,ijcd->abij", W, tau, out=_rows(R, a0, a1))
+        n_a, n_b = a1 - a0, v - a0
+        # W[b', a, c, d] = sum_L Leff[a0+a, c, L] Leff[a0+b', d, L]: product rows (a,c), columns (b',d); stored b'-major
+        # by the index-mapped epilogue so that the diagonal block (b' < n_a) is a contiguous row range
+        # (the weight 1/2 of the diagonal block rides on this product: columns b' < n_a with alpha = 0.5)
+        W = be.empty(n_b * n_a * v * v)
+        rows_a = LA.buf[a0 * v * L:]
+        be.gemm_nt_mapped(rows_a, rows_a, W, n_a * v, n_a * v, L, (v, v * v, v), (v, n_a * v * v, 1), 0.5, 0.0)
+        if n_b > n_a:
+            be.gemm_nt_mapped(rows_a, LA.buf[a1 * v * L:], W[n_a * n_a * v * v:], n_a * v, (n_b - n_a) * v, L,
+                              (v, v * v, v), (v, n_a * v * v, 1), 1.0, 0.0)
+        eng.flops += 2.0 * n_a * v * n_b * v * L
+        # R[a0+a, a0+b', i, j] = sum_cd W[(b',a),(c,d)] tau[(i,j),(c,d)]: one product over all rows (b', a)
+        base = (a0 * v + a0) * o2
+        be.gemm_nt_mapped(W, tau.buf, R.buf[base:], n_b * n_a, o2, v * v, (n_a, o2, v * o2), (BIG, 0, 1), 1.0, 0.0)
+        eng.flops += 2.0 * n_b * n_a * o2 * v * v
+        eng.gemms += 3
         del W
     if world > 1:
-        eng.be.all_reduce(R.buf, group)
+        be.all_reduce(R.buf, group)
     eng.add(t2new, R, 1.0, (2, 3, 0, 1))
+    eng.add(t2new, R, 1.0, (3, 2, 1, 0))
+    del R
+    X = E("kcld,ijcd->klij", eris.ovov, tau)                      # rank-o^2 correction: - t1 t1 X
+    Y = E("ka,klij->alij", t1, X)
+    E("lb,alij->ijab", t1, Y, alpha=-1.0, out=t2new, beta=1.0)
     return t2new
 
 
@@ -183,10 +210,11 @@ def _intermediates(eng, t1, t2, tau, eris, f, cc2=False):
     E("kcad,id->akic", ovvv, t1, out=Wvoov, beta=1.0)
     E("kcli,la->akic", ovoo, t1, alpha=-1.0, out=Wvoov, beta=1.0)
     E("ldkc,ilda->akic", ovov, t2, alpha=-0.5, out=Wvoov, beta=1.0)
-    E("lckd,ilad->akic", ovov, t2, alpha=-0.5, out=Wvoov, beta=1.0)
+    # (:113) -0.5 (lc|kd) t2[i,l,a,d]  and  (:117) + (ld|kc) t2[i,l,a,d]  contract the same amplitudes: one GEMM with
+    # (ld|kc) - 0.5 (lc|kd) = 0.5 * lov[l,d,k,c]
+    E("ldkc,ilad->akic", lov, t2, alpha=0.5, out=Wvoov, beta=1.0)
     y = E("ldkc,id->lkci", ovov, t1)
     E("lkci,la->akic", y, t1, alpha=-1.0, out=Wvoov, beta=1.0)
-    E("ldkc,ilad->akic", ovov, t2, out=Wvoov, beta=1.0)
     Wvovo = eng.transpose(eris.oovv, (2, 0, 3, 1))
     E("kdac,id->akci", ovvv, t1, out=Wvovo, beta=1.0)
     E("lcki,la->akci", ovoo, t1, alpha=-1.0, out=Wvovo, beta=1.0)
@@ -288,9 +316,10 @@ def update_amps(cc, t1, t2, eris, act_hole=(), act_particle=(), idx_singles=(), 
         _pp_ladder(eng, eris, t1, tau, t2new, group=group)                    # particle-particle ladder (:138)
         _sym_add(eng, t2new, E("ac,ijcb->ijab", im["Lvv"], t2), 1.0)          # (:139-140)
         _sym_add(eng, t2new, E("ki,kjab->ijab", im["Loo"], t2), -1.0)         # (:141-142)
-        tmp = E("akic,kjcb->ijab", im["Wvoov"], t2, alpha=2.0)                # ring (:143-145)
-        E("akci,kjcb->ijab", im["Wvovo"], t2, alpha=-1.0, out=tmp, beta=1.0)
-        _sym_add(eng, t2new, tmp, 1.0)
+        ring = eng.scale(im["Wvoov"], 2.0)                                    # ring (:143-145): 2 Wvoov[a,k,i,c] -
+        eng.add(ring, im["Wvovo"], -1.0, (0, 1, 3, 2))                        # Wvovo[a,k,c,i] share t2[k,j,c,b]: one GEMM
+        _sym_add(eng, t2new, E("akic,kjcb->ijab", ring, t2), 1.0)
+        del ring
         _sym_add(eng, t2new, E("akic,kjbc->ijab", im["Wvoov"], t2), -1.0)     # exchange (:146-149)
         _sym_add(eng, t2new, E("bkci,kjac->ijab", im["Wvovo"], t2), -1.0)
     tmp2 = eng.transpose(ovvv, (1, 3, 0, 2))                              # (:151-154)

@@ -82,6 +82,16 @@ class CudaBackend:
     def gemm_nt(self, a, b, c, m, n, k):
         self.ctx.call("mpccb_gemm_nt", a.data_ptr(), b.data_ptr(), c.data_ptr(), int(m), int(n), int(k))
 
+    def gemv(self, a, x, y, rows, k, trans, alpha, beta):
+        self.ctx.call("mpccb_gemv", a.data_ptr(), x.data_ptr(), y.data_ptr(), int(rows), int(k), int(bool(trans)),
+                      float(alpha), float(beta))
+
+    def gemm_nt_mapped(self, a, b, c, m, n, k, mmap, nmap, alpha, beta):
+        """c[map(m, n)] = alpha * a.b^T + beta * c[map(m, n)]; mmap / nmap = (div, hi, lo) two-level index maps."""
+        self.ctx.call("mpccb_gemm_nt_mapped", a.data_ptr(), b.data_ptr(), c.data_ptr(), int(m), int(n), int(k),
+                      int(mmap[0]), int(mmap[1]), int(mmap[2]), int(nmap[0]), int(nmap[1]), int(nmap[2]),
+                      float(alpha), float(beta))
+
     def div_denominators(self, buf, rank):
         self.ctx.call("mpccb_div_denominators", buf.data_ptr(), int(rank))
 
@@ -132,6 +142,17 @@ class CudaBackend:
         self.torch.cuda.current_stream(self.device).synchronize()
         self.torch.distributed.all_reduce(buf, group=group)
 
+    def tick(self):
+        e = self.torch.cuda.Event(enable_timing=True)
+        e.record()
+        return e
+
+    def tock(self, start):
+        e = self.torch.cuda.Event(enable_timing=True)
+        e.record()
+        e.synchronize()
+        return start.elapsed_time(e)
+
     def rank_and_size(self, group):
         d = self.torch.distributed
         return d.get_rank(group), d.get_world_size(group)
@@ -144,6 +165,29 @@ def _prod(xs):
     return n
 
 
+def two_level_map(indices, ext, stride):
+    """(div, hi, lo) with  offset(r) = (r // div) * hi + (r % div) * lo  for the mixed-radix index r over `indices`
+    (last fastest; extents `ext`, target strides `stride`), or None when no split into two linear groups exists.
+    A group is linear when its strides nest: stride[x_k] == stride[x_{k+1}] * ext[x_{k+1}]."""
+    idx = [ch for ch in indices if ext[ch] > 1]
+    if not idx:
+        return (1 << 30, 0, 0)
+
+    def linear(group):
+        return all(stride[a] == stride[b] * ext[b] for a, b in zip(group[:-1], group[1:]))
+
+    for cut in range(len(idx) + 1):
+        head, tail = idx[:cut], idx[cut:]
+        if linear(head) and linear(tail):
+            div = _prod(ext[ch] for ch in tail) if tail else 1
+            hi = stride[head[-1]] if head else 0
+            lo = stride[tail[-1]] if tail else 0
+            if not head:
+                div = 1 << 30
+            return (div, hi, lo)
+    return None
+
+
 class Engine:
     """Pairwise einsum / transpose / axpy on :class:`DTensor` objects. ``flops`` accumulates 2*M*N*K of
     every GEMM issued (the algorithmic count used for throughput reports)."""
@@ -152,6 +196,9 @@ class Engine:
         self.be = backend
         self.flops = 0.0
         self.gemms = 0
+        self.profile = None          # {spec: [ms, flops, calls]} when switched on (tools/cc_bench.py); synchronises per call
+        self.fuse_output = True      # store products through index maps instead of permute passes (tests switch it off)
+        self.fused_outputs = 0
 
     # -- construction ------------------------------------------------------------------------------
     def tensor(self, array):
@@ -192,6 +239,19 @@ class Engine:
     # -- contraction -------------------------------------------------------------------------------
     def einsum(self, spec, a, b, alpha=1.0, out=None, beta=0.0):
         """``out = alpha * einsum(spec, a, b) + beta * out`` for two operands without batch indices."""
+        if self.profile is None:
+            return self._einsum(spec, a, b, alpha, out, beta)
+        f0 = self.flops
+        t0 = self.be.tick()
+        res = self._einsum(spec, a, b, alpha, out, beta)
+        ms = self.be.tock(t0)
+        rec = self.profile.setdefault(spec, [0.0, 0.0, 0])
+        rec[0] += ms
+        rec[1] += self.flops - f0
+        rec[2] += 1
+        return res
+
+    def _einsum(self, spec, a, b, alpha=1.0, out=None, beta=0.0):
         lhs, io = spec.replace(" ", "").split("->")
         ia, ib = lhs.split(",")
         if len(ia) != a.ndim or len(ib) != b.ndim:
@@ -208,6 +268,10 @@ class Engine:
             raise NotImplementedError(f"einsum {spec}: batch index (present in both operands and the output)")
         if any((ch not in ib and ch not in io) for ch in ia) or any((ch not in ia and ch not in io) for ch in ib):
             raise NotImplementedError(f"einsum {spec}: index summed inside a single operand")
+        if io and io[-1] in ia and io[-1] not in ib and self.fuse_output:
+            # the unit-stride index of the result should be a COLUMN index of the product (lanes of the store epilogues
+            # run along n): C = A.B^T -> C^T = B.A^T, same flops
+            a, b, ia, ib = b, a, ib, ia
         mi = [ch for ch in io if ch in ia]
         ni = [ch for ch in io if ch in ib]
         if len(mi) + len(ni) != len(io):
@@ -224,17 +288,65 @@ class Engine:
             return out
         if K == 0:
             raise NotImplementedError("empty contraction index")
+        if (not mi or not ni) and hasattr(self.be, "gemv"):
+            self.flops += 2.0 * M * N * K
+            self.gemms += 1
+            if not ni:
+                return self._gemv(a, ia, b, ib, mi, ksum, ext, io, alpha, out, beta)
+            return self._gemv(b, ib, a, ia, ni, ksum, ext, io, alpha, out, beta)
         am = self._to_matrix(a, ia, mi + ksum)
         bm = self._to_matrix(b, ib, ni + ksum)
         cm_idx = mi + ni
         perm = tuple(cm_idx.index(ch) for ch in io)
         direct = perm == tuple(range(len(io))) and alpha == 1.0 and beta == 0.0
-        cbuf = out.buf if direct else self.be.empty(M * N)
-        self.be.gemm_nt(am, bm, cbuf, M, N, K)
         self.flops += 2.0 * M * N * K
         self.gemms += 1
-        if not direct:
-            self.be.permute_axpby(cbuf, out.buf, tuple(ext[c] for c in cm_idx), perm, alpha, beta)
+        if direct:
+            self.be.gemm_nt(am, bm, out.buf, M, N, K)
+            return out
+        # the permutation of the result (lib.einsum's last transpose) and "out = alpha * .. + beta * out" go into the
+        # GEMM's store epilogue when rows and columns of the product each map onto the result through a two-level
+        # index map; otherwise the product is permuted / accumulated in a second pass
+        ostride, acc = {}, 1
+        for ch in reversed(io):
+            ostride[ch] = acc
+            acc *= ext[ch]
+        # results of less than one wave of tiles with a long contraction index ("->ia", "->ki", "->ac", "->klij":
+        # K = o*v*v or v*v) stay on the split-K path of mpccb_gemm_nt (K spread over the machine, fixed-order
+        # reduction); permuting the small result costs nothing
+        tiles = -(-M // 128) * -(-N // 128)
+        fuse = self.fuse_output and not (tiles < 148 and K >= 2048)
+        mmap = two_level_map(mi, ext, ostride) if fuse else None
+        nmap = two_level_map(ni, ext, ostride) if fuse else None
+        if mmap is not None and nmap is not None:
+            self.be.gemm_nt_mapped(am, bm, out.buf, M, N, K, mmap, nmap, alpha, beta)
+            self.fused_outputs += 1
+            return out
+        cbuf = self.be.empty(M * N)
+        self.be.gemm_nt(am, bm, cbuf, M, N, K)
+        self.be.permute_axpby(cbuf, out.buf, tuple(ext[c] for c in cm_idx), perm, alpha, beta)
+        return out
+
+    def _gemv(self, mat, imat, vec, ivec, free, ksum, ext, io, alpha, out, beta):
+        """One operand (``vec``) is summed away entirely: a matrix-vector product bound by one read of ``mat``. The
+        matrix is used in place when its contracted indices are its leading or its trailing ones."""
+        nk = len(ksum)
+        kset = set(ksum)
+        if set(imat[:nk]) == kset:
+            korder, forder, trans, mbuf = list(imat[:nk]), list(imat[nk:]), True, mat.buf
+        elif set(imat[nk:]) == kset and len(imat) > nk:
+            korder, forder, trans, mbuf = list(imat[len(imat) - nk:]), list(imat[:len(imat) - nk]), False, mat.buf
+        else:
+            korder, forder, trans = list(ksum), list(free), False
+            mbuf = self._to_matrix(mat, imat, forder + korder)
+        xbuf = self._to_matrix(vec, ivec, korder)
+        rows, K = _prod(ext[c] for c in forder), _prod(ext[c] for c in korder)
+        if forder == list(io):
+            self.be.gemv(mbuf, xbuf, out.buf, rows, K, trans, alpha, beta)
+            return out
+        tmp = self.be.empty(rows)
+        self.be.gemv(mbuf, xbuf, tmp, rows, K, trans, 1.0, 0.0)
+        self.be.permute_axpby(tmp, out.buf, tuple(ext[c] for c in forder), tuple(forder.index(ch) for ch in io), alpha, beta)
         return out
 
     def _to_matrix(self, t, idx, order):

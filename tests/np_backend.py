@@ -38,6 +38,20 @@ class NumpyBackend:
     def gemm_nt(self, a, b, c, m, n, k):
         c[:m * n] = (a[:m * k].reshape(m, k) @ b[:n * k].reshape(n, k).T).reshape(-1)
 
+    def gemv(self, a, x, y, rows, k, trans, alpha, beta):
+        mat = a[:rows * k].reshape(k, rows).T if trans else a[:rows * k].reshape(rows, k)
+        val = alpha * (mat @ x[:k])
+        y[:rows] = val + (beta * y[:rows] if beta != 0.0 else 0.0)
+
+    def gemm_nt_mapped(self, a, b, c, m, n, k, mmap, nmap, alpha, beta):
+        prod = a[:m * k].reshape(m, k) @ b[:n * k].reshape(n, k).T
+        mi, ni = np.arange(m), np.arange(n)
+        off = ((mi // mmap[0]) * mmap[1] + (mi % mmap[0]) * mmap[2])[:, None] \
+            + ((ni // nmap[0]) * nmap[1] + (ni % nmap[0]) * nmap[2])[None, :]
+        assert np.unique(off).size == off.size, "output map is not injective"
+        old = c[off] if beta != 0.0 else 0.0
+        c[off] = alpha * prod + beta * old
+
     def div_denominators(self, buf, rank):
         o, v = self.eo.size, self.ev.size
         eia = self.eo[:, None] - self.ev[None, :]

@@ -42,6 +42,18 @@ def run(o, v, L):
                "launches": ll._ctx.launch_count() - launches0, "tflops": eng.flops / (ms * 1e-3) * 1e-12,
                "pp_ladder_flops": 2.0 * v ** 4 * (L + o * o + o), "ms_eris_build": ms_eris, "eris_flops": fl_eris,
                "emp2": emp2, "e_corr_after": rmpccsd.energy(cc, t1n, t2n, eris)}
+    # per-contraction profile (one more call, synchronising after every einsum)
+    eng.profile = {}
+    t0.record()
+    rmpccsd.update_amps(cc, t1, t2, eris, act_h, act_p, [0, 1, 2], list(range(15)))
+    t1e.record(); torch.cuda.synchronize()
+    tot = t0.elapsed_time(t1e)
+    top = sorted(eng.profile.items(), key=lambda kv: -kv[1][0])[:45]
+    out["profiled_ms_total"] = tot
+    out["einsum_ms_total"] = sum(v[0] for v in eng.profile.values())
+    out["top_einsums"] = [{"spec": k, "ms": round(v[0], 3), "tflops": round(v[1] / max(v[0], 1e-9) * 1e-9, 2), "calls": v[2]}
+                          for k, v in top]
+    eng.profile = None
     return out
 
 
