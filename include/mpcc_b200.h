@@ -64,6 +64,14 @@ int mpccb_bind_t2(mpccb_ctx* ctx, double* t2_abij_dev);
 int mpccb_bind_jk_exchange(mpccb_ctx* ctx, double* jk_local_dev, double* const* peer_jk_dev, int npeers,
                            double* jk_multicast_dev);
 
+/* Subset form of the same exchange: with the mirror scheme (below) rank r's JK rows are needed by the nranks/2 + 1 ranks
+ * r, r-1, .., r-nranks/2 (mod nranks) only — one NVLink store per needed peer. The symmetric allocation holds
+ * nov*ldk (JK) + nov (w = Jvo.X, :128,:133) doubles; mpccb_dress also forms the slab's rows of w and broadcasts them
+ * (through w_multicast_dev when given, else through the peer pointers), mpccb_dress_post then only assembles Fov.
+ * peer_jk_dev: the nranks buffers in rank order as mapped on this device. */
+int mpccb_bind_jk_subset(mpccb_ctx* ctx, double* jk_local_dev, double* const* peer_jk_dev, int nranks, int rank,
+                         double* w_multicast_dev);
+
 /* Mirror scheme of the eris -> t2 step: e[(a,i),(b,j)] is a Gram matrix, so t2[a,b,i,j] = t2[b,a,j,i]; only one
  * block of each pair is computed and its CTA also writes the mirror block (always inside one slab; option "t2_sym" 0
  * turns it off). With several ranks and peer-mapped t2 buffers (symmetric memory) this call extends it across slabs:

@@ -36,6 +36,7 @@ SIGNATURES = {
                                   c_void_p, ctypes.c_size_t]),
     "mpccb_bind_t2": (c_int, [c_void_p, c_void_p]),
     "mpccb_bind_jk_exchange": (c_int, [c_void_p, c_void_p, ctypes.POINTER(c_void_p), c_int, c_void_p]),
+    "mpccb_bind_jk_subset": (c_int, [c_void_p, c_void_p, ctypes.POINTER(c_void_p), c_int, c_int, c_void_p]),
     "mpccb_dress": (c_int, [c_void_p, c_void_p]),
     "mpccb_dress_post": (c_int, [c_void_p]),
     "mpccb_doubles": (c_int, [c_void_p, c_void_p]),

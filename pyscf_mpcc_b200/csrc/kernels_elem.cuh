@@ -128,6 +128,23 @@ k_gemv_cols_partial(const double* __restrict__ A, const double* __restrict__ x, 
   partial[(i64)blockIdx.y * N + n] = (s0 + s1) + (s2 + s3);
 }
 
+// y[r0 + r] = sum_k M[(r0 + r)*ld + k] * x[k] for the slab's rows, stored into every target buffer (peer pointers
+// over NVLink or the multicast address): the slab's share of w = Jvo.X (:128, :133) reaches all ranks with the
+// dressed integrals, so that no rank needs the other slabs' JK rows for it. One warp per row.
+__global__ void __launch_bounds__(256)
+k_gemv_rows_bcast(const double* __restrict__ M, const double* __restrict__ x, JkTargets y, i64 y_off,
+                  int r0, int rows, int K, i64 ld) {
+  const int r = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (r >= rows) return;
+  const int lane = threadIdx.x & 31;
+  const double* row = M + (i64)(r0 + r) * ld;
+  double s = 0.0;
+  for (int k = lane; k < K; k += 32) s += row[k] * x[k];
+  s = warp_sum(s);
+  if (lane == 0)
+    for (int t = 0; t < y.n; ++t) y.p[t][y_off + r0 + r] = s;
+}
+
 // dst[i] = beta*dst[i] + alpha * sum_s P[s*stride + i]   (split-K / tile partial reduction, fixed order)
 __global__ void __launch_bounds__(256)
 k_reduce_splits(double* __restrict__ dst, const double* __restrict__ P, int nsplit, i64 n, i64 stride,

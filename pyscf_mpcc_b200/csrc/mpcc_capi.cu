@@ -61,6 +61,9 @@ struct mpccb_ctx {
       *P, *OmRep, *OmLoc, *OmTot, *Z, *scal, *red, *YP;
   int yvo_split, yvo_split_force;
   JkTargets jk_targets;      // n == 0: plain local JK
+  JkTargets w_targets;       // n > 0: the slab's rows of w = Jvo.X are broadcast by mpccb_dress (subset JK exchange)
+  i64 w_off;                 // offset of w inside the symmetric JK allocation (doubles)
+  double* w_ws;              // w in the private workspace (used unless the subset exchange is bound)
   SymInfo sym;               // symmetric eris/t2 scheme (host copy; tiles/OmPm are device pointers)
   int sym_off, n_tiles;
   const unsigned char* blkflags;   // unfused t2 path under the mirror scheme (see build_tile_list)
@@ -357,6 +360,7 @@ i64 carve_workspace(mpccb_ctx* c, unsigned char* base) {
   c->E1K = w.take(nov * ldk);
   c->Wov = w.take(L * o * v);
   c->w = w.take(nov);
+  c->w_ws = c->w;
   c->F2 = w.take(nov);
   c->Fvo = w.take(nov);
   c->OmP_count = (i64)c->t2_tiles_n * na * o;
@@ -593,6 +597,8 @@ int mpccb_bind_jk_exchange(mpccb_ctx* c, double* jk_local_dev, double* const* pe
   if (!jk_local_dev) return fail(c, "null JK buffer");
   if (npeers < 0 || npeers > 16) return fail(c, "at most 16 peers");
   c->JK = jk_local_dev;
+  c->w_targets.n = 0;        // full exchange: every rank has every JK row and forms w itself
+  c->w = c->w_ws;
   if (jk_multicast_dev) {
     c->jk_targets.n = 1;
     c->jk_targets.p[0] = jk_multicast_dev;
@@ -600,6 +606,37 @@ int mpccb_bind_jk_exchange(mpccb_ctx* c, double* jk_local_dev, double* const* pe
     c->jk_targets.n = npeers;
     for (int r = 0; r < npeers; ++r) c->jk_targets.p[r] = peer_jk_dev[r];
     if (npeers == 0) { c->jk_targets.n = 1; c->jk_targets.p[0] = jk_local_dev; }
+  }
+  return 0;
+}
+
+// Subset form of the fused exchange. The mirror scheme lets rank q compute only the slab pairs (q, s) with
+// (s - q) mod P <= P/2, so rank r's JK rows are needed by the P/2 + 1 ranks q = r - d, d = 0..P/2, only: one NVLink
+// store per needed peer instead of a multicast to everybody (8 ranks: 5 x 50 MB leave and 4 x 50 MB enter each GPU
+// instead of 7 x 50 MB entering). The one consumer that wanted every row on every rank, w = Jvo.X (:128, :133), is
+// computed for the own slab inside mpccb_dress and broadcast (nov doubles in total): the symmetric allocation is
+// nov*ldk (JK) + nov (w) doubles. peer_jk_dev: all nranks buffers in rank order; w goes through w_multicast_dev (the
+// multicast address of the allocation) when given, else through the peer pointers.
+int mpccb_bind_jk_subset(mpccb_ctx* c, double* jk_local_dev, double* const* peer_jk_dev, int nranks, int rank,
+                         double* w_multicast_dev) {
+  if (!c->ws) return fail(c, "bind the workspace first");
+  if (!jk_local_dev || nranks < 2 || nranks > 16 || rank < 0 || rank >= nranks) return fail(c, "bad rank layout");
+  c->JK = jk_local_dev;
+  c->w_off = c->nov * c->ldk;
+  c->w = jk_local_dev + c->w_off;
+  c->jk_targets.n = 0;
+  for (int d = 0; d <= nranks / 2; ++d) {
+    const int q = (rank - d + nranks) % nranks;
+    bool seen = false;
+    for (int t = 0; t < c->jk_targets.n; ++t) seen |= (c->jk_targets.p[t] == peer_jk_dev[q]);
+    if (!seen) c->jk_targets.p[c->jk_targets.n++] = peer_jk_dev[q];
+  }
+  if (w_multicast_dev) {
+    c->w_targets.n = 1;
+    c->w_targets.p[0] = w_multicast_dev;
+  } else {
+    c->w_targets.n = nranks;
+    for (int r = 0; r < nranks; ++r) c->w_targets.p[r] = peer_jk_dev[r];
   }
   return 0;
 }
@@ -683,6 +720,11 @@ extern "C" int mpccb_dress(mpccb_ctx* c, const double* t1_dev) {
     k_dress_finalize<<<grid, block, 0, c->stream>>>(c->Xov, c->Lov, c->JT, c->XT, c->X, c->t1, jk, c->E1K,
                                                     c->Wov, L, o, v, c->ldk, a0, a0 + na);
     LAUNCH_OK(c, "k_dress_finalize");
+    if (c->w_targets.n > 0) {   // subset exchange: the slab's rows of w = Jvo.X go to every rank with the integrals
+      k_gemv_rows_bcast<<<cdiv((i64)na * o, 8), 256, 0, c->stream>>>(c->JK, c->X, c->w_targets, c->w_off, a0 * o,
+                                                                     na * o, L, c->ldk);
+      LAUNCH_OK(c, "k_gemv_rows_bcast");
+    }
   }
   {  // :126-127  OmRep[a][i] = sum_{(L,j)} W[(L,j)][a] Joo[(L,j)][i],  a in slab
     Operand A = flat_operand(c->Wov + a0, na, 1, v);
@@ -701,9 +743,11 @@ extern "C" int mpccb_dress_post(mpccb_ctx* c) {
   if (!c->ws || !c->Lov) return fail(c, "workspace/integrals not bound");
   StageTimer timer(c, ST_DRESS_POST);
   const i64 nov = c->nov;
-  // :128 and first half of :133   w[(a,i)] = sum_L J[(a,i)][L] X[L]
-  k_gemv_rows<<<cdiv(nov, 8), 256, 0, c->stream>>>(c->JK, c->X, c->w, (int)nov, c->L, c->ldk);
-  LAUNCH_OK(c, "k_gemv_rows");
+  // :128 and first half of :133   w[(a,i)] = sum_L J[(a,i)][L] X[L]   (already exchanged in the subset form)
+  if (c->w_targets.n == 0) {
+    k_gemv_rows<<<cdiv(nov, 8), 256, 0, c->stream>>>(c->JK, c->X, c->w, (int)nov, c->L, c->ldk);
+    LAUNCH_OK(c, "k_gemv_rows");
+  }
   k_make_fvo<<<cdiv(nov, 256), 256, 0, c->stream>>>(c->w, c->F2, c->Fvo, nov);
   LAUNCH_OK(c, "k_make_fvo");
   return 0;

@@ -246,8 +246,10 @@ class MPCC_LL:
         if self.world_size > 1:
             self._setup_jk_exchange(jk_exchange or os.environ.get("MPCC_JK_EXCHANGE", "auto"))
         self._t2_peers = False
-        if self.world_size > 1 and self._t2_sym and self._jk_mode in ("multicast", "p2p"):
+        if self.world_size > 1 and self._t2_sym and self._jk_mode in ("multicast", "p2p", "subset"):
             self._setup_t2_peers()
+        if self._jk_mode == "subset" and not self._t2_peers:
+            self._bind_jk(subset=False)                  # without the cross-rank mirror every rank needs every JK row
         if not self._t2_peers:
             # odd nocc: the pad column is read by TMA boxes (and multiplied by Lvo's zero column) — it must stay finite
             self._T = (torch.zeros if self._jp != o else torch.empty)(self._na * v * o * self._jp, **f64)
@@ -414,13 +416,13 @@ class MPCC_LL:
         o, v = self.nocc, self.nvir
         ptr, count = self._ctx.buffer("JK")
         ldk = count // self.nov
-        if mode not in ("auto", "multicast", "p2p", "nccl"):
+        if mode not in ("auto", "multicast", "p2p", "subset", "nccl"):
             raise ValueError(f"jk_exchange={mode!r}")
         ok, hdl, buf = 0, None, None
         if mode != "nccl" and self._symm_agreed():
             try:
                 import torch.distributed._symmetric_memory as symm
-                buf = symm.empty(count, dtype=torch.float64, device=self.device)
+                buf = symm.empty(count + self.nov, dtype=torch.float64, device=self.device)   # JK rows + w = Jvo.X
                 hdl = symm.rendezvous(buf, self.group)
                 ok = 1
             except Exception as e:                      # no peer mapping on this system: use NCCL
@@ -433,11 +435,14 @@ class MPCC_LL:
             torch.cuda.current_stream(self.device).synchronize()
             hdl.barrier(channel=0)                       # nobody stores into a buffer that is still being cleared
             mc = int(getattr(hdl, "multicast_ptr", 0) or 0)
-            use_mc = mc != 0 and mode in ("auto", "multicast")
-            peers = (ctypes.c_void_p * self.world_size)(*[int(p) for p in hdl.buffer_ptrs])
-            self._ctx.call("mpccb_bind_jk_exchange", buf.data_ptr(), peers, self.world_size, mc if use_mc else None)
-            self._jk_buf, self._jk_hdl = buf, hdl
-            self._jk_mode = "multicast" if use_mc else "p2p"
+            self._jk_buf, self._jk_hdl, self._jk_mc = buf, hdl, mc
+            # "subset": one store per rank that needs the slab (world/2 + 1 of them under the mirror scheme) instead of
+            # a multicast to everybody; pays from 4 ranks on and needs the cross-rank mirror (peer-mapped t2)
+            want_subset = mode == "subset" or (mode == "auto" and self.world_size >= 4)
+            if want_subset and self._t2_sym:
+                self._bind_jk(subset=True)
+            else:
+                self._bind_jk(subset=False, multicast=mode in ("auto", "multicast", "subset"))
             return
         off = ptr - self._ws.data_ptr()
         self._jk_view = self._ws[off:off + count * 8].view(torch.float64)
@@ -446,6 +451,17 @@ class MPCC_LL:
             self._jk_rows.append((b0 * o * ldk, b1 * o * ldk))
         self._equal_slabs = len({hi - lo for lo, hi in self._jk_rows}) == 1
         self._jk_mode = "nccl"
+
+    def _bind_jk(self, subset, multicast=True):
+        hdl, buf, mc = self._jk_hdl, self._jk_buf, self._jk_mc
+        peers = (ctypes.c_void_p * self.world_size)(*[int(p) for p in hdl.buffer_ptrs])
+        if subset:
+            self._ctx.call("mpccb_bind_jk_subset", buf.data_ptr(), peers, self.world_size, self.rank, mc if mc else None)
+            self._jk_mode = "subset"
+            return
+        use_mc = mc != 0 and multicast
+        self._ctx.call("mpccb_bind_jk_exchange", buf.data_ptr(), peers, self.world_size, mc if use_mc else None)
+        self._jk_mode = "multicast" if use_mc else "p2p"
 
     def _symm_agreed(self):
         """All ranks agree, BEFORE anyone enters the collective rendezvous, that symmetric memory can be tried: a
@@ -516,7 +532,7 @@ class MPCC_LL:
         ctx.call("mpccb_dress", t1_dev.data_ptr())
         if self.world_size == 1:
             return
-        if self._jk_mode in ("multicast", "p2p"):
+        if self._jk_mode in ("multicast", "p2p", "subset"):
             self._jk_hdl.barrier(channel=0)              # every rank's rows have landed in every buffer
         else:
             jk, rows = self._jk_view, self._jk_rows
