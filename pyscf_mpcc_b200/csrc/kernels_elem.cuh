@@ -415,11 +415,14 @@ __device__ __forceinline__ i64 tril_below(i64 r, i64 c) { return (r * (r + 1)) /
 // together, so it is served by L1), 4 elements per thread in flight. Measured against two alternatives (staging the
 // block through shared memory; 8 x 4 thread tiles with sector-exact slab reads) this form was the fastest; it still
 // runs about 25 % below the row-owned kernel per byte.
+// xprev is always an explicit stored vector here: the on-the-fly combination of the row-owned kernel costs this
+// one (bound by its address arithmetic and the strided slab read, not by HBM) more than the combine pass saves
+// (two ranks: 8.3 ms against 3.2 + 1.8 ms).
 // scatter_to != nullptr: instead of the DIIS update, copy the local vector `xprev` into a full reference-order
 // packed vector (host-facing gathers; the caller all-reduces the zero-initialised targets).
 __global__ void __launch_bounds__(256)
 k_diis_push_cols(const double* __restrict__ T, const double* __restrict__ t1new,
-                 const double* xprev, DiisPrev pv, double* xs, double* es,
+                 const double* __restrict__ xprev, double* __restrict__ xs, double* __restrict__ es,
                  DiisPtrs eptr, int nd, int slot, int first_call, int count_t1,
                  int o, int jp, int v, int a0, int na, const i64* __restrict__ prefix, int G,
                  double* __restrict__ partial, double* __restrict__ scatter_to) {
@@ -467,7 +470,7 @@ k_diis_push_cols(const double* __restrict__ T, const double* __restrict__ t1new,
         } else {
           double e[U];
 #pragma unroll
-          for (int u = 0; u < U; ++u) e[u] = ok[u] ? val[u] - diis_prev_value(pv, xprev, pos[u]) : 0.0;
+          for (int u = 0; u < U; ++u) e[u] = ok[u] ? val[u] - xprev[pos[u]] : 0.0;
 #pragma unroll
           for (int q = 0; q < 6; ++q) {
             if (q < nd) {
@@ -489,7 +492,7 @@ k_diis_push_cols(const double* __restrict__ T, const double* __restrict__ t1new,
       if (first_call) {
         xs[c] = val;
       } else {
-        const double e = val - diis_prev_value(pv, xprev, c);
+        const double e = val - xprev[c];
         double other[6];
 #pragma unroll
         for (int q = 0; q < 6; ++q) other[q] = (q < nd && q != slot) ? eptr.e[q][c] : 0.0;

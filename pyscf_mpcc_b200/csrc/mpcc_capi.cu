@@ -1131,13 +1131,13 @@ extern "C" int mpccb_t2_to_aibj(mpccb_ctx* c, double* out_dev) {
 }
 
 namespace {
-int launch_diis_cols(mpccb_ctx* c, const double* t1_new_dev, const double* xprev_dev, const DiisPrev& pv,
+int launch_diis_cols(mpccb_ctx* c, const double* t1_new_dev, const double* xprev_dev,
                      double* x_slot_dev, double* e_slot_dev, const DiisPtrs& ep, int nd, int slot, int first_call,
                      int count_t1, double* scatter_to, int* grid_out) {
   const i64 nblocks = (i64)c->na * c->v;
   const int G = (int)std::min<i64>(nblocks, DIIS_COLS_GRID);
   if ((i64)(G + 1) * 7 > c->P_count) return fail(c, "DIIS partial scratch too small");
-  k_diis_push_cols<<<G + 1, 256, 0, c->stream>>>(c->T, t1_new_dev, xprev_dev, pv, x_slot_dev, e_slot_dev, ep, nd, slot,
+  k_diis_push_cols<<<G + 1, 256, 0, c->stream>>>(c->T, t1_new_dev, xprev_dev, x_slot_dev, e_slot_dev, ep, nd, slot,
                                                  first_call, count_t1, c->o, c->jp, c->v, c->a_begin, c->na,
                                                  reinterpret_cast<const i64*>(c->diis_prefix), G, c->P, scatter_to);
   LAUNCH_OK(c, "k_diis_push_cols");
@@ -1156,8 +1156,7 @@ extern "C" int mpccb_pack_tril_rows(mpccb_ctx* c, double* seg_dev) {
   if (!c->T) return fail(c, "t2 buffer not bound");
   if (c->diis_prefix) {                      // column-owned order; seg_dev is the t2 part (vector + nov)
     DiisPtrs ep = {};
-    DiisPrev pv = {};
-    return launch_diis_cols(c, nullptr, nullptr, pv, seg_dev - c->nov, nullptr, ep, 0, 0, 1, 0, nullptr, nullptr);
+    return launch_diis_cols(c, nullptr, nullptr, seg_dev - c->nov, nullptr, ep, 0, 0, 1, 0, nullptr, nullptr);
   }
   k_pack_rows<<<c->na * c->o, 256, 0, c->stream>>>(c->T, seg_dev, c->nov, (i64)c->a_begin * c->o, c->o, c->jp - c->o);
   LAUNCH_OK(c, "k_pack_rows");
@@ -1168,8 +1167,7 @@ extern "C" int mpccb_diis_scatter_tril(mpccb_ctx* c, const double* seg_dev, doub
   CUDA_OK(c, enter_device(c));
   if (!c->diis_prefix) return fail(c, "the DIIS vector is row-owned: its segments are contiguous, no scatter needed");
   DiisPtrs ep = {};
-  DiisPrev pv = {};
-  return launch_diis_cols(c, nullptr, seg_dev - c->nov, pv, nullptr, nullptr, ep, 0, 0, 0, 0, full_packed_dev, nullptr);
+  return launch_diis_cols(c, nullptr, seg_dev - c->nov, nullptr, nullptr, ep, 0, 0, 0, 0, full_packed_dev, nullptr);
 }
 
 extern "C" int mpccb_unpack_oovv(mpccb_ctx* c, const double* packed_dev, double* out_dev) {
@@ -1201,7 +1199,8 @@ extern "C" int mpccb_diis_push(mpccb_ctx* c, const double* t1_new_dev, const dou
   }
   int grid = 0;
   if (c->diis_prefix) {
-    if (launch_diis_cols(c, t1_new_dev, xprev_dev, pv, x_slot_dev, e_slot_dev, ep, nd, slot, first_call, count_t1,
+    if (n_prev > 0) return fail(c, "the column-owned DIIS push takes an explicit xprev (n_prev = 0)");
+    if (launch_diis_cols(c, t1_new_dev, xprev_dev, x_slot_dev, e_slot_dev, ep, nd, slot, first_call, count_t1,
                          nullptr, &grid)) return 1;
   } else {
     const i64 r0 = (i64)c->a_begin * c->o;
