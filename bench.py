@@ -517,7 +517,7 @@ def run_b200(args):
                    "l2": "inputs_exceed_l2 (t2 buffer 8.6 GB, DIIS vectors 4.3 GB each at the default shape)",
                    "inputs": "pyscf_mpcc_b200.synthetic.host_blocks (seeded host generator of the fixtures), uploaded before the timed region",
                    "parallelism": f"a-slab x{world}", "slab_bounds": list(ll._bounds) if world > 1 else None,
-                   "diis_vector": "column-owned" if ll._diis_columns else "row-owned", "jk_exchange": ll._jk_mode, "t2_peer_mirror": bool(ll._t2_peers),
+                   "diis_vector": "column-owned" if ll._diis_columns else "row-owned", "jk_exchange": ll._jk_mode, "xoo": ll._xoo_mode, "t2_peer_mirror": bool(ll._t2_peers),
                    "flop_per_iteration": flop_it,
                    "flop_note": "value counts the ALGORITHMIC flops of the reference iteration (SURVEY.md 8d: 4 L nov^2 + ...); "
                                 "the eris GEMM executes about half of its share by symmetry, so value can exceed the FP64 peak"},

@@ -66,11 +66,22 @@ int mpccb_bind_jk_exchange(mpccb_ctx* ctx, double* jk_local_dev, double* const* 
 
 /* Subset form of the same exchange: with the mirror scheme (below) rank r's JK rows are needed by the nranks/2 + 1 ranks
  * r, r-1, .., r-nranks/2 (mod nranks) only — one NVLink store per needed peer. The symmetric allocation holds
- * nov*ldk (JK) + nov (w = Jvo.X, :128,:133) doubles; mpccb_dress also forms the slab's rows of w and broadcasts them
- * (through w_multicast_dev when given, else through the peer pointers), mpccb_dress_post then only assembles Fov.
+ * nov*ldk (JK) + nov (w = Jvo.X, :128) + nov (Fvo = w - F2, :133) doubles; mpccb_dress forms the slab's rows of w and
+ * of Fvo (F2 is then a GEMM over the slab's rows only) and broadcasts them (through w_multicast_dev when given, else
+ * through the peer pointers); mpccb_dress_post has nothing left to do.
  * peer_jk_dev: the nranks buffers in rank order as mapped on this device. */
 int mpccb_bind_jk_subset(mpccb_ctx* ctx, double* jk_local_dev, double* const* peer_jk_dev, int nranks, int rank,
                          double* w_multicast_dev);
+
+/* Xoo = Lov.t1^T (:120) and Joo = Xoo + Loo (:123) do not depend on the virtual slab; replicated they cost every rank
+ * the same GEMM however many ranks there are. Sharded form: the ranks allocate [Xoo | Joo] (2 * naux * nocc^2 doubles)
+ * in symmetric memory; rank r computes the rows of its slab of the AUXILIARY index, l in [naux r / P, naux (r+1) / P),
+ * and stores its Xoo rows into every rank's buffer (through xoo_multicast_dev when given, else one store per peer
+ * pointer; Joo is completed locally from the exchanged Xoo).
+ * mpccb_dress then returns once the exchange and the slab's Xvo GEMM (:119) are issued; the caller runs a cross-rank
+ * barrier on the stream and calls mpccb_dress_rest. xoo_local_dev == NULL goes back to the replicated form. */
+int mpccb_bind_xoo_exchange(mpccb_ctx* ctx, double* xoo_local_dev, double* const* peer_xoo_dev, int nranks, int rank,
+                            double* xoo_multicast_dev);
 
 /* Mirror scheme of the eris -> t2 step: e[(a,i),(b,j)] is a Gram matrix, so t2[a,b,i,j] = t2[b,a,j,i]; only one
  * block of each pair is computed and its CTA also writes the mirror block (always inside one slab; option "t2_sym" 0
@@ -87,6 +98,9 @@ int mpccb_dress(mpccb_ctx* ctx, const double* t1_dev);
 /* phase 1b — several ranks: after the caller has all-gathered the JK rows of all slabs (buffer "JK" of
  * mpccb_get_buffer; slabs are contiguous row ranges), form w = Jvo.X and Fov for every (b,j) (:128,:133) */
 int mpccb_dress_post(mpccb_ctx* ctx);
+/* second half of mpccb_dress (everything that reads Xoo / Joo for every auxiliary index); mpccb_dress runs it itself
+ * unless the Xoo exchange is bound */
+int mpccb_dress_rest(mpccb_ctx* ctx);
 /* phase 2, :135-147 — eris/t2 (fused), Yvo, doubles->singles, energy, for the local slab.
  * Writes the slab's partial sums to red_dev[0..nov) = Omega part [a,i], red_dev[nov] = dE part;
  * with several ranks the caller all-reduces red_dev (nov+1 doubles) before phase 3. */

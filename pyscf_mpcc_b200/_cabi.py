@@ -39,6 +39,8 @@ SIGNATURES = {
     "mpccb_bind_jk_subset": (c_int, [c_void_p, c_void_p, ctypes.POINTER(c_void_p), c_int, c_int, c_void_p]),
     "mpccb_dress": (c_int, [c_void_p, c_void_p]),
     "mpccb_dress_post": (c_int, [c_void_p]),
+    "mpccb_dress_rest": (c_int, [c_void_p]),
+    "mpccb_bind_xoo_exchange": (c_int, [c_void_p, c_void_p, ctypes.POINTER(c_void_p), c_int, c_int, c_void_p]),
     "mpccb_doubles": (c_int, [c_void_p, c_void_p]),
     "mpccb_t2_tiles": (c_int, [c_void_p, ctypes.POINTER(c_ll), ctypes.POINTER(c_ll)]),
     "mpccb_sym_query": (c_int, [c_int, c_int, ctypes.POINTER(c_int), c_int, c_int, c_int]),

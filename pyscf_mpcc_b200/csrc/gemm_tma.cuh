@@ -75,6 +75,12 @@ __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, u
       ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
       : "memory");
 }
+__device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+      ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
 __device__ __forceinline__ void tma_load_4d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1,
                                             int c2, int c3) {
   asm volatile(
@@ -134,6 +140,9 @@ struct TmaGemmParams {
   int nk;                // number of 16-wide K steps
   // A-operand addressing: mode 0 = 2-D map (k, row); mode 1 = 4-D map over T[a][b][i][j]:
   //   k step kt -> (b = kt / jsteps, j0 = 16 * (kt % jsteps)), rows = (a, i)
+  // mode 2 = 3-D map (k, r, q) over a matrix whose rows m = q * rows_per_q + r are NOT equally spaced (a slab of the
+  //   middle index of a 3-index tensor, e.g. Lvv[L][a in slab][b]): rows_per_q = o (reused), tile row m0 -> box origin
+  //   (r = m0 % rows_per_q, q = m0 / rows_per_q); the box is (16, min(rows_per_q, 128), 128 / that)
   int a_mode, jsteps, o, n_a;
   int i0;                // a_mode 1: first occupied index i of the rows this launch covers (box = 16 j x w i x 1 b x n_a a)
   uint32_t a_bytes, b_bytes;   // bytes one stage receives for A / B (box sizes)
@@ -196,6 +205,9 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
     mbar_expect_tx(&full[s], p.a_bytes + p.b_bytes);
     if (p.a_mode == 0) {
       tma_load_2d(a_dst, &mapA, &full[s], kt * TMA_TK, m0);
+    } else if (p.a_mode == 2) {
+      const int q = m0 / p.o;
+      tma_load_3d(a_dst, &mapA, &full[s], kt * TMA_TK, m0 - q * p.o, q);
     } else {
       // K runs over (b, j); j in chunks of 16 — for nocc not a multiple of 16 the last chunk of every b reads past
       // the j extent of the 4-D map and TMA zero-fills it, which also cancels B's columns of the next b

@@ -128,21 +128,69 @@ k_gemv_cols_partial(const double* __restrict__ A, const double* __restrict__ x, 
   partial[(i64)blockIdx.y * N + n] = (s0 + s1) + (s2 + s3);
 }
 
-// y[r0 + r] = sum_k M[(r0 + r)*ld + k] * x[k] for the slab's rows, stored into every target buffer (peer pointers
-// over NVLink or the multicast address): the slab's share of w = Jvo.X (:128, :133) reaches all ranks with the
-// dressed integrals, so that no rank needs the other slabs' JK rows for it. One warp per row.
+// w[r0 + r] = sum_k M[(r0 + r)*ld + k] * x[k] and f[r0 + r] = w[r0 + r] - F2[r0 + r] for the slab's rows, both stored
+// into every target buffer (peer pointers over NVLink or the multicast address) at offsets w_off / f_off: the slab's
+// share of w = Jvo.X (:128) and of Fvo (:133) reaches all ranks with the dressed integrals, so that no rank needs the
+// other slabs' JK rows or F2 rows for them. One warp per row, four independent partial sums per lane.
 __global__ void __launch_bounds__(256)
-k_gemv_rows_bcast(const double* __restrict__ M, const double* __restrict__ x, JkTargets y, i64 y_off,
-                  int r0, int rows, int K, i64 ld) {
+k_gemv_rows_bcast(const double* __restrict__ M, const double* __restrict__ x, const double* __restrict__ F2,
+                  JkTargets y, i64 w_off, i64 f_off, int r0, int rows, int K, i64 ld) {
   const int r = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (r >= rows) return;
   const int lane = threadIdx.x & 31;
   const double* row = M + (i64)(r0 + r) * ld;
-  double s = 0.0;
-  for (int k = lane; k < K; k += 32) s += row[k] * x[k];
-  s = warp_sum(s);
-  if (lane == 0)
-    for (int t = 0; t < y.n; ++t) y.p[t][y_off + r0 + r] = s;
+  double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+  int k = lane;
+  for (; k + 96 < K; k += 128) {
+    s0 = fma(row[k], x[k], s0);
+    s1 = fma(row[k + 32], x[k + 32], s1);
+    s2 = fma(row[k + 64], x[k + 64], s2);
+    s3 = fma(row[k + 96], x[k + 96], s3);
+  }
+  for (; k < K; k += 32) s0 = fma(row[k], x[k], s0);
+  const double s = warp_sum((s0 + s1) + (s2 + s3));
+  if (lane == 0) {
+    const double f = s - F2[r0 + r];
+    for (int t = 0; t < y.n; ++t) {
+      y.p[t][w_off + r0 + r] = s;
+      y.p[t][f_off + r0 + r] = f;
+    }
+  }
+}
+
+// Copies base[off .. off+n) to the same offsets of every target buffer (peer pointers over NVLink, or the multicast
+// address, which also rewrites the — identical — local copy): the L slab of Xoo a rank has just computed, for
+// everybody. Eight loads in flight per thread.
+__global__ void __launch_bounds__(256)
+k_bcast_rows(const double* __restrict__ base, JkTargets tg, i64 off, i64 n) {
+  const i64 stride = (i64)gridDim.x * blockDim.x;
+  for (i64 i0 = (i64)blockIdx.x * blockDim.x + threadIdx.x; i0 < n; i0 += 8 * stride) {
+    double a[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const i64 i = i0 + u * stride;
+      a[u] = i < n ? base[off + i] : 0.0;
+    }
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const i64 i = i0 + u * stride;
+      if (i < n)
+        for (int t = 0; t < tg.n; ++t) tg.p[t][off + i] = a[u];
+    }
+  }
+}
+
+// out[i] = x[i] + y[i] for i in [0, skip0) and [skip1, n): Joo = Xoo + Loo (:123) for the L slabs that arrived from
+// the other ranks (the slab [skip0, skip1) computed here got its Joo rows from the GEMM epilogue)
+__global__ void __launch_bounds__(256)
+k_add_outside(const double* __restrict__ x, const double* __restrict__ y, double* __restrict__ out,
+              i64 skip0, i64 skip1, i64 n) {
+  const i64 stride = (i64)gridDim.x * blockDim.x;
+  const i64 m = n - (skip1 - skip0);
+  for (i64 q = (i64)blockIdx.x * blockDim.x + threadIdx.x; q < m; q += stride) {
+    const i64 i = q < skip0 ? q : q + (skip1 - skip0);
+    out[i] = x[i] + y[i];
+  }
 }
 
 // dst[i] = beta*dst[i] + alpha * sum_s P[s*stride + i]   (split-K / tile partial reduction, fixed order)
@@ -207,48 +255,51 @@ k_final_sums(const double* __restrict__ partial, double* __restrict__ out, int n
 // Singles residual assembly + T1 update (reference :128-131, :149-151).
 //   Om[a,i]  = [OmRep[a,i] if given] + w[(a,i)] + OmLoc[a,i] + sum_b t1[i,b] fvv[b,a] - sum_k t1[k,a] foo[i,k]
 //   t1n[i,a] = -Om[a,i]/(ev[a]-eo[i]);  partial[block] = sum (t1[i,a] - t1n[i,a])^2
+// grid (ceil(v/32), o), 256 threads: a CTA makes 32 consecutive a of one i; warp p sums the terms b = p (mod 8) and
+// k = p (mod 8) of the two contractions (lanes along a: t1 / fvv rows coalesced), warp 0 adds the eight parts in
+// fixed order. The kernel is replicated on every rank — its latency is serial time at 8 GPUs — hence the split of
+// each 576-term sum over eight warps rather than one thread per element.
 __global__ void __launch_bounds__(256)
 k_t1_update(const double* __restrict__ OmRep, const double* __restrict__ w, const double* __restrict__ OmLoc,
             const double* __restrict__ t1, const double* __restrict__ fvv, const double* __restrict__ foo,
             const double* __restrict__ eo, const double* __restrict__ ev,
             double* __restrict__ t1n, double* __restrict__ OmOut, double* __restrict__ partial, int o, int v) {
-  __shared__ double scratch[32];
-  const i64 idx = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  __shared__ double part[8][33];
+  const int x = threadIdx.x & 31, p = threadIdx.x >> 5;
+  const int i = blockIdx.y, a = blockIdx.x * 32 + x;
+  double acc = 0.0;
+  if (a < v) {
+    const double* t1i = t1 + (i64)i * v;
+    double s0 = 0.0, s1 = 0.0;
+    int b = p;
+    for (; b + 8 < v; b += 16) {
+      s0 = fma(t1i[b], fvv[(i64)b * v + a], s0);
+      s1 = fma(t1i[b + 8], fvv[(i64)(b + 8) * v + a], s1);
+    }
+    if (b < v) s0 = fma(t1i[b], fvv[(i64)b * v + a], s0);
+    double u = 0.0;
+    for (int k = p; k < o; k += 8) u = fma(t1[(i64)k * v + a], foo[(i64)i * o + k], u);
+    acc = (s0 + s1) - u;
+  }
+  part[p][x] = acc;
+  __syncthreads();
+  if (p != 0) return;
   double r2 = 0.0;
-  if (idx < (i64)o * v) {
-    const int i = (int)(idx / v), a = (int)(idx % v);   // lanes along a: t1/t1n/fvv coalesced
-    const i64 ai = (i64)a * o + i;
+  if (a < v) {
+    const i64 ai = (i64)a * o + i, idx = (i64)i * v + a;
     double om = (OmRep ? OmRep[ai] : 0.0) + w[ai] + OmLoc[ai];
-    // four independent accumulation chains per sum (fixed order): the loads of a chain no longer wait for the
-    // previous FMA — this kernel is replicated on every rank, its latency is serial time at 8 GPUs
-    double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
-    int b = 0;
-    for (; b + 4 <= v; b += 4) {
-      s0 = fma(t1[(i64)i * v + b], fvv[(i64)b * v + a], s0);
-      s1 = fma(t1[(i64)i * v + b + 1], fvv[(i64)(b + 1) * v + a], s1);
-      s2 = fma(t1[(i64)i * v + b + 2], fvv[(i64)(b + 2) * v + a], s2);
-      s3 = fma(t1[(i64)i * v + b + 3], fvv[(i64)(b + 3) * v + a], s3);
-    }
-    for (; b < v; ++b) s0 = fma(t1[(i64)i * v + b], fvv[(i64)b * v + a], s0);
-    om += (s0 + s1) + (s2 + s3);
-    s0 = s1 = s2 = s3 = 0.0;
-    int k = 0;
-    for (; k + 4 <= o; k += 4) {
-      s0 = fma(t1[(i64)k * v + a], foo[(i64)i * o + k], s0);
-      s1 = fma(t1[(i64)(k + 1) * v + a], foo[(i64)i * o + k + 1], s1);
-      s2 = fma(t1[(i64)(k + 2) * v + a], foo[(i64)i * o + k + 2], s2);
-      s3 = fma(t1[(i64)(k + 3) * v + a], foo[(i64)i * o + k + 3], s3);
-    }
-    for (; k < o; ++k) s0 = fma(t1[(i64)k * v + a], foo[(i64)i * o + k], s0);
-    om -= (s0 + s1) + (s2 + s3);
+    double s = 0.0;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) s += part[q][x];
+    om += s;
     const double q = om / (ev[a] - eo[i]);
     t1n[idx] = -q;
     OmOut[ai] = om;
     const double d = t1[idx] + q;
     r2 = d * d;
   }
-  r2 = block_sum(r2, scratch);
-  if (threadIdx.x == 0) partial[blockIdx.x] = r2;
+  r2 = warp_sum(r2);
+  if (x == 0) partial[(i64)blockIdx.y * gridDim.x + blockIdx.x] = r2;
 }
 
 // ---------------------------------------------------------------------------
@@ -582,17 +633,22 @@ k_pack_rows(const double* __restrict__ T, double* __restrict__ seg, i64 nov, i64
 }  // namespace mpccb
 
 namespace mpccb {
-// out[q] = sum_b partial[b*ld + q] for q < nq  (single block; fixed order)
+// out[q] = sum_b partial[b*ld + q] for q < nq  (one block per q; fixed order). The DIIS dots wait for this on the
+// host, so the nq sums run side by side instead of one after the other.
 __global__ void __launch_bounds__(256)
 k_final_sums_strided(const double* __restrict__ partial, double* __restrict__ out, int nblocks, int ld, int nq) {
   __shared__ double scratch[32];
-  for (int q = 0; q < nq; ++q) {
-    double s = 0.0;
-    for (int b = threadIdx.x; b < nblocks; b += blockDim.x) s += partial[(i64)b * ld + q];
-    s = block_sum(s, scratch);
-    if (threadIdx.x == 0) out[q] = s;
-    __syncthreads();
+  const int q = blockIdx.x;
+  if (q >= nq) return;
+  double s0 = 0.0, s1 = 0.0;
+  int b = threadIdx.x;
+  for (; b + 256 < nblocks; b += 512) {
+    s0 += partial[(i64)b * ld + q];
+    s1 += partial[(i64)(b + 256) * ld + q];
   }
+  if (b < nblocks) s0 += partial[(i64)b * ld + q];
+  const double s = block_sum(s0 + s1, scratch);
+  if (threadIdx.x == 0) out[q] = s;
 }
 }  // namespace mpccb
 

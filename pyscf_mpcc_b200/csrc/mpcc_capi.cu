@@ -45,6 +45,7 @@ struct mpccb_ctx {
   cudaStream_t stream;
   long long launches;
   int use_tma;
+  int xvo_generic;           // 1: keep the Xvo GEMM (:119) on the generic kernel (A/B measurements)
   char err[512];
   // bound tensors
   const double *Loo, *Lov, *Lvv, *foo, *fvv, *eo, *ev;
@@ -64,6 +65,10 @@ struct mpccb_ctx {
   JkTargets w_targets;       // n > 0: the slab's rows of w = Jvo.X are broadcast by mpccb_dress (subset JK exchange)
   i64 w_off;                 // offset of w inside the symmetric JK allocation (doubles)
   double* w_ws;              // w in the private workspace (used unless the subset exchange is bound)
+  double* Fvo_ws;            // Fvo likewise
+  double* Xoo_ws;            // [Xoo | Joo] in the private workspace (used unless the Xoo exchange is bound)
+  JkTargets xoo_targets;     // n > 0: Xoo is computed for an L slab per rank and stored into the peers' buffers
+  int xoo_l0, xoo_l1;        // this rank's slab of the auxiliary index
   SymInfo sym;               // symmetric eris/t2 scheme (host copy; tiles/OmPm are device pointers)
   int sym_off, n_tiles;
   const unsigned char* blkflags;   // unfused t2 path under the mirror scheme (see build_tile_list)
@@ -353,6 +358,7 @@ i64 carve_workspace(mpccb_ctx* c, unsigned char* base) {
   c->Xov = w.take(L * o * v);
   c->Xoo = w.take(2 * L * o * o);           // [Xoo | Joo] adjacent: one GEMM dresses both with t1
   c->Joo = c->Xoo ? c->Xoo + L * o * o : nullptr;
+  c->Xoo_ws = c->Xoo;
   c->X = w.take(L);
   c->XT = w.take(2 * L * o * v);            // [XT | JT]
   c->JT = c->XT ? c->XT + L * o * v : nullptr;
@@ -363,6 +369,7 @@ i64 carve_workspace(mpccb_ctx* c, unsigned char* base) {
   c->w_ws = c->w;
   c->F2 = w.take(nov);
   c->Fvo = w.take(nov);
+  c->Fvo_ws = c->Fvo;
   c->OmP_count = (i64)c->t2_tiles_n * na * o;
   c->OmP = w.take(c->OmP_count);
   const bool symm = t2_sym_active(c);
@@ -383,7 +390,8 @@ i64 carve_workspace(mpccb_ctx* c, unsigned char* base) {
   mx((DIIS_COLS_GRID + 1) * 7);                                //   "   (column-owned vector)
   c->P_count = p;
   c->P = w.take(p);
-  c->P2_count = splitk_scratch((int)v, (int)o, (int)(L * o), 128, 64);
+  c->P2_count = std::max(splitk_scratch((int)v, (int)o, (int)(L * o), 128, 64),      // F2 (mpccb_dress_rest)
+                         splitk_scratch((int)o, (int)o, (int)(L * na), 128, 64));    // Lov.Yvo (mpccb_doubles_end)
   c->P2 = w.take(c->P2_count);
   c->OmRep = w.take(nov);
   c->OmLoc = w.take(nov);
@@ -435,7 +443,7 @@ int mpccb_create(mpccb_ctx** out, int nocc, int nvir, int naux, int a_begin, int
   if (nocc <= 0 || nvir <= 0 || naux <= 0) return fail(c, "sizes must be positive");
   if (a_begin < 0 || a_end > nvir || a_begin >= a_end) return fail(c, "bad slab [%d,%d) of %d", a_begin, a_end, nvir);
   // explicit limits of the index arithmetic (rows and tile ids are 32-bit, element offsets 64-bit):
-  //   nov <= 2^21            residual-norm scratch of mpccb_finish (8000 blocks of 256) and 32-bit GEMM row indices
+  //   nov <= 2^21            32-bit GEMM row indices, (row, L) products below 2^31 elements per operand view
   //   nocc <= 2^15           umulhi index split of the fused epilogue
   //   nov * ldk, nov * nov   < 2^62 as byte counts (always true under the nov limit; kept for the record)
   //   (na*nvir) block count and (tiles_m * tiles_n) tile count of the eris launch < 2^31 (checked after the geometry)
@@ -512,6 +520,7 @@ int mpccb_set_option(mpccb_ctx* c, const char* name, long long value) {
     return 0;
   }
   if (!strcmp(name, "profile")) { c->profile = value != 0; return 0; }
+  if (!strcmp(name, "xvo_generic")) { c->xvo_generic = value != 0; return 0; }
   if (!strcmp(name, "t2_sym")) {          // 0: compute every (a,b) block (no mirror writes); before bind_workspace
     if (c->ws) return fail(c, "set t2_sym before binding the workspace");
     c->sym_off = value == 0;
@@ -599,6 +608,7 @@ int mpccb_bind_jk_exchange(mpccb_ctx* c, double* jk_local_dev, double* const* pe
   c->JK = jk_local_dev;
   c->w_targets.n = 0;        // full exchange: every rank has every JK row and forms w itself
   c->w = c->w_ws;
+  c->Fvo = c->Fvo_ws;
   if (jk_multicast_dev) {
     c->jk_targets.n = 1;
     c->jk_targets.p[0] = jk_multicast_dev;
@@ -614,8 +624,9 @@ int mpccb_bind_jk_exchange(mpccb_ctx* c, double* jk_local_dev, double* const* pe
 // (s - q) mod P <= P/2, so rank r's JK rows are needed by the P/2 + 1 ranks q = r - d, d = 0..P/2, only: one NVLink
 // store per needed peer instead of a multicast to everybody (8 ranks: 5 x 50 MB leave and 4 x 50 MB enter each GPU
 // instead of 7 x 50 MB entering). The one consumer that wanted every row on every rank, w = Jvo.X (:128, :133), is
-// computed for the own slab inside mpccb_dress and broadcast (nov doubles in total): the symmetric allocation is
-// nov*ldk (JK) + nov (w) doubles. peer_jk_dev: all nranks buffers in rank order; w goes through w_multicast_dev (the
+// computed for the own slab inside mpccb_dress and broadcast, together with the slab's rows of Fvo = w - F2 (so that
+// F2, :133, is a GEMM over the slab's rows only): the symmetric allocation is nov*ldk (JK) + nov (w) + nov (Fvo)
+// doubles. peer_jk_dev: all nranks buffers in rank order; w goes through w_multicast_dev (the
 // multicast address of the allocation) when given, else through the peer pointers.
 int mpccb_bind_jk_subset(mpccb_ctx* c, double* jk_local_dev, double* const* peer_jk_dev, int nranks, int rank,
                          double* w_multicast_dev) {
@@ -624,6 +635,7 @@ int mpccb_bind_jk_subset(mpccb_ctx* c, double* jk_local_dev, double* const* peer
   c->JK = jk_local_dev;
   c->w_off = c->nov * c->ldk;
   c->w = jk_local_dev + c->w_off;
+  c->Fvo = c->w + c->nov;          // Fvo = w - F2 follows w in the symmetric allocation
   c->jk_targets.n = 0;
   for (int d = 0; d <= nranks / 2; ++d) {
     const int q = (rank - d + nranks) % nranks;
@@ -641,6 +653,36 @@ int mpccb_bind_jk_subset(mpccb_ctx* c, double* jk_local_dev, double* const* peer
   return 0;
 }
 
+// Xoo = Lov.t1^T (:120) and Joo = Xoo + Loo (:123) do not depend on the virtual slab: replicated they cost every rank
+// the same GEMM however many ranks there are. Sharded form: rank r computes the rows of its slab of the AUXILIARY
+// index, l in [L r / P, L (r+1) / P), and stores its Xoo rows into every rank's [Xoo | Joo] buffer (2 L o^2 doubles
+// in symmetric memory; only the Xoo half travels, Joo is completed locally) — through the multicast address when
+// given, else one store per peer. mpccb_dress then stops
+// after the exchange has been issued (the slab's Xvo GEMM hides its latency); the caller runs a cross-rank barrier
+// on the stream and calls mpccb_dress_rest. xoo_local_dev == nullptr: back to the replicated form.
+int mpccb_bind_xoo_exchange(mpccb_ctx* c, double* xoo_local_dev, double* const* peer_xoo_dev, int nranks, int rank,
+                            double* xoo_multicast_dev) {
+  if (!c->ws) return fail(c, "bind the workspace first");
+  if (!xoo_local_dev) {
+    c->Xoo = c->Xoo_ws; c->Joo = c->Xoo + (i64)c->L * c->o * c->o;
+    c->xoo_targets.n = 0;
+    return 0;
+  }
+  if (nranks < 2 || nranks > 16 || rank < 0 || rank >= nranks) return fail(c, "bad rank layout");
+  if (c->L < nranks) return fail(c, "fewer auxiliary functions than ranks");
+  c->Xoo = xoo_local_dev; c->Joo = c->Xoo + (i64)c->L * c->o * c->o;
+  c->xoo_l0 = (int)((i64)c->L * rank / nranks);
+  c->xoo_l1 = (int)((i64)c->L * (rank + 1) / nranks);
+  c->xoo_targets.n = 0;
+  if (xoo_multicast_dev) {
+    c->xoo_targets.p[c->xoo_targets.n++] = xoo_multicast_dev;
+  } else {
+    for (int r = 0; r < nranks; ++r)
+      if (peer_xoo_dev[r] != xoo_local_dev) c->xoo_targets.p[c->xoo_targets.n++] = peer_xoo_dev[r];
+  }
+  return 0;
+}
+
 }  // extern "C"
 
 // ===========================================================================
@@ -652,11 +694,25 @@ extern "C" int mpccb_dress_post(mpccb_ctx* c);
 // only (JK/E1K rows, W columns, the W.Joo singles term); Xoo/Joo/X/F2 have no virtual index and are
 // replicated (2 x 2 L o^2 v flop). With several ranks the caller all-gathers the JK rows and then
 // calls mpccb_dress_post; on one rank mpccb_dress runs the post part itself.
+extern "C" int mpccb_dress_rest(mpccb_ctx* c);
+namespace {
+int ensure_side(mpccb_ctx* c) {       // side stream + fork/join events, created on first use
+  if (!c->side) {
+    CUDA_OK(c, cudaStreamCreateWithFlags(&c->side, cudaStreamNonBlocking));
+    CUDA_OK(c, cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+    CUDA_OK(c, cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
+  }
+  return 0;
+}
+}  // namespace
+namespace { int launch_xvo_tma(mpccb_ctx* c); int launch_xtjt_tma(mpccb_ctx* c); }
+
 extern "C" int mpccb_dress(mpccb_ctx* c, const double* t1_dev) {
   CUDA_OK(c, enter_device(c));
   if (!c->ws || !c->Lov) return fail(c, "workspace/integrals not bound");
   const int o = c->o, v = c->v, L = c->L, a0 = c->a_begin, na = c->na;
   const i64 nov = c->nov;
+  const bool xoo_sharded = c->xoo_targets.n > 0;
   {
   StageTimer timer(c, ST_DRESS);
   if (t1_dev != c->t1)
@@ -666,39 +722,59 @@ extern "C" int mpccb_dress(mpccb_ctx* c, const double* t1_dev) {
     k_transpose_batched<<<grid, block, 0, c->stream>>>(c->t1, c->t1T, o, v, o);
     LAUNCH_OK(c, "k_transpose_batched(t1)");
   }
+  {  // :120,:123  Xoo[(L,i)][j] = sum_a Lov[(L,i)][a] t1[j][a];  Joo = Xoo + Loo
+     // replicated, or (Xoo exchange bound) the rows of this rank's L slab, stored into every rank's buffer
+    const int l0 = xoo_sharded ? c->xoo_l0 : 0, l1 = xoo_sharded ? c->xoo_l1 : L;
+    const i64 roff = (i64)l0 * o * o;
+    Operand A = flat_operand(c->Lov + (i64)l0 * o * v, (l1 - l0) * o, v, 1);
+    Operand B = flat_operand(c->t1, o, v, 1);
+    Output C = flat_output(c->Xoo + roff, o, 1);
+    C.base2 = c->Joo + roff; C.aux = c->Loo + roff;
+    if (launch_gemm<CfgN64KK>(c, "Xoo", A, B, C, (l1 - l0) * o, o, v, 1, nullptr)) return 1;
+    if (xoo_sharded) {
+      const i64 n = (i64)(l1 - l0) * o * o;
+      k_bcast_rows<<<(int)std::min<i64>(cdiv(n, 2048), 4 * NSM), 256, 0, c->stream>>>(c->Xoo, c->xoo_targets, roff, n);
+      LAUNCH_OK(c, "k_bcast_rows");
+    }
+  }
   {  // :119  Xov[L][i][a] = sum_b Lvv[L][a][b] t1[i][b]      M=(L, a in slab) N=i K=b
+    const int rc = launch_xvo_tma(c);
+    if (rc < 0) return 1;
+    if (rc == 0) {
     Operand A = flat_operand(c->Lvv + (i64)a0 * v, L * na, v, 1);
     A.rdiv = na; A.r_hi = (i64)v * v; A.r_lo = v;
     Operand B = flat_operand(c->t1, o, v, 1);
     Output C = flat_output(c->Xov + a0, 0, v);
     C.mdiv = na; C.m_hi = (i64)o * v; C.m_lo = 1;
     if (launch_gemm<CfgN64KK>(c, "Xvo", A, B, C, L * na, o, v, 1, nullptr)) return 1;
+    }
   }
-  {  // :120,:123  Xoo[(L,i)][j] = sum_a Lov[(L,i)][a] t1[j][a];  Joo = Xoo + Loo      (replicated)
-    Operand A = flat_operand(c->Lov, L * o, v, 1);
-    Operand B = flat_operand(c->t1, o, v, 1);
-    Output C = flat_output(c->Xoo, o, 1);
-    C.base2 = c->Joo; C.aux = c->Loo;
-    if (launch_gemm<CfgN64KK>(c, "Xoo", A, B, C, L * o, o, v, 1, nullptr)) return 1;
+  }
+  if (xoo_sharded) return 0;        // caller: cross-rank barrier on the stream, then mpccb_dress_rest
+  return mpccb_dress_rest(c);
+}
+
+// Second half of the dressing: everything that reads Xoo / Joo for every auxiliary index.
+extern "C" int mpccb_dress_rest(mpccb_ctx* c) {
+  CUDA_OK(c, enter_device(c));
+  if (!c->ws || !c->Lov) return fail(c, "workspace/integrals not bound");
+  const int o = c->o, v = c->v, L = c->L, a0 = c->a_begin, na = c->na;
+  const i64 nov = c->nov;
+  {
+  StageTimer timer(c, ST_DRESS);
+  if (c->xoo_targets.n > 0) {   // :123 for the L slabs computed elsewhere (only Xoo travels)
+    const i64 n = (i64)L * o * o;
+    k_add_outside<<<4 * NSM, 256, 0, c->stream>>>(c->Xoo, c->Loo, c->Joo, (i64)c->xoo_l0 * o * o,
+                                                  (i64)c->xoo_l1 * o * o, n);
+    LAUNCH_OK(c, "k_add_outside");
   }
   // :121  X[L] = trace_i Xoo[L]
   k_trace<<<cdiv(L, 4), 128, 0, c->stream>>>(c->Xoo, c->X, L, o);
   LAUNCH_OK(c, "k_trace");
-  {  // [XT | JT][(L,i)][a] = sum_k [Xoo | Joo][(L,i)][k] t1[k][a], a in slab    (:124 last term, :127, :146)
-    Operand A = flat_operand(c->Xoo, 2 * L * o, o, 1);
-    Operand B = flat_operand(c->t1T + (i64)a0 * o, na, o, 1);
-    Output C = flat_output(c->XT + a0, v, 1);
-    if (na >= 96) { if (launch_gemm<CfgBig16KK>(c, "XT|JT", A, B, C, 2 * L * o, na, o, 1, nullptr)) return 1; }
-    else          { if (launch_gemm<CfgN64KK>(c, "XT|JT", A, B, C, 2 * L * o, na, o, 1, nullptr)) return 1; }
-  }
   // :133 second half   F2[b][j] = sum_{(L,i)} Lov[(L,i)][b] Xoo[(L,i)][j]      (replicated)
-  // Needs only Xoo and is compute-bound, while k_dress_finalize is bound by HBM (one rank) or by the NVLink stores
-  // of the JK exchange (several ranks): it runs on a side stream next to it.
-  if (!c->side) {
-    CUDA_OK(c, cudaStreamCreateWithFlags(&c->side, cudaStreamNonBlocking));
-    CUDA_OK(c, cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
-    CUDA_OK(c, cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
-  }
+  // Needs only Xoo and is compute-bound, while [XT | JT] is bound by its output and k_dress_finalize by HBM (one rank)
+  // or by the NVLink stores of the JK exchange (several ranks): it runs on a side stream next to them.
+  if (ensure_side(c)) return 1;
   CUDA_OK(c, cudaEventRecord(c->ev_fork, c->stream));
   CUDA_OK(c, cudaStreamWaitEvent(c->side, c->ev_fork, 0));
   {
@@ -706,12 +782,26 @@ extern "C" int mpccb_dress(mpccb_ctx* c, const double* t1_dev) {
     double* main_P = c->P;
     const i64 main_P_count = c->P_count;
     c->stream = c->side; c->P = c->P2; c->P_count = c->P2_count;
-    Operand A = flat_operand(c->Lov, v, 1, v);
+    // subset exchange: only the slab's rows b of F2 (Fvo = w - F2 is broadcast with w below), else all of them
+    const bool slab_only = c->w_targets.n > 0;
+    const int fb0 = slab_only ? a0 : 0, fnb = slab_only ? na : v;
+    Operand A = flat_operand(c->Lov + fb0, fnb, 1, v);
     Operand B = flat_operand(c->Xoo, o, 1, o);
-    const int rc = splitk_gemm<CfgN64RR>(c, "Xoo.Lov", A, B, c->F2, v, o, L * o, 1.0, 0.0);
+    const int rc = splitk_gemm<CfgN64RR>(c, "Xoo.Lov", A, B, c->F2 + (i64)fb0 * o, fnb, o, L * o, 1.0, 0.0);
     c->stream = main_stream; c->P = main_P; c->P_count = main_P_count;
     if (rc) return 1;
     CUDA_OK(c, cudaEventRecord(c->ev_join, c->side));
+  }
+  {  // [XT | JT][(L,i)][a] = sum_k [Xoo | Joo][(L,i)][k] t1[k][a], a in slab    (:124 last term, :127, :146)
+    Operand A = flat_operand(c->Xoo, 2 * L * o, o, 1);
+    Operand B = flat_operand(c->t1T + (i64)a0 * o, na, o, 1);
+    Output C = flat_output(c->XT + a0, v, 1);
+    const int rc = launch_xtjt_tma(c);
+    if (rc < 0) return 1;
+    if (rc == 0) {
+    if (na >= 96) { if (launch_gemm<CfgBig16KK>(c, "XT|JT", A, B, C, 2 * L * o, na, o, 1, nullptr)) return 1; }
+    else          { if (launch_gemm<CfgN64KK>(c, "XT|JT", A, B, C, 2 * L * o, na, o, 1, nullptr)) return 1; }
+    }
   }
   {  // :124, :146 integrand, W = XT - Xov   (columns a of the slab -> JK/E1K rows of the slab)
     dim3 grid(cdiv(na, 32), cdiv(L, 32), o), block(32, 8);
@@ -720,9 +810,12 @@ extern "C" int mpccb_dress(mpccb_ctx* c, const double* t1_dev) {
     k_dress_finalize<<<grid, block, 0, c->stream>>>(c->Xov, c->Lov, c->JT, c->XT, c->X, c->t1, jk, c->E1K,
                                                     c->Wov, L, o, v, c->ldk, a0, a0 + na);
     LAUNCH_OK(c, "k_dress_finalize");
-    if (c->w_targets.n > 0) {   // subset exchange: the slab's rows of w = Jvo.X go to every rank with the integrals
-      k_gemv_rows_bcast<<<cdiv((i64)na * o, 8), 256, 0, c->stream>>>(c->JK, c->X, c->w_targets, c->w_off, a0 * o,
-                                                                     na * o, L, c->ldk);
+    if (c->w_targets.n > 0) {
+      // subset exchange: the slab's rows of w = Jvo.X (:128) and of Fvo = w - F2 (:133) go to every rank with the
+      // integrals — nobody needs the other slabs' JK rows or a replicated F2 GEMM for them
+      CUDA_OK(c, cudaStreamWaitEvent(c->stream, c->ev_join, 0));
+      k_gemv_rows_bcast<<<cdiv((i64)na * o, 8), 256, 0, c->stream>>>(c->JK, c->X, c->F2, c->w_targets, c->w_off,
+                                                                     c->w_off + nov, a0 * o, na * o, L, c->ldk);
       LAUNCH_OK(c, "k_gemv_rows_bcast");
     }
   }
@@ -744,10 +837,9 @@ extern "C" int mpccb_dress_post(mpccb_ctx* c) {
   StageTimer timer(c, ST_DRESS_POST);
   const i64 nov = c->nov;
   // :128 and first half of :133   w[(a,i)] = sum_L J[(a,i)][L] X[L]   (already exchanged in the subset form)
-  if (c->w_targets.n == 0) {
-    k_gemv_rows<<<cdiv(nov, 8), 256, 0, c->stream>>>(c->JK, c->X, c->w, (int)nov, c->L, c->ldk);
-    LAUNCH_OK(c, "k_gemv_rows");
-  }
+  if (c->w_targets.n > 0) return 0;     // subset exchange: w and Fvo arrived with the integrals
+  k_gemv_rows<<<cdiv(nov, 8), 256, 0, c->stream>>>(c->JK, c->X, c->w, (int)nov, c->L, c->ldk);
+  LAUNCH_OK(c, "k_gemv_rows");
   k_make_fvo<<<cdiv(nov, 256), 256, 0, c->stream>>>(c->w, c->F2, c->Fvo, nov);
   LAUNCH_OK(c, "k_make_fvo");
   return 0;
@@ -920,6 +1012,73 @@ int launch_yvo_tma_pieces(mpccb_ctx* c) {
   return 0;
 }
 
+// :119 through the TMA-fed kernel: A = Lvv[L][a in slab][b] as a 3-D map (rows (L,a) of the slab are not equally
+// spaced), B = t1[i][b], stored into Xov[L][i][a] through the index map (lanes along a). Needs 16-byte strides (even
+// nvir) and a slab that tiles 128 rows (na a multiple of 128, or a divisor of it).
+// Returns 1 if launched, 0 if the shape is not eligible (caller uses the generic kernel), -1 on error.
+int launch_xvo_tma(mpccb_ctx* c) {
+  const int o = c->o, v = c->v, L = c->L, na = c->na, a0 = c->a_begin;
+  if (!c->use_tma || c->xvo_generic || (v & 1) || v < 16) return 0;
+  if (!(na % TMA_TM == 0 || TMA_TM % na == 0)) return 0;
+  const int ba = std::min(na, TMA_TM), bl = TMA_TM / ba;
+  CUtensorMap mA, mB;
+  {
+    cuuint64_t dims[3] = {(cuuint64_t)v, (cuuint64_t)na, (cuuint64_t)L};
+    cuuint64_t strides[2] = {(cuuint64_t)v * 8, (cuuint64_t)v * v * 8};
+    cuuint32_t box[3] = {(cuuint32_t)TMA_TK, (cuuint32_t)ba, (cuuint32_t)bl};
+    if (make_tensor_map(c, &mA, c->Lvv + (i64)a0 * v, 3, dims, strides, box)) return -1;
+  }
+  const bool narrow = o <= 64;
+  const int TN = narrow ? TmaCfg<2>::TN : TmaCfg<4>::TN;
+  if (make_map_2d(c, &mB, c->t1, v, o, v, TN)) return -1;
+  TmaGemmParams p;
+  memset(&p, 0, sizeof(p));
+  p.M = L * na; p.N = o;
+  p.tm_eff = TMA_TM; p.tn_eff = TN;
+  p.tiles_m = cdiv(p.M, TMA_TM); p.tiles_n = cdiv(o, TN);
+  p.nk = cdiv(v, TMA_TK);
+  p.a_mode = 2; p.o = na;
+  p.a_bytes = TMA_TM * TMA_TK * 8; p.b_bytes = (uint32_t)(TN * TMA_TK * 8);
+  p.ksplit = 1;
+  p.out = flat_output(c->Xov + a0, 0, v);
+  p.out.mdiv = na; p.out.m_hi = (i64)o * v; p.out.m_lo = 1;
+  T2Params t;
+  memset(&t, 0, sizeof(t));
+  const int rc = narrow ? launch_tma<2, 2>(c, "gemm_tma_kernel<Xvo>", mA, mB, p, t)
+                        : launch_tma<2, 4>(c, "gemm_tma_kernel<Xvo>", mA, mB, p, t);
+  return rc ? -1 : 1;
+}
+
+// [XT | JT] = [Xoo | Joo] . t1 (:124, :127, :146) through the TMA-fed kernel. K = nocc only: the product is bound by
+// its 2 L o na output, which this kernel stores in full rows. Needs even nocc (16-byte strides).
+// Returns 1 if launched, 0 if not eligible, -1 on error.
+int launch_xtjt_tma(mpccb_ctx* c) {
+  const int o = c->o, v = c->v, L = c->L, na = c->na, a0 = c->a_begin;
+  const double* Bp = c->t1T + (i64)a0 * o;
+  if (!c->use_tma || c->xvo_generic || (o & 1) || o < 16 || na < 64) return 0;
+  if (((reinterpret_cast<uintptr_t>(c->Xoo) | reinterpret_cast<uintptr_t>(Bp)) & 15) != 0) return 0;
+  const bool narrow = na <= 64;
+  const int TN = narrow ? TmaCfg<2>::TN : TmaCfg<4>::TN;
+  CUtensorMap mA, mB;
+  if (make_map_2d(c, &mA, c->Xoo, o, (i64)2 * L * o, o, TMA_TM)) return -1;
+  if (make_map_2d(c, &mB, Bp, o, na, o, TN)) return -1;
+  TmaGemmParams p;
+  memset(&p, 0, sizeof(p));
+  p.M = 2 * L * o; p.N = na;
+  p.tm_eff = TMA_TM; p.tn_eff = TN;
+  p.tiles_m = cdiv(p.M, TMA_TM); p.tiles_n = cdiv(na, TN);
+  p.nk = cdiv(o, TMA_TK);
+  p.a_mode = 0;
+  p.a_bytes = TMA_TM * TMA_TK * 8; p.b_bytes = (uint32_t)(TN * TMA_TK * 8);
+  p.ksplit = 1;
+  p.C = c->XT + a0; p.ldc = v;
+  T2Params t;
+  memset(&t, 0, sizeof(t));
+  const int rc = narrow ? launch_tma<0, 2>(c, "gemm_tma_kernel<XT|JT>", mA, mB, p, t)
+                        : launch_tma<0, 4>(c, "gemm_tma_kernel<XT|JT>", mA, mB, p, t);
+  return rc ? -1 : 1;
+}
+
 int launch_eris_t2_unfused(mpccb_ctx* c) {
   const int o = c->o, v = c->v, L = c->L;
   Operand A = flat_operand(c->JK + (i64)c->a_begin * o * c->ldk, c->na * o, c->ldk, 1);
@@ -1045,6 +1204,28 @@ extern "C" int mpccb_doubles_end(mpccb_ctx* c, double* red_dev) {
   }
   StageTimer timer(c, ST_SINGLES_FROM_Y);
   const double* Yslab = c->Y + (i64)c->a_begin * o * L;
+  Operand By;   // Y[(b,i)][L] read as rows i, K = (b in slab, L)
+  By.base = Yslab; By.rows = o; By.rdiv = BIG; By.r_hi = 0; By.r_lo = L;
+  By.kdiv = L; By.k_hi = (i64)o * L; By.k_lo = 1;
+  // :141-142 (Lov.t1 part)  Z[j][i] = sum_{(b,L)} Lvo[L][b][j] Y[(b,i)][L]  — its own output buffer, so it runs on the
+  // side stream next to the two products that accumulate into Om (all three have small outputs and long K: alone,
+  // none of them fills the machine at 8 ranks)
+  if (ensure_side(c)) return 1;
+  CUDA_OK(c, cudaEventRecord(c->ev_fork, c->stream));
+  CUDA_OK(c, cudaStreamWaitEvent(c->side, c->ev_fork, 0));
+  {
+    cudaStream_t main_stream = c->stream;
+    double* main_P = c->P;
+    const i64 main_P_count = c->P_count;
+    c->stream = c->side; c->P = c->P2; c->P_count = c->P2_count;
+    Operand A;
+    A.base = c->Lvo + (i64)c->a_begin * c->jp; A.rows = o; A.rdiv = BIG; A.r_hi = 0; A.r_lo = 1;
+    A.kdiv = L; A.k_hi = c->jp; A.k_lo = (i64)v * c->jp;
+    const int rc = splitk_gemm<CfgN64RK>(c, "Lov.Yvo", A, By, c->Z, o, o, na * L, 1.0, 0.0);
+    c->stream = main_stream; c->P = main_P; c->P_count = main_P_count;
+    if (rc) return 1;
+    CUDA_OK(c, cudaEventRecord(c->ev_join, c->side));
+  }
   {  // :143  Om[a][i] -= sum_{(j,L)} Y[(a,j)][L] Joo[L][j][i]          (a in slab)
     Operand A = flat_operand(Yslab, na, (i64)o * L, 1);
     Operand B;
@@ -1052,20 +1233,14 @@ extern "C" int mpccb_doubles_end(mpccb_ctx* c, double* red_dev) {
     B.kdiv = L; B.k_hi = o; B.k_lo = (i64)o * o;
     if (splitk_gemm<CfgN64KR>(c, "Joo.Yvo", A, B, Om + (i64)c->a_begin * o, na, o, o * L, -1.0, 1.0)) return 1;
   }
-  Operand By;   // Y[(b,i)][L] read as rows i, K = (b in slab, L)
-  By.base = Yslab; By.rows = o; By.rdiv = BIG; By.r_hi = 0; By.r_lo = L;
-  By.kdiv = L; By.k_hi = (i64)o * L; By.k_lo = 1;
   {  // :141-142 (Lvv part)  Om[a][i] += sum_{(b,L)} Lvv[L][b][a] Y[(b,i)][L]     (b in slab, all a)
     Operand A;
     A.base = c->Lvv + (i64)c->a_begin * v; A.rows = v; A.rdiv = BIG; A.r_hi = 0; A.r_lo = 1;
     A.kdiv = L; A.k_hi = v; A.k_lo = (i64)v * v;
     if (splitk_gemm<CfgN64RK>(c, "Lvv.Yvo", A, By, Om, v, o, na * L, 1.0, 1.0)) return 1;
   }
-  {  // :141-142 (Lov.t1 part)  Z[j][i] = sum_{(b,L)} Lvo[L][b][j] Y[(b,i)][L];  Om[a][i] += sum_j t1[j][a] Z[j][i]
-    Operand A;
-    A.base = c->Lvo + (i64)c->a_begin * c->jp; A.rows = o; A.rdiv = BIG; A.r_hi = 0; A.r_lo = 1;
-    A.kdiv = L; A.k_hi = c->jp; A.k_lo = (i64)v * c->jp;
-    if (splitk_gemm<CfgN64RK>(c, "Lov.Yvo", A, By, c->Z, o, o, na * L, 1.0, 0.0)) return 1;
+  {  // Om[a][i] += sum_j t1[j][a] Z[j][i]
+    CUDA_OK(c, cudaStreamWaitEvent(c->stream, c->ev_join, 0));
     k_add_t1T_Z<<<cdiv(nov, 256), 256, 0, c->stream>>>(Om, c->t1, c->Z, o, v);
     LAUNCH_OK(c, "k_add_t1T_Z");
   }
@@ -1087,12 +1262,12 @@ extern "C" int mpccb_finish(mpccb_ctx* c, const double* red_dev, double* t1_new_
   CUDA_OK(c, enter_device(c));
   StageTimer timer(c, ST_FINISH);
   const i64 nov = c->nov;
-  const int nb = cdiv(nov, 256);
-  if (nb > 8000) return fail(c, "nov too large for the residual scratch");
-  k_t1_update<<<nb, 256, 0, c->stream>>>(nullptr, c->w, red_dev, c->t1, c->fvv, c->foo, c->eo, c->ev, t1_new_dev,
-                                         c->OmTot, c->scal, c->o, c->v);
+  const int nb = cdiv(c->v, 32) * c->o;       // residual-norm partials go to the split-K scratch (idle here)
+  if ((i64)nb > c->P_count) return fail(c, "residual scratch too small");
+  k_t1_update<<<dim3(cdiv(c->v, 32), c->o), 256, 0, c->stream>>>(nullptr, c->w, red_dev, c->t1, c->fvv, c->foo, c->eo,
+                                                                 c->ev, t1_new_dev, c->OmTot, c->P, c->o, c->v);
   LAUNCH_OK(c, "k_t1_update");
-  k_final_sums<<<1, 256, 0, c->stream>>>(c->scal, scal_dev, nb, 1);
+  k_final_sums<<<1, 256, 0, c->stream>>>(c->P, scal_dev, nb, 1);
   LAUNCH_OK(c, "k_final_sums");
   CUDA_OK(c, cudaMemcpyAsync(scal_dev + 1, red_dev + nov, sizeof(double), cudaMemcpyDeviceToDevice, c->stream));
   return 0;
@@ -1214,8 +1389,8 @@ extern "C" int mpccb_diis_push(mpccb_ctx* c, const double* t1_new_dev, const dou
                                              first_call, count_t1, c->nov, r0, nrows, chunk, G, c->o, c->jp - c->o, c->P);
     LAUNCH_OK(c, "k_diis_push");
   }
-  if (!first_call) {
-    k_final_sums_strided<<<1, 256, 0, c->stream>>>(c->P, dots_dev, grid, 7, nd);
+  if (!first_call && nd > 0) {
+    k_final_sums_strided<<<nd, 256, 0, c->stream>>>(c->P, dots_dev, grid, 7, nd);
     LAUNCH_OK(c, "k_final_sums_strided");
   }
   return 0;
@@ -1242,8 +1417,8 @@ extern "C" int mpccb_vec_diis_push(mpccb_ctx* c, const double* x_new_dev, long l
   k_vec_diis_push<<<grid, 256, 0, c->stream>>>(x_new_dev, xprev_dev, pv, x_slot_dev, e_slot_dev, ep, nd, slot,
                                                first_call, n, c->P);
   LAUNCH_OK(c, "k_vec_diis_push");
-  if (!first_call) {
-    k_final_sums_strided<<<1, 256, 0, c->stream>>>(c->P, dots_dev, grid, 7, nd);
+  if (!first_call && nd > 0) {
+    k_final_sums_strided<<<nd, 256, 0, c->stream>>>(c->P, dots_dev, grid, 7, nd);
     LAUNCH_OK(c, "k_final_sums_strided");
   }
   return 0;

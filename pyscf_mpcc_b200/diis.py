@@ -30,11 +30,31 @@ import torch
 from . import _cabi
 
 
+_SYEVR_WORK = {}
+
+
+def _eigh(h: np.ndarray):
+    """``scipy.linalg.eigh(h)`` without its Python wrapper: the same LAPACK routine (dsyevr, lower triangle, all
+    eigenpairs, workspace sizes from dsyevr_lwork) called directly — bit-identical eigenpairs (checked in
+    tests/test_host_logic.py) in half the time; this solve sits on the critical path of every iteration."""
+    n = h.shape[0]
+    if h.dtype != np.float64:
+        return scipy.linalg.eigh(h)
+    work = _SYEVR_WORK.get(n)
+    if work is None:
+        r = scipy.linalg.lapack.dsyevr_lwork(n, lower=1)
+        work = _SYEVR_WORK[n] = (int(r[0]), int(r[1]))
+    w, v, _, _, info = scipy.linalg.lapack.dsyevr(h, lwork=work[0], liwork=work[1], lower=1, compute_v=1)
+    if info != 0:
+        return scipy.linalg.eigh(h)
+    return w, v
+
+
 def solve_diis_system(h: np.ndarray) -> np.ndarray:
     """c with ``h c = (1, 0, ..)``; pseudo-inverse if |eigenvalue| < 1e-14 (diis.py:251-265)."""
     g = np.zeros(h.shape[0], h.dtype)
     g[0] = 1
-    w, v = scipy.linalg.eigh(h)
+    w, v = _eigh(h)
     if np.any(abs(w) < 1e-14):
         idx = abs(w) > 1e-14
         return np.dot(v[:, idx] * (1. / w[idx]), np.dot(v[:, idx].T.conj(), g))
@@ -92,6 +112,7 @@ class DIIS:
         :class:`AmplitudeVector` (``diis.py:202-243``)."""
         ll = amps.solver
         ctx = ll._ctx
+        self.synced = False          # did this call wait for the solver's stream (after the push)?
         n_local = ll._vec_len_local
         dev = ll.device
         if len(self._bookkeep) >= self.space:
@@ -127,7 +148,7 @@ class DIIS:
         # the column-owned push kernel (several ranks) walks scattered block fragments and is bound by its address
         # arithmetic, not by HBM: six more vector streams cost it more than the combine pass saves (measured at two
         # ranks: 8.3 vs 5.1 ms per update), so only the row-owned form recomputes xprev on the fly
-        implicit = not getattr(ll, "_diis_columns", False)
+        implicit = ll._diis_implicit
         if self._prev is not None and implicit:
             coeffs, slots = self._prev
             n_prev = len(slots)
@@ -142,6 +163,7 @@ class DIIS:
             torch.distributed.all_reduce(dots, group=ll.group)
         ll._dots_host.copy_(dots, non_blocking=True)
         ll._sync()
+        self.synced = True
         d = ll._dots_host.numpy()
 
         if nd < self.min_space:
@@ -161,21 +183,25 @@ class DIIS:
         self._prev_stored = False
         self.generation += 1
         if not implicit:
-            xp = self._xprev                     # materialises the combination into the explicit buffer
+            # explicit xprev, formed at once. (Forming its t2 part on a side stream next to the following T1 dressing
+            # was tried: a streaming kernel that fills every SM does not share them with the dressing's GEMMs, whose
+            # CTAs take the whole register file — the two simply ran one after the other.)
+            xp = self._xprev
             return AmplitudeVector(ll, vec=xp, t1_dev=xp[:ll.nov], owner=self, serial=self.generation)
         if self._t1_next is None:
             self._t1_next = torch.empty(ll.nov, dtype=torch.float64, device=dev)
         self._combine_into(self._t1_next, ll.nov)
         return AmplitudeVector(ll, vec=None, t1_dev=self._t1_next, owner=self, serial=self.generation, lazy=True)
 
-    def _combine_into(self, out, n):
+    def _combine_into(self, out, n, offset=0):
+        """out[offset : offset + n] = sum_k c_k x_k[offset : offset + n]"""
         coeffs, slots = self._prev
         x_list = (ctypes.c_void_p * 6)()
         coeff = (ctypes.c_double * 6)()
         for k, sl in enumerate(slots):
-            x_list[k] = self._x[sl].data_ptr()
+            x_list[k] = self._x[sl].data_ptr() + 8 * offset
             coeff[k] = coeffs[k]
-        self._solver._ctx.call("mpccb_diis_combine", x_list, coeff, len(slots), out.data_ptr(), n)
+        self._solver._ctx.call("mpccb_diis_combine", x_list, coeff, len(slots), out.data_ptr() + 8 * offset, n)
 
     @property
     def _xprev(self):

@@ -215,6 +215,11 @@ class MPCC_LL:
         if diis_layout not in ("columns", "rows"):
             raise ValueError(f"diis_layout={diis_layout!r}")
         self._diis_columns = diis_layout == "columns"
+        # xprev folded into the push (row-owned kernel only) or stored and combined next to the next dressing
+        imp = os.environ.get("MPCC_DIIS_IMPLICIT", "auto")
+        if imp not in ("auto", "0", "1"):
+            raise ValueError(f"MPCC_DIIS_IMPLICIT={imp!r}")
+        self._diis_implicit = (not self._diis_columns) if imp == "auto" else (imp == "1" and not self._diis_columns)
         self._diis_prefix = None
         if self._diis_columns:
             prefix = sharding.column_owned_prefix(o, v, self._a_begin, self._a_end)
@@ -222,6 +227,8 @@ class MPCC_LL:
             self._diis_prefix = torch.from_numpy(prefix).to(self.device)
         self._ctx = _cabi.Context(o, v, L, self._a_begin, self._a_end, self.device.index)
         self._ctx.call("mpccb_set_option", b"tma", int(bool(use_tma)))
+        if os.environ.get("MPCC_XVO_GENERIC", "0") != "0":      # A/B switch: Xvo GEMM (:119) on the generic kernel
+            self._ctx.call("mpccb_set_option", b"xvo_generic", 1)
         if self._diis_columns:
             self._ctx.call("mpccb_bind_diis_columns", self._diis_prefix.data_ptr())
         if t2_wide_tiles is None and os.environ.get("MPCC_T2_WIDE_TILES"):
@@ -243,6 +250,7 @@ class MPCC_LL:
         ws_ptr = (self._ws.data_ptr() + 255) // 256 * 256
         self._ctx.call("mpccb_bind_workspace", ws_ptr, self._ctx.workspace_bytes())
         self._jk_mode = "local"
+        self._xoo_hdl, self._xoo_mode = None, "replicated"
         if self.world_size > 1:
             self._setup_jk_exchange(jk_exchange or os.environ.get("MPCC_JK_EXCHANGE", "auto"))
         self._t2_peers = False
@@ -422,7 +430,7 @@ class MPCC_LL:
         if mode != "nccl" and self._symm_agreed():
             try:
                 import torch.distributed._symmetric_memory as symm
-                buf = symm.empty(count + self.nov, dtype=torch.float64, device=self.device)   # JK rows + w = Jvo.X
+                buf = symm.empty(count + 2 * self.nov, dtype=torch.float64, device=self.device)   # JK rows + w + Fvo
                 hdl = symm.rendezvous(buf, self.group)
                 ok = 1
             except Exception as e:                      # no peer mapping on this system: use NCCL
@@ -437,12 +445,14 @@ class MPCC_LL:
             mc = int(getattr(hdl, "multicast_ptr", 0) or 0)
             self._jk_buf, self._jk_hdl, self._jk_mc = buf, hdl, mc
             # "subset": one store per rank that needs the slab (world/2 + 1 of them under the mirror scheme) instead of
-            # a multicast to everybody; pays from 4 ranks on and needs the cross-rank mirror (peer-mapped t2)
-            want_subset = mode == "subset" or (mode == "auto" and self.world_size >= 4)
+            # a multicast to everybody, and w / Fvo broadcast with it (F2 becomes a GEMM over the slab's rows); needs
+            # the cross-rank mirror (peer-mapped t2). Measured faster than the multicast form from 2 ranks on.
+            want_subset = mode in ("subset", "auto")
             if want_subset and self._t2_sym:
                 self._bind_jk(subset=True)
             else:
                 self._bind_jk(subset=False, multicast=mode in ("auto", "multicast", "subset"))
+            self._setup_xoo_exchange()
             return
         off = ptr - self._ws.data_ptr()
         self._jk_view = self._ws[off:off + count * 8].view(torch.float64)
@@ -451,6 +461,32 @@ class MPCC_LL:
             self._jk_rows.append((b0 * o * ldk, b1 * o * ldk))
         self._equal_slabs = len({hi - lo for lo, hi in self._jk_rows}) == 1
         self._jk_mode = "nccl"
+
+    def _setup_xoo_exchange(self):
+        """Xoo / Joo (:120, :123) sharded over the auxiliary index and exchanged through symmetric memory
+        (include/mpcc_b200.h, mpccb_bind_xoo_exchange) instead of the same GEMM on every rank. MPCC_XOO_EXCHANGE=0
+        keeps the replicated form. All ranks agree on the outcome."""
+        want = os.environ.get("MPCC_XOO_EXCHANGE", "1") != "0" and self.naux >= self.world_size
+        ok, hdl, buf = 0, None, None
+        if want:
+            try:
+                import torch.distributed._symmetric_memory as symm
+                buf = symm.empty(2 * self.naux * self.nocc * self.nocc, dtype=torch.float64, device=self.device)
+                hdl = symm.rendezvous(buf, self.group)
+                ok = 1
+            except Exception as e:
+                self._xoo_exchange_error = repr(e)
+        flag = torch.tensor([ok], device=self.device)
+        torch.distributed.all_reduce(flag, op=torch.distributed.ReduceOp.MIN, group=self.group)
+        if int(flag.item()) != 1:
+            return
+        peers = (ctypes.c_void_p * self.world_size)(*[int(p) for p in hdl.buffer_ptrs])
+        mc = int(getattr(hdl, "multicast_ptr", 0) or 0)
+        use_mc = mc != 0 and os.environ.get("MPCC_XOO_MULTICAST", "1") != "0"
+        self._ctx.call("mpccb_bind_xoo_exchange", buf.data_ptr(), peers, self.world_size, self.rank,
+                       mc if use_mc else None)
+        self._xoo_buf, self._xoo_hdl = buf, hdl
+        self._xoo_mode = "multicast" if use_mc else "p2p"
 
     def _bind_jk(self, subset, multicast=True):
         hdl, buf, mc = self._jk_hdl, self._jk_buf, self._jk_mc
@@ -532,6 +568,9 @@ class MPCC_LL:
         ctx.call("mpccb_dress", t1_dev.data_ptr())
         if self.world_size == 1:
             return
+        if self._xoo_hdl is not None:
+            self._xoo_hdl.barrier(channel=0)             # every rank's L slab of Xoo / Joo has landed everywhere
+            ctx.call("mpccb_dress_rest")
         if self._jk_mode in ("multicast", "p2p", "subset"):
             self._jk_hdl.barrier(channel=0)              # every rank's rows have landed in every buffer
         else:
@@ -590,10 +629,14 @@ class MPCC_LL:
         ctx.call("mpccb_finish", self._red.data_ptr(), self._t1n_dev.data_ptr(), self._scal_dev.data_ptr())
         self._scal_host.copy_(self._scal_dev, non_blocking=True)
         if adiis is not None:
+            # update() waits for the DIIS dot products, which follow the two scalars on the stream: both are on the
+            # host when it returns, and the kernels it launches afterwards need not be waited for
             nxt = adiis.update(AmplitudeVector(self, vec=None, t1_dev=self._t1n_dev)).t1_dev
+            if not getattr(adiis, "synced", False):
+                self._sync()
         else:
             nxt = self._t1n_dev
-        self._sync()
+            self._sync()
         return float(np.sqrt(self._scal_host[0].item())), float(self._scal_host[1].item()), nxt
 
     def energy(self, t1=None):

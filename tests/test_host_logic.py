@@ -135,12 +135,13 @@ class _FakeTensor:
         return self
 
 
-def test_device_diis_bookkeeping_against_reference_fixture(monkeypatch):
+@pytest.mark.parametrize("implicit", [True, False])
+def test_device_diis_bookkeeping_against_reference_fixture(monkeypatch, implicit):
     g = np.load(os.path.join(GOLDEN, "diis_kat.npz"))
     n = g["inputs"].shape[1]
     ctx = _FakeCtx()
     ll = types.SimpleNamespace(_ctx=ctx, _vec_len_local=n, device="cpu", nov=n, _count_t1=True, world_size=1,
-                               _sync=lambda: None)
+                               _sync=lambda: None, _diis_implicit=implicit)
     ll._dots_dev = _FakeTensor(ctx, np.zeros(7))
     ll._dots_host = _FakeTensor(ctx, np.zeros(7))
     d = DIIS()
@@ -270,3 +271,22 @@ def test_staged_reference_files_match_the_reference_tree():
         with open(os.path.join(make_ref.SOURCE_ROOT, rel), "rb") as f:
             assert hashlib.sha256(f.read()).hexdigest() == digest
     assert make_ref.staged()
+
+
+def test_direct_lapack_eigh_is_bit_identical_to_scipy_eigh():
+    """The DIIS solve calls dsyevr directly (pyscf_mpcc_b200.diis._eigh); the reference goes through
+    scipy.linalg.eigh (pyscf/lib/diis.py:251-265). Same routine, same arguments: identical bits, including the
+    nearly singular B matrices of a converged solve where the |w| < 1e-14 filter decides the branch."""
+    import scipy.linalg
+    from pyscf_mpcc_b200.diis import _eigh
+    rng = np.random.default_rng(1)
+    for n in range(2, 8):
+        for decay in (1, 3, 5, 8, 10):
+            for _ in range(10):
+                e = rng.standard_normal((n - 1, 50)) * np.logspace(0, -decay, n - 1)[:, None]
+                h = np.zeros((n, n))
+                h[0, 1:] = h[1:, 0] = 1
+                h[1:, 1:] = e @ e.T
+                w0, v0 = scipy.linalg.eigh(h)
+                w1, v1 = _eigh(h.copy())
+                assert np.array_equal(w0, w1) and np.array_equal(v0, v1)
