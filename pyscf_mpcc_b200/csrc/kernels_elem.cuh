@@ -653,6 +653,23 @@ k_final_sums_strided(const double* __restrict__ partial, double* __restrict__ ou
 }  // namespace mpccb
 
 namespace mpccb {
+// Tk[(a,i)][(b,j)] = T[a][b][i][j], both with j pitch jp (pad column copied as it is: zero): the slab with K = (b,j)
+// contiguous per row, for the flat-K Yvo GEMM. grid (v, na): one CTA per (a,b) block, read contiguously, written as
+// o runs of jp doubles.
+__global__ void __launch_bounds__(256)
+k_t2_flatten_k(const double* __restrict__ T, double* __restrict__ Tk, int o, int jp, int v) {
+  const int b = blockIdx.x, a = blockIdx.y;
+  const double* src = T + ((i64)a * v + b) * o * jp;
+  double* dst = Tk + (i64)a * o * v * jp + (i64)b * jp;
+  const int n = o * jp;
+  for (int t = threadIdx.x; t < n; t += blockDim.x) {
+    const int i = t / jp, j = t - i * jp;
+    dst[(i64)i * v * jp + j] = src[t];
+  }
+}
+}  // namespace mpccb
+
+namespace mpccb {
 // In-place t2 build for the unfused path (reference dfrmpcc_lowlevel.py:137,:139): the GEMM wrote
 // e[(a,i),(b,j)] into T[a][b][i][j]; one block per (a,b) turns its o x o block into
 //   t2[i][j] = (2 e[i][j] - e[j][i]) / (eo[i] + eo[j] - ev[a] - ev[b])

@@ -61,6 +61,8 @@ struct mpccb_ctx {
   double *Lvo, *t1, *t1T, *t1n, *Xov, *Xoo, *Joo, *X, *XT, *JT, *JK, *E1K, *Wov, *w, *F2, *Fvo, *OmP, *Y,
       *P, *OmRep, *OmLoc, *OmTot, *Z, *scal, *red, *YP;
   int yvo_split, yvo_split_force;
+  int yvo_flat, yvo_flat_force;  // flat-K form of the Yvo GEMM (below); force: 0 automatic, 1 on, -1 off
+  double* Tk;                    // t2 slab re-laid as [(a,i)][(b,j)] for it
   JkTargets jk_targets;      // n == 0: plain local JK
   JkTargets w_targets;       // n > 0: the slab's rows of w = Jvo.X are broadcast by mpccb_dress (subset JK exchange)
   i64 w_off;                 // offset of w inside the symmetric JK allocation (doubles)
@@ -328,14 +330,31 @@ int build_tile_list(mpccb_ctx* c) {
 // tile (nocc = 64, 32, 22, 42, 110..128, ...). Other even nocc: power-of-two pieces (launch_yvo_tma_pieces).
 bool yvo_single_launch(int o) { return o <= 128 && (128 / o) * o >= 109; }
 
+// Flat-K form of the Yvo GEMM. K runs over (b, j) and the 4-D tensor map over T[a][b][i][j] takes 16 columns j of one b
+// per step, so an occupied count that is not a multiple of 16 pays ceil(o/16)*16 columns per b: 32 for nocc = 21
+// (34 % of the DMMA work wasted), 48 for 42. (Packing 16 / jw different b times jw columns into one step would fix it
+// at the source, but a TMA box narrower than its swizzle span is padded to the span in shared memory, and without the
+// 128-byte swizzle the fragment loads conflict 4-way.) Instead the slab is copied once per iteration into
+// Tk[(a,i)][(b,j)] — j pitch jp, pad columns zero — where K is a plain contiguous index of length v*jp: two more
+// HBM passes over t2 (< 4 % of the GEMM's time) against the wasted columns. Used when it saves more than 10 % of the
+// K steps and the copy fits 24 GB.
+bool yvo_flat_wanted(const mpccb_ctx* c) {
+  if (!c->use_tma || c->yvo_flat_force < 0) return false;
+  const double steps16 = (double)c->v * cdiv(c->o, TMA_TK);
+  const double steps_flat = (double)cdiv((i64)c->v * c->jp, TMA_TK);
+  const double bytes = 8.0 * c->na * c->o * (double)c->v * c->jp;
+  if (c->yvo_flat_force > 0) return true;
+  return steps_flat < 0.9 * steps16 && bytes <= 24e9;
+}
+
 // Split-K factor of the TMA Yvo GEMM: with few output tiles per SM (a-slab sharding) the last wave is
 // mostly idle; s K-slices turn T tiles into T*s shorter CTAs. Pick s <= 8 minimising ceil(T*s/148)/s.
 int choose_yvo_splits(const mpccb_ctx* c) {
   const int o = c->o;
-  if (!c->use_tma || !yvo_single_launch(o)) return 1;      // split-K only on the single-launch path (launch_yvo)
+  if (!c->use_tma || !(c->yvo_flat || yvo_single_launch(o))) return 1;      // split-K only on the one-launch paths
   const int n_a = 128 / o;
-  const i64 T = (i64)cdiv(c->na, n_a) * cdiv(c->L, 128);
-  const i64 nk = (i64)c->v * cdiv(o, TMA_TK);
+  const i64 T = (c->yvo_flat ? (i64)cdiv(c->na * o, TMA_TM) : (i64)cdiv(c->na, n_a)) * cdiv(c->L, 128);
+  const i64 nk = c->yvo_flat ? (i64)cdiv((i64)c->v * c->jp, TMA_TK) : (i64)c->v * cdiv(o, TMA_TK);
   if (c->yvo_split_force > 0) return (int)std::min<i64>(c->yvo_split_force, nk);
   double best = (double)cdiv(T, NSM);
   int best_s = 1;
@@ -377,6 +396,8 @@ i64 carve_workspace(mpccb_ctx* c, unsigned char* base) {
   c->tiles_dev = reinterpret_cast<int2*>(w.take(c->tiles_cap));          // int2 = one double each
   c->sym.OmPm = w.take(symm ? (i64)c->t2_tiles_m * nov : 0);
   c->Y = w.take(nov * L);
+  c->yvo_flat = yvo_flat_wanted(c) ? 1 : 0;
+  c->Tk = w.take(c->yvo_flat ? na * o * v * c->jp : 0);
   c->yvo_split = choose_yvo_splits(c);
   c->YP = w.take(c->yvo_split > 1 ? (i64)c->yvo_split * na * o * L : 0);
   i64 p = 0;
@@ -521,6 +542,11 @@ int mpccb_set_option(mpccb_ctx* c, const char* name, long long value) {
   }
   if (!strcmp(name, "profile")) { c->profile = value != 0; return 0; }
   if (!strcmp(name, "xvo_generic")) { c->xvo_generic = value != 0; return 0; }
+  if (!strcmp(name, "yvo_flat")) {        // 1 / -1: force the flat-K Yvo form on / off (0 = automatic; before bind_workspace)
+    if (c->ws) return fail(c, "set yvo_flat before binding the workspace");
+    c->yvo_flat_force = (int)value;
+    return 0;
+  }
   if (!strcmp(name, "t2_sym")) {          // 0: compute every (a,b) block (no mirror writes); before bind_workspace
     if (c->ws) return fail(c, "set t2_sym before binding the workspace");
     c->sym_off = value == 0;
@@ -1139,8 +1165,45 @@ int launch_eris_t2(mpccb_ctx* c) {
   return 0;
 }
 
+// Yvo with K flattened (yvo_flat_wanted): copy the slab into Tk[(a,i)][(b,j)], then a plain K-major product
+int launch_yvo_flat(mpccb_ctx* c) {
+  constexpr int TN = TmaCfg<4>::TN;
+  const int o = c->o, v = c->v, L = c->L, jp = c->jp, na = c->na;
+  const i64 K = (i64)v * jp;
+  k_t2_flatten_k<<<dim3(v, na), 256, 0, c->stream>>>(c->T, c->Tk, o, jp, v);
+  LAUNCH_OK(c, "k_t2_flatten_k");
+  CUtensorMap mA, mB;
+  if (make_map_2d(c, &mA, c->Tk, K, (i64)na * o, K, TMA_TM)) return 1;
+  if (make_map_2d(c, &mB, c->Lvo, K, L, K, TN)) return 1;
+  TmaGemmParams p;
+  memset(&p, 0, sizeof(p));
+  p.M = na * o; p.N = L;
+  p.tm_eff = TMA_TM; p.tn_eff = TN;
+  p.tiles_m = cdiv(p.M, TMA_TM); p.tiles_n = cdiv(L, TN);
+  p.nk = (int)cdiv(K, TMA_TK);
+  p.a_mode = 0;
+  p.a_bytes = TMA_TM * TMA_TK * 8; p.b_bytes = TN * TMA_TK * 8;
+  double* Yslab = c->Y + (i64)c->a_begin * o * L;
+  p.C = Yslab; p.ldc = L;
+  p.ksplit = 1;
+  const int splits = c->yvo_split;
+  if (splits > 1) {
+    p.ksplit = splits; p.nk_split = cdiv(p.nk, splits);
+    p.ksplit = cdiv(p.nk, p.nk_split);
+    p.C = c->YP; p.split_stride = (i64)na * o * L;
+  }
+  T2Params t;
+  memset(&t, 0, sizeof(t));
+  p.tiles_total = p.tiles_m * p.tiles_n * p.ksplit;
+  if (launch_tma<0, 4>(c, "gemm_tma_kernel<yvo flat>", mA, mB, p, t)) return 1;
+  if (p.ksplit > 1)
+    return reduce_splits(c, Yslab, c->YP, p.ksplit, (i64)na * o * L, p.split_stride, 1.0, 0.0);
+  return 0;
+}
+
 int launch_yvo(mpccb_ctx* c) {
   const int o = c->o, v = c->v, L = c->L;
+  if (c->yvo_flat && c->Tk) return launch_yvo_flat(c);
   // TMA strides must be multiples of 16 bytes: the j pitch of T and Lvo is nocc rounded up to even
   if (c->use_tma && yvo_single_launch(o)) return launch_yvo_tma(c);
   if (c->use_tma) return launch_yvo_tma_pieces(c);
