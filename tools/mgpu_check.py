@@ -3,7 +3,7 @@ reproduce the reference-generated fixtures of tests/golden — iteration counts,
 final t1 and the (all-gathered) final t2 — and, at the full target shape, the single-rank iteration.
 
     python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 \
-        tools/mgpu_check.py [--full]
+        tools/mgpu_check.py [--full] [--shape=o,v,L]
 """
 import glob
 import os
@@ -26,7 +26,8 @@ def main():
     from pyscf_mpcc_b200.synthetic import SyntheticMF
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     bad = 0
-    for path in sorted(glob.glob(os.path.join(root, "tests", "golden", "mpcc_*.npz"))):
+    fixtures = [] if "--only-shape" in sys.argv else sorted(glob.glob(os.path.join(root, "tests", "golden", "mpcc_*.npz")))
+    for path in fixtures:
         g = np.load(path)
         o, v, L = (int(x) for x in g["shape"])
         if v < world:
@@ -65,6 +66,11 @@ def main():
             del ll
     if "--full" in sys.argv:
         bad += full_shape(rank, world, dev)
+    for arg in sys.argv:
+        # --shape=o,v,L : the same sharded-vs-single comparison at another shape, DIIS off (13 history vectors of a
+        # large shape do not fit one GPU), two iterations
+        if arg.startswith("--shape="):
+            bad += full_shape(rank, world, dev, tuple(int(x) for x in arg.split("=")[1].split(",")), diis=False, its=2)
     dist.destroy_process_group()
     if bad:
         sys.exit(1)
@@ -90,16 +96,17 @@ def uneven_bounds(v, world):
     return out
 
 
-def full_shape(rank, world, dev):
-    """(64,512,1536): sharded vs single-rank (group of one) on the same device inputs."""
+def full_shape(rank, world, dev, shape=(64, 512, 1536), diis=True, its=4):
+    """(64,512,1536) by default: sharded vs single-rank (group of one) on the same device inputs."""
     from pyscf_mpcc_b200.lowlevel import MPCC_LL
     from pyscf_mpcc_b200.synthetic import device_blocks, default_scale
-    o, v, L = 64, 512, 1536
+    o, v, L = shape
     Loo, Lov, Lvv, eo, ev = device_blocks(o, v, L, seed=0, scale=default_scale(o, v), device=dev)
     blocks = (Loo, Lov, Lvv, torch.diag(eo), torch.diag(ev), torch.cat([eo, ev]))
     ll = MPCC_LL(blocks=blocks, device=dev)
     ll.verbose_print = False
-    ll.max_its = 4
+    ll.max_its = its
+    ll.diis = diis
     ll.kernel()
     hist_sharded = np.array(ll.history)
     t1_sharded = ll.t1.copy()
@@ -109,7 +116,8 @@ def full_shape(rank, world, dev):
     groups = [dist.new_group([r]) for r in range(world)]
     ll1 = MPCC_LL(blocks=blocks, device=dev, group=groups[rank])
     ll1.verbose_print = False
-    ll1.max_its = 4
+    ll1.max_its = its
+    ll1.diis = diis
     ll1.kernel()
     h1 = np.array(ll1.history)
     ok = (np.abs(h1[:, 1] - hist_sharded[:, 1]).max() <= E_TOL and np.allclose(h1[:, 2], hist_sharded[:, 2], rtol=1e-6)
@@ -117,7 +125,7 @@ def full_shape(rank, world, dev):
     flag = torch.tensor([0 if ok else 1], device=dev)
     dist.all_reduce(flag)
     if rank == 0:
-        print(f"full shape world={world}: sharded vs single  dE diff {np.abs(h1[:, 1] - hist_sharded[:, 1]).max():.2e} "
+        print(f"full shape {shape} world={world}: sharded vs single  dE diff {np.abs(h1[:, 1] - hist_sharded[:, 1]).max():.2e} "
               f"t1 diff {np.abs(ll1.t1 - t1_sharded).max():.2e} {'OK' if flag.item() == 0 else 'MISMATCH'}", flush=True)
     return int(flag.item())
 
