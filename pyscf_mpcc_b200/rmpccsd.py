@@ -90,6 +90,9 @@ class DFERIs:
         self.ovvo = eng.transpose(self.ovov, (0, 1, 3, 2))
         self.ovvv = E("Lia,Lbc->iabc", Lov, Lvv)
         self.vvvv = None
+        # the integrals do not change during a solve: the engine keeps the permuted copies it needs of them
+        for t in (Loo, Lov, Lvv, self.oooo, self.ovoo, self.ooov, self.oovv, self.ovov, self.ovvo, self.ovvv):
+            t.const = True
 
     @classmethod
     def from_numpy(cls, eng, Loo, Lov, Lvv, fock):

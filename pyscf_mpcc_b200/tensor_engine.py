@@ -22,12 +22,14 @@ import numpy as np
 
 
 class DTensor:
-    """Shape + flat device buffer (a torch float64 CUDA tensor for the product backend)."""
-    __slots__ = ("buf", "shape")
+    """Shape + flat device buffer (a torch float64 CUDA tensor for the product backend). ``const`` marks tensors
+    that do not change between calls (integral blocks): the engine keeps their permuted copies."""
+    __slots__ = ("buf", "shape", "const")
 
-    def __init__(self, buf, shape):
+    def __init__(self, buf, shape, const=False):
         self.buf = buf
         self.shape = tuple(int(s) for s in shape)
+        self.const = bool(const)
 
     @property
     def size(self):
@@ -199,6 +201,11 @@ class Engine:
         self.profile = None          # {spec: [ms, flops, calls]} when switched on (tools/cc_bench.py); synchronises per call
         self.fuse_output = True      # store products through index maps instead of permute passes (tests switch it off)
         self.fused_outputs = 0
+        self.plan_layouts = True     # choose operand roles / index orders that avoid permuted copies (tests switch it off)
+        # permuted copies of const tensors (integral blocks), made once: {(id(tensor), perm): (tensor, buffer)}
+        self._perm_cache = {}
+        self.perm_cache_bytes = 0
+        self.perm_cache_limit = 16 << 30
 
     # -- construction ------------------------------------------------------------------------------
     def tensor(self, array):
@@ -268,12 +275,15 @@ class Engine:
             raise NotImplementedError(f"einsum {spec}: batch index (present in both operands and the output)")
         if any((ch not in ib and ch not in io) for ch in ia) or any((ch not in ia and ch not in io) for ch in ib):
             raise NotImplementedError(f"einsum {spec}: index summed inside a single operand")
-        if io and io[-1] in ia and io[-1] not in ib and self.fuse_output:
-            # the unit-stride index of the result should be a COLUMN index of the product (lanes of the store epilogues
-            # run along n): C = A.B^T -> C^T = B.A^T, same flops
-            a, b, ia, ib = b, a, ib, ia
-        mi = [ch for ch in io if ch in ia]
-        ni = [ch for ch in io if ch in ib]
+        if self.plan_layouts and self.fuse_output:
+            a, b, ia, ib, mi, ni, ksum = self._plan(a, b, ia, ib, io, ksum, ext)
+        else:
+            if io and io[-1] in ia and io[-1] not in ib and self.fuse_output:
+                # the unit-stride index of the result should be a COLUMN index of the product (lanes of the store
+                # epilogues run along n): C = A.B^T -> C^T = B.A^T, same flops
+                a, b, ia, ib = b, a, ib, ia
+            mi = [ch for ch in io if ch in ia]
+            ni = [ch for ch in io if ch in ib]
         if len(mi) + len(ni) != len(io):
             raise ValueError(f"einsum {spec}: output index not found in the operands")
         M, N, K = _prod(ext[c] for c in mi), _prod(ext[c] for c in ni), _prod(ext[c] for c in ksum)
@@ -353,9 +363,72 @@ class Engine:
         perm = tuple(idx.index(ch) for ch in order)
         if perm == tuple(range(len(idx))):
             return t.buf
+        if t.const:
+            hit = self._perm_cache.get((id(t), perm))
+            if hit is not None:
+                return hit[1]
         tmp = self.be.empty(t.size)
         self.be.permute_axpby(t.buf, tmp, t.shape, perm, 1.0, 0.0)
+        if t.const and self.perm_cache_bytes + 8 * t.size <= self.perm_cache_limit:
+            self._perm_cache[(id(t), perm)] = (t, tmp)        # holds `t`, so its id stays unique
+            self.perm_cache_bytes += 8 * t.size
         return tmp
+
+    def _plan(self, a, b, ia, ib, io, ksum, ext):
+        """Operand roles and index orders of C[m,n] = sum_k A[m,k] B[n,k] that move the fewest bytes outside the GEMM.
+        Any order of the row indices, of the column indices and of the contraction indices gives the same numbers up
+        to the order of the K summation; what differs is which operands need a permuted copy first and whether the
+        result can be stored in place. Candidates: either operand as A; K in the order of either operand; rows /
+        columns in the order of the result or of their operand. Cost = bytes of the permuted copies (const tensors:
+        made once, cached) + bytes of a separate result pass when the store cannot be fused, or is fused but scattered
+        (neither the last row index nor the last column index is the result's unit-stride index)."""
+        ostride, acc = {}, 1
+        for ch in reversed(io):
+            ostride[ch] = acc
+            acc *= ext[ch]
+        csize = 8.0 * acc
+
+        def operand_cost(t, idx, order):
+            if list(idx) == list(order):
+                return 0.0
+            if t.const:
+                if (id(t), tuple(idx.index(ch) for ch in order)) in self._perm_cache:
+                    return 0.0
+                return 0.25 * 8.0 * t.size          # made once, amortised over the iterations
+            return 2.0 * 8.0 * t.size
+
+        best = None
+        for swap in (False, True):
+            xa, xb, xia, xib = (b, a, ib, ia) if swap else (a, b, ia, ib)
+            fa = [ch for ch in io if ch in xia]
+            fb = [ch for ch in io if ch in xib]
+            m_orders = [fa] + ([[ch for ch in xia if ch in fa]] if [ch for ch in xia if ch in fa] != fa else [])
+            n_orders = [fb] + ([[ch for ch in xib if ch in fb]] if [ch for ch in xib if ch in fb] != fb else [])
+            k_orders = [[ch for ch in xia if ch in ksum]]
+            kb = [ch for ch in xib if ch in ksum]
+            if kb != k_orders[0]:
+                k_orders.append(kb)
+            for ko in k_orders:
+                for mo in m_orders:
+                    for no in n_orders:
+                        cost = operand_cost(xa, xia, mo + ko) + operand_cost(xb, xib, no + ko)
+                        if mo + no != list(io):
+                            M, N, K = _prod(ext[c] for c in mo), _prod(ext[c] for c in no), _prod(ext[c] for c in ko)
+                            tiles = -(-M // 128) * -(-N // 128)
+                            mmap = two_level_map(mo, ext, ostride)
+                            nmap = two_level_map(no, ext, ostride)
+                            fused = mmap is not None and nmap is not None and not (tiles < 148 and K >= 2048)
+                            unit = io[-1]
+                            coalesced = (no and no[-1] == unit) or (mo and mo[-1] == unit)
+                            if not fused:
+                                cost += 3.0 * csize
+                            elif not coalesced:
+                                cost += 4.0 * csize
+                        # mild preferences on ties: the result's unit-stride index among the columns, no role swap
+                        cost += 1e-3 * csize * ((0 if (no and no[-1] == io[-1]) else 1) + (1 if swap else 0))
+                        if best is None or cost < best[0]:
+                            best = (cost, xa, xb, xia, xib, mo, no, ko)
+        return best[1:]
 
     # -- reductions / elementwise ------------------------------------------------------------------
     def dot(self, x, y):

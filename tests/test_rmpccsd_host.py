@@ -144,3 +144,48 @@ def test_driver_loop_against_fixture(path):
     assert abs(e2 - float(g["emp2"])) <= 1e-12
     with pytest.raises(RuntimeError):
         cc.kernel([], [], [], [], mbpt2=True, cc2=True)
+
+
+class _CountingBackend(NumpyBackend):
+    """NumPy stand-in that counts the elements moved by permute passes (what the layout planner minimises)."""
+
+    def __init__(self, *a):
+        super().__init__(*a)
+        self.permuted = 0
+
+    def permute_axpby(self, src, dst, dims, perm, alpha, beta):
+        n = 1
+        for d in dims:
+            n *= d
+        self.permuted += n
+        return super().permute_axpby(src, dst, dims, perm, alpha, beta)
+
+
+def test_layout_planner_leaves_the_large_operand_in_place_and_caches_integral_copies():
+    """'kcad,id->akic' (rmpccsd_slow.py Wvoov build): the o v^3 integral block already is [(k,c,a)][d]; only the
+    o^2 v^2 result may be permuted. And a permuted copy of a const tensor is made once. Values unchanged."""
+    rng = np.random.default_rng(3)
+    o, v = 3, 7
+    be = _CountingBackend(np.zeros(o), np.ones(v))
+    eng = Engine(be)
+    ovvv = eng.tensor(rng.standard_normal((o, v, v, v)))
+    t1 = eng.tensor(rng.standard_normal((o, v)))
+    want = np.einsum("kcad,id->akic", eng.numpy(ovvv), eng.numpy(t1))
+    be.permuted = 0
+    got = eng.numpy(eng.einsum("kcad,id->akic", ovvv, t1))
+    np.testing.assert_allclose(got, want, rtol=1e-12, atol=1e-12)
+    assert be.permuted <= o * o * v * v + o * v          # never the o v^3 operand
+    # 'kdac,ikcd->ia' needs the block as [a][(k,d,c)] whatever the roles: a copy, but only once when it is const
+    t2 = eng.tensor(rng.standard_normal((o, o, v, v)))
+    want = np.einsum("kdac,ikcd->ia", eng.numpy(ovvv), eng.numpy(t2))
+    ovvv.const = True
+    be.permuted = 0
+    np.testing.assert_allclose(eng.numpy(eng.einsum("kdac,ikcd->ia", ovvv, t2)), want, rtol=1e-12, atol=1e-12)
+    first = be.permuted
+    be.permuted = 0
+    np.testing.assert_allclose(eng.numpy(eng.einsum("kdac,ikcd->ia", ovvv, t2)), want, rtol=1e-12, atol=1e-12)
+    assert first >= o * v ** 3 and be.permuted <= first - o * v ** 3
+    # planner off: same numbers
+    eng.plan_layouts = False
+    np.testing.assert_allclose(eng.numpy(eng.einsum("kcad,id->akic", ovvv, t1)),
+                               np.einsum("kcad,id->akic", eng.numpy(ovvv), eng.numpy(t1)), rtol=1e-12, atol=1e-12)
