@@ -72,6 +72,8 @@ int mpccb_bind_jk_exchange(mpccb_ctx* ctx, double* jk_local_dev, double* const* 
  * peer_jk_dev: the nranks buffers in rank order as mapped on this device. */
 int mpccb_bind_jk_subset(mpccb_ctx* ctx, double* jk_local_dev, double* const* peer_jk_dev, int nranks, int rank,
                          double* w_multicast_dev);
+/* the rule behind it, as a pure host function (no device): 1 if rank dst needs the JK rows of rank src's slab */
+int mpccb_jk_subset_needs(int nranks, int src, int dst);
 
 /* Xoo = Lov.t1^T (:120) and Joo = Xoo + Loo (:123) do not depend on the virtual slab; replicated they cost every rank
  * the same GEMM however many ranks there are. Sharded form: the ranks allocate [Xoo | Joo] (2 * naux * nocc^2 doubles)

@@ -44,6 +44,7 @@ SIGNATURES = {
     "mpccb_doubles": (c_int, [c_void_p, c_void_p]),
     "mpccb_t2_tiles": (c_int, [c_void_p, ctypes.POINTER(c_ll), ctypes.POINTER(c_ll)]),
     "mpccb_sym_query": (c_int, [c_int, c_int, ctypes.POINTER(c_int), c_int, c_int, c_int]),
+    "mpccb_jk_subset_needs": (c_int, [c_int, c_int, c_int]),
     "mpccb_doubles_begin": (c_int, [c_void_p, c_void_p]),
     "mpccb_doubles_end": (c_int, [c_void_p, c_void_p]),
     "mpccb_bind_t2_peers": (c_int, [c_void_p, c_int, c_int, ctypes.POINTER(c_int), ctypes.POINTER(c_void_p)]),

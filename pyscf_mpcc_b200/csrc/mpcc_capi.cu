@@ -654,6 +654,14 @@ int mpccb_bind_jk_exchange(mpccb_ctx* c, double* jk_local_dev, double* const* pe
 // F2, :133, is a GEMM over the slab's rows only): the symmetric allocation is nov*ldk (JK) + nov (w) + nov (Fvo)
 // doubles. peer_jk_dev: all nranks buffers in rank order; w goes through w_multicast_dev (the
 // multicast address of the allocation) when given, else through the peer pointers.
+// Pure host rule of the subset exchange: does rank `dst` need the JK rows of rank `src`'s slab? It does iff it computes
+// a slab pair (dst, src) under the mirror scheme, i.e. (src - dst) mod P <= P/2 (checked against mpccb_sym_query in
+// tests/test_host_logic.py).
+int mpccb_jk_subset_needs(int nranks, int src, int dst) {
+  if (nranks < 1 || src < 0 || dst < 0 || src >= nranks || dst >= nranks) return 0;
+  return ((src - dst + nranks) % nranks) <= nranks / 2 ? 1 : 0;
+}
+
 int mpccb_bind_jk_subset(mpccb_ctx* c, double* jk_local_dev, double* const* peer_jk_dev, int nranks, int rank,
                          double* w_multicast_dev) {
   if (!c->ws) return fail(c, "bind the workspace first");
@@ -663,12 +671,9 @@ int mpccb_bind_jk_subset(mpccb_ctx* c, double* jk_local_dev, double* const* peer
   c->w = jk_local_dev + c->w_off;
   c->Fvo = c->w + c->nov;          // Fvo = w - F2 follows w in the symmetric allocation
   c->jk_targets.n = 0;
-  for (int d = 0; d <= nranks / 2; ++d) {
-    const int q = (rank - d + nranks) % nranks;
-    bool seen = false;
-    for (int t = 0; t < c->jk_targets.n; ++t) seen |= (c->jk_targets.p[t] == peer_jk_dev[q]);
-    if (!seen) c->jk_targets.p[c->jk_targets.n++] = peer_jk_dev[q];
-  }
+  c->jk_targets.p[c->jk_targets.n++] = peer_jk_dev[rank];              // own buffer first
+  for (int q = 0; q < nranks; ++q)
+    if (q != rank && mpccb_jk_subset_needs(nranks, rank, q)) c->jk_targets.p[c->jk_targets.n++] = peer_jk_dev[q];
   if (w_multicast_dev) {
     c->w_targets.n = 1;
     c->w_targets.p[0] = w_multicast_dev;

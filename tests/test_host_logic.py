@@ -290,3 +290,29 @@ def test_direct_lapack_eigh_is_bit_identical_to_scipy_eigh():
                 w0, v0 = scipy.linalg.eigh(h)
                 w1, v1 = _eigh(h.copy())
                 assert np.array_equal(w0, w1) and np.array_equal(v0, v1)
+
+
+@pytest.mark.parametrize("nranks,v", [(2, 8), (3, 10), (4, 13), (5, 11), (8, 16), (8, 37)])
+def test_subset_exchange_sends_every_slab_to_every_rank_that_computes_with_it(nranks, v):
+    """mpccb_bind_jk_subset stores a slab's dressed integrals only into the ranks given by mpccb_jk_subset_needs.
+    Every block (a,b) a rank computes under the mirror scheme reads the JK rows of the slabs of a (its own) and of b:
+    the owner of b must be sending to it. And nobody receives a slab it never reads (that is the saving)."""
+    import ctypes
+    from pyscf_mpcc_b200 import _cabi, sharding
+    lib = _cabi.load()
+    bounds = [sharding.slab_bounds(v, nranks, r)[0] for r in range(nranks)] + [v]
+    arr = (ctypes.c_int * (nranks + 1))(*bounds)
+    owner = lambda x: max(r for r in range(nranks) if bounds[r] <= x)
+    used = set()
+    for a in range(v):
+        for b in range(v):
+            q = owner(a)
+            if lib.mpccb_sym_query(nranks, q, arr, 1, a, b) & 1:          # rank q computes block (a,b)
+                assert lib.mpccb_jk_subset_needs(nranks, owner(b), q) == 1, (a, b)
+                used.add((owner(b), q))
+    for src in range(nranks):
+        assert lib.mpccb_jk_subset_needs(nranks, src, src) == 1
+        for dst in range(nranks):
+            if lib.mpccb_jk_subset_needs(nranks, src, dst):
+                assert (src, dst) in used, (src, dst)
+        assert sum(lib.mpccb_jk_subset_needs(nranks, src, d) for d in range(nranks)) == nranks // 2 + 1
