@@ -114,7 +114,26 @@ def _rows(t, lo, hi):
     return DTensor(t.buf[lo * inner:hi * inner], (hi - lo,) + t.shape[1:])
 
 
-def _pp_ladder(eng, eris, t1, tau, t2new, slab_bytes=4 << 30, group=None):
+def _ladder_slabs(v, na_max, rank, world):
+    """Slabs [a0, a1) of the first virtual index for this rank. One rank: pieces of na_max. Several ranks: 2*world (or a
+    multiple) equal pieces, piece s and piece n-1-s to the same rank — the work of a slab is proportional to v - a0
+    (only the blocks b >= a0 are formed), so the two halves of a folded pair add up to the same for every rank."""
+    if world == 1:
+        return [(a0, min(v, a0 + na_max)) for a0 in range(0, v, na_max)]
+    n = 2 * world
+    while -(-v // n) > na_max:
+        n += 2 * world
+    bounds = [v * s // n for s in range(n + 1)]
+    mine = []
+    for s in range(n):
+        owner = s % (2 * world)
+        owner = owner if owner < world else 2 * world - 1 - owner
+        if owner == rank and bounds[s + 1] > bounds[s]:
+            mine.append((bounds[s], bounds[s + 1]))
+    return mine
+
+
+def _pp_ladder(eng, eris, t1, tau, t2new, slab_bytes=4 << 30, group=None, ring=None):
     """t2new[i,j,a,b] += sum_cd W[a,b,c,d] tau[i,j,c,d]  (:138), W = cc_Wvvvv (rintermediates.py:92-99):
         W[a,b,c,d] = (ac|bd) - sum_k (kd|ac) t1[k,b] - sum_k (kc|bd) t1[k,a]
     DF-direct, in slabs of the first virtual index a, so that no v^4 array is ever stored (the blocking idea of
@@ -124,7 +143,9 @@ def _pp_ladder(eng, eris, t1, tau, t2new, slab_bytes=4 << 30, group=None):
     and the second piece is of rank o^2:  sum_L Lt[L,a,c] Lt[L,b,d] = sum_kl t1[k,a] t1[l,b] (kc|ld), so its ladder
     contribution is  sum_kl t1[k,a] t1[l,b] X[k,l,i,j],  X = sum_cd (kc|ld) tau[i,j,c,d]  — O(o^4 v^2) flops instead
     of a pass over every slab of W. Per slab: one GEMM (ac|bd)-shaped product stored straight in [a,b,c,d] order by
-    the index-mapped epilogue, one GEMM against tau. Several ranks: slabs are dealt round-robin, one all-reduce."""
+    the index-mapped epilogue, one GEMM against tau. Several ranks: slabs are dealt in folded pairs (_ladder_slabs),
+    ``ring`` (a callable R -> None, see _ring_terms_into) adds this rank's share of the ring / exchange terms to the
+    same [a,b,i,j] accumulator, and one all-reduce completes both."""
     E = eng.einsum
     be = eng.be
     v, L = eris.nvir, eris.naux
@@ -140,14 +161,11 @@ def _pp_ladder(eng, eris, t1, tau, t2new, slab_bytes=4 << 30, group=None):
     # diagonal slab block holds both members of a pair and enters with weight 1/2, and the final
     # t2new += R^T(2,3,0,1) + R^T(3,2,1,0) restores everything. About (1 + 1/nslabs)/2 of the ladder flops.
     na = max(1, min(v, int(slab_bytes // (8 * v * v * v)), -(-v // 6)))
-    # several ranks: the slabs are dealt round-robin (north_star: "the ladder ... shards naturally over ab"); every
-    # rank fills its blocks of R, one all-reduce (sum with zeros) completes it
+    # several ranks (north_star: "the ladder ... shards naturally over ab"): every rank fills its blocks of R, one
+    # all-reduce (sum with zeros) completes it
     rank, world = (0, 1) if group is None else be.rank_and_size(group)
     BIG = 1 << 30
-    for n_slab, a0 in enumerate(range(0, v, na)):
-        if n_slab % world != rank:
-            continue
-        a1 = min(v, a0 + na)
+    for a0, a1 in _ladder_slabs(v, na, rank, world):
         n_a, n_b = a1 - a0, v - a0
         # W[b', a, c, d] = sum_L Leff[a0+a, c, L] Leff[a0+b', d, L]: product rows (a,c), columns (b',d); stored b'-major
         # by the index-mapped epilogue so that the diagonal block (b' < n_a) is a contiguous row range
@@ -165,6 +183,8 @@ def _pp_ladder(eng, eris, t1, tau, t2new, slab_bytes=4 << 30, group=None):
         eng.flops += 2.0 * n_b * n_a * o2 * v * v
         eng.gemms += 3
         del W
+    if ring is not None:
+        ring(R)
     if world > 1:
         be.all_reduce(R.buf, group)
     eng.add(t2new, R, 1.0, (2, 3, 0, 1))
@@ -176,7 +196,7 @@ def _pp_ladder(eng, eris, t1, tau, t2new, slab_bytes=4 << 30, group=None):
     return t2new
 
 
-def _intermediates(eng, t1, t2, tau, eris, f, cc2=False):
+def _intermediates(eng, t1, t2, tau, eris, f, cc2=False, ring_gemms=True):
     """Foo, Fvv, Fov (rintermediates.py:29-59), Loo, Lvv (:63-79), Woooo, Wvoov, Wvovo (:83-126).
     `f` holds the fock blocks as device tensors (fov, foo, fvv)."""
     E = eng.einsum
@@ -212,19 +232,50 @@ def _intermediates(eng, t1, t2, tau, eris, f, cc2=False):
     Wvoov = eng.transpose(eris.ovvo, (2, 0, 3, 1))
     E("kcad,id->akic", ovvv, t1, out=Wvoov, beta=1.0)
     E("kcli,la->akic", ovoo, t1, alpha=-1.0, out=Wvoov, beta=1.0)
-    E("ldkc,ilda->akic", ovov, t2, alpha=-0.5, out=Wvoov, beta=1.0)
-    # (:113) -0.5 (lc|kd) t2[i,l,a,d]  and  (:117) + (ld|kc) t2[i,l,a,d]  contract the same amplitudes: one GEMM with
-    # (ld|kc) - 0.5 (lc|kd) = 0.5 * lov[l,d,k,c]
-    E("ldkc,ilad->akic", lov, t2, alpha=0.5, out=Wvoov, beta=1.0)
+    if ring_gemms:
+        E("ldkc,ilda->akic", ovov, t2, alpha=-0.5, out=Wvoov, beta=1.0)
+        # (:113) -0.5 (lc|kd) t2[i,l,a,d]  and  (:117) + (ld|kc) t2[i,l,a,d]  contract the same amplitudes: one GEMM
+        # with (ld|kc) - 0.5 (lc|kd) = 0.5 * lov[l,d,k,c]
+        E("ldkc,ilad->akic", lov, t2, alpha=0.5, out=Wvoov, beta=1.0)
     y = E("ldkc,id->lkci", ovov, t1)
     E("lkci,la->akic", y, t1, alpha=-1.0, out=Wvoov, beta=1.0)
     Wvovo = eng.transpose(eris.oovv, (2, 0, 3, 1))
     E("kdac,id->akci", ovvv, t1, out=Wvovo, beta=1.0)
     E("lcki,la->akci", ovoo, t1, alpha=-1.0, out=Wvovo, beta=1.0)
-    E("lckd,ilda->akci", ovov, t2, alpha=-0.5, out=Wvovo, beta=1.0)
+    if ring_gemms:
+        E("lckd,ilda->akci", ovov, t2, alpha=-0.5, out=Wvovo, beta=1.0)
     y = E("lckd,id->lcki", ovov, t1)
     E("lcki,la->akci", y, t1, alpha=-1.0, out=Wvovo, beta=1.0)
-    return dict(Foo=Foo, Fvv=Fvv, Fov=Fov, Loo=Loo, Lvv=Lvv, Woooo=Woooo, Wvoov=Wvoov, Wvovo=Wvovo)
+    return dict(Foo=Foo, Fvv=Fvv, Fov=Fov, Loo=Loo, Lvv=Lvv, Woooo=Woooo, Wvoov=Wvoov, Wvovo=Wvovo, lov=lov)
+
+
+def _ring_terms_into(eng, eris, t2, im, R, rank, world):
+    """This rank's share of the ring / exchange terms (:143-149), accumulated into R[a,b,i,j] for its slab of the
+    virtual index a (the ROW index of Wvoov / Wvovo): the three o^3 v^3 products that complete the intermediates for
+    the slab (``im`` was built with ``ring_gemms=False``) and the three that contract them with t2. With
+    tmp[i,j,a,b] -> R[a,b,i,j] the symmetrisation tmp + tmp^T(1,0,3,2) of :142-155 is the R^T(2,3,0,1) + R^T(3,2,1,0)
+    of the ladder; the third term enters in its transposed form so that its row index is the slab index as well:
+        - sum_kc Wvovo[b,k,c,i] t2[k,j,a,c]  (+ transpose)  ==  - sum_kc Wvovo[a,k,c,j] t2[k,i,b,c]  (+ transpose)."""
+    E = eng.einsum
+    v = eris.nvir
+    a0, a1 = v * rank // world, v * (rank + 1) // world
+    if a1 <= a0:
+        return
+    # t2 with the slab index leading, so that the slab is a row range: t2[i,l,d,a] -> [a,i,l,d] and t2[i,l,a,d] -> [a,i,l,d]
+    tA = _rows(eng.transpose(t2, (3, 0, 1, 2)), a0, a1)
+    tB = _rows(eng.transpose(t2, (2, 0, 1, 3)), a0, a1)
+    Wvoov, Wvovo = _rows(im["Wvoov"], a0, a1), _rows(im["Wvovo"], a0, a1)
+    E("aild,ldkc->akic", tA, eris.ovov, alpha=-0.5, out=Wvoov, beta=1.0)          # (:113)
+    E("aild,ldkc->akic", tB, im["lov"], alpha=0.5, out=Wvoov, beta=1.0)           # (:113) + (:117)
+    E("aild,lckd->akci", tA, eris.ovov, alpha=-0.5, out=Wvovo, beta=1.0)          # (:124)
+    del tA, tB
+    ring = eng.scale(Wvoov, 2.0)
+    eng.add(ring, Wvovo, -1.0, (0, 1, 3, 2))
+    Rs = _rows(R, a0, a1)
+    E("akic,kjcb->abij", ring, t2, out=Rs, beta=1.0)                              # ring (:143-145)
+    del ring
+    E("akic,kjbc->abij", Wvoov, t2, alpha=-1.0, out=Rs, beta=1.0)                 # exchange (:146-147)
+    E("akcj,kibc->abij", Wvovo, t2, alpha=-1.0, out=Rs, beta=1.0)                 # exchange (:148-149), transposed form
 
 
 def _fock_blocks(eng, eris, remove_diag=False):
@@ -260,7 +311,9 @@ def update_amps(cc, t1, t2, eris, act_hole=(), act_particle=(), idx_singles=(), 
     f = _fock_blocks(eng, eris)
     ovvv, ooov, ovvo, oovv, ovov = eris.ovvv, eris.ooov, eris.ovvo, eris.oovv, eris.ovov
     tau = make_tau(eng, t1, t2)
-    im = _intermediates(eng, t1, t2, tau, eris, f, cc2=cc2)
+    rank, world = (0, 1) if group is None else eng.be.rank_and_size(group)
+    shard_ring = world > 1 and not cc2
+    im = _intermediates(eng, t1, t2, tau, eris, f, cc2=cc2, ring_gemms=not shard_ring)
     Foo, Fvv, Fov = im["Foo"], im["Fvv"], im["Fov"]
     # move energy terms to the other side (:90-91, :135)
     shifted = ((Foo, "foo_diag"), (Fvv, "fvv_diag"))
@@ -316,9 +369,12 @@ def update_amps(cc, t1, t2, eris, act_hole=(), act_particle=(), idx_singles=(), 
         _sym_add(eng, t2new, E("ki,kjab->ijab", Loo2, t2), -1.0)          # (:132-133)
     else:
         E("klij,klab->ijab", im["Woooo"], tau, out=t2new, beta=1.0)          # hole-hole ladder (:137)
-        _pp_ladder(eng, eris, t1, tau, t2new, group=group)                    # particle-particle ladder (:138)
+        # particle-particle ladder (:138); several ranks: the ring / exchange terms ride in the same accumulator
+        _pp_ladder(eng, eris, t1, tau, t2new, group=group,
+                   ring=(lambda R: _ring_terms_into(eng, eris, t2, im, R, rank, world)) if shard_ring else None)
         _sym_add(eng, t2new, E("ac,ijcb->ijab", im["Lvv"], t2), 1.0)          # (:139-140)
         _sym_add(eng, t2new, E("ki,kjab->ijab", im["Loo"], t2), -1.0)         # (:141-142)
+    if not cc2 and not shard_ring:
         ring = eng.scale(im["Wvoov"], 2.0)                                    # ring (:143-145): 2 Wvoov[a,k,i,c] -
         eng.add(ring, im["Wvovo"], -1.0, (0, 1, 3, 2))                        # Wvovo[a,k,c,i] share t2[k,j,c,b]: one GEMM
         _sym_add(eng, t2new, E("akic,kjcb->ijab", ring, t2), 1.0)

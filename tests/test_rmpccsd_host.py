@@ -189,3 +189,55 @@ def test_layout_planner_leaves_the_large_operand_in_place_and_caches_integral_co
     eng.plan_layouts = False
     np.testing.assert_allclose(eng.numpy(eng.einsum("kcad,id->akic", ovvv, t1)),
                                np.einsum("kcad,id->akic", eng.numpy(ovvv), eng.numpy(t1)), rtol=1e-12, atol=1e-12)
+
+
+class _RankBackend(NumpyBackend):
+    """One simulated rank of a group: ``all_reduce`` only records the buffer (the test sums the ranks' buffers)."""
+
+    def __init__(self, eo, ev, rank, world):
+        super().__init__(eo, ev)
+        self.rank, self.world, self.reduced = rank, world, []
+
+    def rank_and_size(self, group):
+        return self.rank, self.world
+
+    def all_reduce(self, buf, group):
+        self.reduced.append(buf.copy())
+
+
+@pytest.mark.parametrize("world", [2, 3, 8])
+def test_sharded_ladder_and_ring_terms_sum_to_the_one_rank_result(world):
+    """Several ranks (rmpccsd.update_amps with cc.group): every rank fills its slabs of the particle-particle ladder
+    and its slab of the ring / exchange terms into one [a,b,i,j] accumulator that is all-reduced. Simulated rank by
+    rank on the CPU: the accumulators add up to an R whose symmetrised transpose is exactly what the one-rank code
+    adds to t2new for those terms; checked through the final amplitudes by linearity (the terms outside R are
+    replicated, the division by the denominators is linear)."""
+    p = make_problem(5, 11, 23, seed=9)
+    o, v = 5, 11
+    ah, ap, ids, idd = [1, 3], [0, 4, 7], [0, 2], [1, 5, 10, 12]
+
+    def run(rank, world):
+        be = _RankBackend(p["eo"], p["ev"], rank, world)
+        eng = Engine(be)
+        eris = rmpccsd.DFERIs.from_numpy(eng, p["Loo"], p["Lov"], p["Lvv"], p["fock"])
+        cc = types.SimpleNamespace(cc2=False, group="g" if world > 1 else None)
+        t1n, t2n = rmpccsd.update_amps(cc, p["t1"], p["t2"], eris, [], [], [], [])
+        return t1n, t2n, be.reduced
+
+    t1_ref, t2_ref, _ = run(0, 1)
+    parts = [run(r, world) for r in range(world)]
+    # every rank's t2new = D^-1 (replicated terms + sym(R_r)); sum over ranks = D^-1 (world * replicated + sym(R));
+    # and with all ranks' R summed in place of its own, each rank would return t2_ref
+    t2_sum = sum(t2n for _, t2n, _ in parts)
+    t2_rep = (t2_sum - t2_ref) / (world - 1)            # D^-1 (replicated terms) if and only if sum_r R_r == R
+    assert all(len(red) == 1 for _, _, red in parts)
+    for t1n, _, _ in parts:
+        np.testing.assert_allclose(t1n, t1_ref, rtol=1e-11, atol=1e-12)          # singles are replicated
+    R_total = sum(red[0] for _, _, red in parts).reshape(v, v, o, o)
+    # reference R: ladder + ring terms of the reference code = what the one-rank result contains beyond the
+    # replicated terms; compare sym(R_total) / D with t2_ref - t2_rep
+    eia = p["eo"][:, None] - p["ev"][None, :]
+    D = eia[:, None, :, None] + eia[None, :, None, :]
+    symR = R_total.transpose(2, 3, 0, 1) + R_total.transpose(3, 2, 1, 0)
+    # a wrong or missing share Delta = R_total - R would show up here as Delta * world / (world - 1)
+    np.testing.assert_allclose(t2_ref - t2_rep, symR / D, rtol=1e-9, atol=1e-11)

@@ -1,6 +1,6 @@
-"""Several ranks (torchrun, NCCL): the CCSD-type residual with the particle-particle ladder sharded over the ranks
-(slabs of the first virtual index dealt round-robin, one all-reduce of the ladder result) against the fixtures the
-reference's own update_amps produced, then a timing of one update at a larger shape.
+"""Several ranks (torchrun, NCCL): the CCSD-type residual with the particle-particle ladder and the ring / exchange
+terms sharded over the ranks (slabs of the first virtual index, one all-reduce of the [a,b,i,j] accumulator) against
+the fixtures the reference's own update_amps produced, then a timing of one update at a larger shape.
 
     python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 tools/cc_mgpu_check.py
 
@@ -60,10 +60,10 @@ Loo, Lov, Lvv, eo, ev = device_blocks(o, v, L, seed=0, scale=default_scale(o, v)
 ll = MPCC_LL(blocks=(Loo, Lov, Lvv, torch.diag(eo), torch.diag(ev), torch.cat([eo, ev])), device=dev, group=mine)
 eris = ll.high_level_eris()
 res = {}
-for label, group in (("replicated", None), ("ladder_sharded", dist.group.WORLD)):
+for label, group in (("replicated", None), ("sharded", dist.group.WORLD)):
     cc = types.SimpleNamespace(cc2=False, group=group)
     emp2, t1, t2 = rmpccsd.init_amps(cc, eris)
-    for rep in range(2):
+    for rep in range(3):
         torch.cuda.synchronize()
         dist.barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
