@@ -133,7 +133,16 @@ def _ladder_slabs(v, na_max, rank, world):
     return mine
 
 
-def _pp_ladder(eng, eris, t1, tau, t2new, slab_bytes=4 << 30, group=None, ring=None):
+def _pair_symmetric(eng, t):
+    """Is t[i,j,a,b] == t[j,i,b,a] (to rounding)? True for amplitudes that went through the DIIS vector (symmetric
+    unpack of a lower triangle, ccsd.py:594-603) or came out of the symmetrised equations; not guaranteed for an
+    arbitrary input of update_amps, e.g. after a class overwrite with a class list that is not closed under the swap."""
+    d = eng.copy(t)
+    eng.add(d, t, -1.0, (1, 0, 3, 2))
+    return eng.dot(d, d) <= 1e-24 * max(eng.dot(t, t), 1e-300)
+
+
+def _pp_ladder(eng, eris, t1, tau, t2new, slab_bytes=4 << 30, group=None, ring=None, halve=True):
     """t2new[i,j,a,b] += sum_cd W[a,b,c,d] tau[i,j,c,d]  (:138), W = cc_Wvvvv (rintermediates.py:92-99):
         W[a,b,c,d] = (ac|bd) - sum_k (kd|ac) t1[k,b] - sum_k (kc|bd) t1[k,a]
     DF-direct, in slabs of the first virtual index a, so that no v^4 array is ever stored (the blocking idea of
@@ -162,10 +171,23 @@ def _pp_ladder(eng, eris, t1, tau, t2new, slab_bytes=4 << 30, group=None, ring=N
     # t2new += R^T(2,3,0,1) + R^T(3,2,1,0) restores everything. About (1 + 1/nslabs)/2 of the ladder flops.
     na = max(1, min(v, int(slab_bytes // (8 * v * v * v)), -(-v // 6)))
     # several ranks (north_star: "the ladder ... shards naturally over ab"): every rank fills its blocks of R, one
-    # all-reduce (sum with zeros) completes it
+    # all-reduce (sum with zeros) completes it.
+    # halve=False (tau not pair-symmetric): every block b of a slab is formed and R enters once, untransposed; the ring
+    # terms, whose symmetrisation is part of the equations, then get an accumulator of their own.
     rank, world = (0, 1) if group is None else be.rank_and_size(group)
     BIG = 1 << 30
     for a0, a1 in _ladder_slabs(v, na, rank, world):
+        if not halve:
+            n_a = a1 - a0
+            W = be.empty(v * n_a * v * v)
+            be.gemm_nt_mapped(LA.buf[a0 * v * L:], LA.buf, W, n_a * v, v * v, L, (v, v * v, v), (v, n_a * v * v, 1),
+                              1.0, 0.0)
+            be.gemm_nt_mapped(W, tau.buf, R.buf[a0 * v * o2:], v * n_a, o2, v * v, (n_a, o2, v * o2), (BIG, 0, 1),
+                              1.0, 0.0)
+            eng.flops += 2.0 * n_a * v * v * v * (L + o2)
+            eng.gemms += 2
+            del W
+            continue
         n_a, n_b = a1 - a0, v - a0
         # W[b', a, c, d] = sum_L Leff[a0+a, c, L] Leff[a0+b', d, L]: product rows (a,c), columns (b',d); stored b'-major
         # by the index-mapped epilogue so that the diagonal block (b' < n_a) is a contiguous row range
@@ -183,13 +205,21 @@ def _pp_ladder(eng, eris, t1, tau, t2new, slab_bytes=4 << 30, group=None, ring=N
         eng.flops += 2.0 * n_b * n_a * o2 * v * v
         eng.gemms += 3
         del W
-    if ring is not None:
+    if ring is not None and halve:
         ring(R)
     if world > 1:
         be.all_reduce(R.buf, group)
     eng.add(t2new, R, 1.0, (2, 3, 0, 1))
-    eng.add(t2new, R, 1.0, (3, 2, 1, 0))
+    if halve:
+        eng.add(t2new, R, 1.0, (3, 2, 1, 0))
     del R
+    if ring is not None and not halve:
+        R2 = eng.zeros((v, v) + tau.shape[:2])
+        ring(R2)
+        be.all_reduce(R2.buf, group)
+        eng.add(t2new, R2, 1.0, (2, 3, 0, 1))
+        eng.add(t2new, R2, 1.0, (3, 2, 1, 0))
+        del R2
     X = E("kcld,ijcd->klij", eris.ovov, tau)                      # rank-o^2 correction: - t1 t1 X
     Y = E("ka,klij->alij", t1, X)
     E("lb,alij->ijab", t1, Y, alpha=-1.0, out=t2new, beta=1.0)
@@ -328,20 +358,26 @@ def update_amps(cc, t1, t2, eris, act_hole=(), act_particle=(), idx_singles=(), 
     E("ki,ka->ia", z, t1, alpha=-2.0, out=t1new, beta=1.0)
     E("ac,ic->ia", Fvv, t1, out=t1new, beta=1.0)
     E("ki,ka->ia", Foo, t1, alpha=-1.0, out=t1new, beta=1.0)
-    E("kc,kica->ia", Fov, t2, alpha=2.0, out=t1new, beta=1.0)
-    E("kc,ikca->ia", Fov, t2, alpha=-1.0, out=t1new, beta=1.0)
+    # The "2 x - x'" pairs of :99-100, :105-106, :109-110 each contract the same integrals with t2 in two index
+    # orders: one product with 2 t2 - t2' instead of two with t2 (no symmetry of t2 is assumed: the class overwrite
+    # of a previous update may have broken t2[ijab] = t2[jiba]).
+    theta_o = eng.scale(t2, 2.0)                                  # 2 t2[k,i,c,a] - t2[i,k,c,a]
+    eng.add(theta_o, t2, -1.0, (1, 0, 2, 3))
+    E("kc,kica->ia", Fov, theta_o, out=t1new, beta=1.0)
     z = E("kc,ic->ki", Fov, t1)
     E("ki,ka->ia", z, t1, out=t1new, beta=1.0)
     E("kcai,kc->ia", ovvo, t1, alpha=2.0, out=t1new, beta=1.0)
     E("kiac,kc->ia", oovv, t1, alpha=-1.0, out=t1new, beta=1.0)
-    E("kdac,ikcd->ia", ovvv, t2, alpha=2.0, out=t1new, beta=1.0)
-    E("kcad,ikcd->ia", ovvv, t2, alpha=-1.0, out=t1new, beta=1.0)
+    theta_v = eng.scale(t2, 2.0)                                  # 2 t2[i,k,c,d] - t2[i,k,d,c]
+    eng.add(theta_v, t2, -1.0, (0, 1, 3, 2))
+    E("kdac,ikcd->ia", ovvv, theta_v, out=t1new, beta=1.0)       # 2 (kd|ac) t2[ikcd] - (kc|ad) t2[ikcd], c <-> d in the second
+    del theta_v
     w = E("kdac,kd->ac", ovvv, t1)
     E("ac,ic->ia", w, t1, alpha=2.0, out=t1new, beta=1.0)
     w = E("kcad,kd->ca", ovvv, t1)
     E("ca,ic->ia", w, t1, alpha=-1.0, out=t1new, beta=1.0)
-    E("kilc,klac->ia", ooov, t2, alpha=-2.0, out=t1new, beta=1.0)
-    E("likc,klac->ia", ooov, t2, out=t1new, beta=1.0)
+    E("kilc,klac->ia", ooov, theta_o, alpha=-1.0, out=t1new, beta=1.0)  # -2 (ki|lc) t2[klac] + (li|kc) t2[klac], k <-> l
+    del theta_o
     u = E("kilc,lc->ki", ooov, t1)
     E("ki,ka->ia", u, t1, alpha=-2.0, out=t1new, beta=1.0)
     u = E("likc,lc->ik", ooov, t1)
@@ -370,7 +406,7 @@ def update_amps(cc, t1, t2, eris, act_hole=(), act_particle=(), idx_singles=(), 
     else:
         E("klij,klab->ijab", im["Woooo"], tau, out=t2new, beta=1.0)          # hole-hole ladder (:137)
         # particle-particle ladder (:138); several ranks: the ring / exchange terms ride in the same accumulator
-        _pp_ladder(eng, eris, t1, tau, t2new, group=group,
+        _pp_ladder(eng, eris, t1, tau, t2new, group=group, halve=_pair_symmetric(eng, t2),
                    ring=(lambda R: _ring_terms_into(eng, eris, t2, im, R, rank, world)) if shard_ring else None)
         _sym_add(eng, t2new, E("ac,ijcb->ijab", im["Lvv"], t2), 1.0)          # (:139-140)
         _sym_add(eng, t2new, E("ki,kjab->ijab", im["Loo"], t2), -1.0)         # (:141-142)

@@ -1,7 +1,7 @@
 """Fixtures for the CC2 branch and the driver loop of the high-level stage, from the REFERENCE's own code.
 
 Run in the build container only (needs /root/reference):
-    python tests/golden/generate_golden_cc2.py
+    python tests/golden/generate_golden_cc2.py            (--asym: only the non-symmetric t2 case at the end of this file)
 * ``rmpccsd_cc2_*.npz``    — ``rmpccsd_slow.update_amps`` with ``cc.cc2 = True`` (:115-133).
 * ``rmpccsd_kernel_*.npz`` — the iteration ``RMPCCSD.ccsd`` runs (:223-258 -> ``ccsd.kernel``, ccsd.py:42-150): the loop
   is ``oracle/cc_oracle.ccsd_kernel`` (restated; ccsd.py itself is not importable here) around the reference's
@@ -67,5 +67,28 @@ def main():
         print(path, "cycles =", len(hist), "converged =", conv, "E_corr =", e)
 
 
-if __name__ == "__main__":
+if __name__ == "__main__" and "--asym" not in sys.argv:
     main()
+
+
+def asym_case():
+    """``rmpccsd_asym_4_9_21.npz`` — update_amps of the reference on a t2 that is NOT pair-symmetric
+    (t2[ijab] != t2[jiba]): make_problem's t2 plus seeded noise, both branches."""
+    slow, _ = ref_shim.load_reference_cc()
+    o, v, L, seed, noise_seed, eps = 4, 9, 21, 11, 5, 0.05
+    p = make_problem(o, v, L, seed=seed)
+    t2 = p["t2"] + eps * np.random.default_rng(noise_seed).standard_normal(p["t2"].shape)
+    er = reference_eris(p)
+    out = dict(shape=np.array([o, v, L]), seed=seed, noise_seed=noise_seed, eps=eps, act_hole=np.array([0, 2]),
+               act_particle=np.array([1, 3]), idx_singles=np.array([0]), idx_doubles=np.array([1, 5]))
+    for cc2 in (False, True):
+        t1n, t2n = slow.update_amps(types.SimpleNamespace(cc2=cc2), p["t1"], t2, er, [0, 2], [1, 3], [0], [1, 5])
+        tag = "cc2" if cc2 else "ccsd"
+        out[f"t1new_{tag}"], out[f"t2new_{tag}"] = t1n, t2n
+    path = os.path.join(HERE, f"rmpccsd_asym_{o}_{v}_{L}.npz")
+    np.savez_compressed(path, **out)
+    print(path)
+
+
+if __name__ == "__main__" and "--asym" in sys.argv:
+    asym_case()

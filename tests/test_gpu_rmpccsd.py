@@ -151,3 +151,20 @@ def test_vector_layouts_on_device():
     t1, t2 = eng.vector_to_amplitudes(vec, 5, 9)
     t1o, t2o = cc_oracle.vector_to_amplitudes(want, 14, 5)
     assert np.array_equal(eng.numpy(t1), t1o) and np.array_equal(eng.numpy(t2), t2o)
+
+
+@pytest.mark.parametrize("cc2", [False, True])
+def test_update_amps_with_a_t2_that_is_not_pair_symmetric(cc2):
+    """The reference's update_amps on a t2 with t2[ijab] != t2[jiba] (fixture rmpccsd_asym_*.npz): the halved
+    particle-particle ladder needs that symmetry, so the residual checks it and falls back to the full ladder."""
+    from pyscf_mpcc_b200 import rmpccsd
+    g = np.load(os.path.join(GOLDEN, "rmpccsd_asym_4_9_21.npz"))
+    o, v, L = (int(x) for x in g["shape"])
+    p = make_problem(o, v, L, seed=int(g["seed"]))
+    t2 = p["t2"] + float(g["eps"]) * np.random.default_rng(int(g["noise_seed"])).standard_normal(p["t2"].shape)
+    ll, eris = _device_problem(p)
+    t1n, t2n = rmpccsd.update_amps(types.SimpleNamespace(cc2=cc2), p["t1"], t2, eris, list(g["act_hole"]),
+                                   list(g["act_particle"]), list(g["idx_singles"]), list(g["idx_doubles"]))
+    tag = "cc2" if cc2 else "ccsd"
+    assert np.abs(t1n - g[f"t1new_{tag}"]).max() <= 1e-10
+    assert np.abs(t2n - g[f"t2new_{tag}"]).max() <= 1e-10

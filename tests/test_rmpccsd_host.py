@@ -205,8 +205,8 @@ class _RankBackend(NumpyBackend):
         self.reduced.append(buf.copy())
 
 
-@pytest.mark.parametrize("world", [2, 3, 8])
-def test_sharded_ladder_and_ring_terms_sum_to_the_one_rank_result(world):
+@pytest.mark.parametrize("world,asym", [(2, 0.0), (3, 0.0), (8, 0.0), (3, 0.05)])
+def test_sharded_ladder_and_ring_terms_sum_to_the_one_rank_result(world, asym):
     """Several ranks (rmpccsd.update_amps with cc.group): every rank fills its slabs of the particle-particle ladder
     and its slab of the ring / exchange terms into one [a,b,i,j] accumulator that is all-reduced. Simulated rank by
     rank on the CPU: the accumulators add up to an R whose symmetrised transpose is exactly what the one-rank code
@@ -214,14 +214,14 @@ def test_sharded_ladder_and_ring_terms_sum_to_the_one_rank_result(world):
     replicated, the division by the denominators is linear)."""
     p = make_problem(5, 11, 23, seed=9)
     o, v = 5, 11
-    ah, ap, ids, idd = [1, 3], [0, 4, 7], [0, 2], [1, 5, 10, 12]
+    t2_in = p["t2"] + asym * np.random.default_rng(2).standard_normal(p["t2"].shape)   # asym > 0: the full-ladder path
 
     def run(rank, world):
         be = _RankBackend(p["eo"], p["ev"], rank, world)
         eng = Engine(be)
         eris = rmpccsd.DFERIs.from_numpy(eng, p["Loo"], p["Lov"], p["Lvv"], p["fock"])
         cc = types.SimpleNamespace(cc2=False, group="g" if world > 1 else None)
-        t1n, t2n = rmpccsd.update_amps(cc, p["t1"], p["t2"], eris, [], [], [], [])
+        t1n, t2n = rmpccsd.update_amps(cc, p["t1"], t2_in, eris, [], [], [], [])
         return t1n, t2n, be.reduced
 
     t1_ref, t2_ref, _ = run(0, 1)
@@ -230,14 +230,34 @@ def test_sharded_ladder_and_ring_terms_sum_to_the_one_rank_result(world):
     # and with all ranks' R summed in place of its own, each rank would return t2_ref
     t2_sum = sum(t2n for _, t2n, _ in parts)
     t2_rep = (t2_sum - t2_ref) / (world - 1)            # D^-1 (replicated terms) if and only if sum_r R_r == R
-    assert all(len(red) == 1 for _, _, red in parts)
+    assert all(len(red) == (2 if asym else 1) for _, _, red in parts)
     for t1n, _, _ in parts:
         np.testing.assert_allclose(t1n, t1_ref, rtol=1e-11, atol=1e-12)          # singles are replicated
-    R_total = sum(red[0] for _, _, red in parts).reshape(v, v, o, o)
+    R_total = sum(red[-1] for _, _, red in parts).reshape(v, v, o, o)           # asym: [ladder R, ring R2]
+    R_once = sum(red[0] for _, _, red in parts).reshape(v, v, o, o) if asym else 0.0
     # reference R: ladder + ring terms of the reference code = what the one-rank result contains beyond the
     # replicated terms; compare sym(R_total) / D with t2_ref - t2_rep
     eia = p["eo"][:, None] - p["ev"][None, :]
     D = eia[:, None, :, None] + eia[None, :, None, :]
     symR = R_total.transpose(2, 3, 0, 1) + R_total.transpose(3, 2, 1, 0)
+    if asym:
+        symR = symR + R_once.transpose(2, 3, 0, 1)
     # a wrong or missing share Delta = R_total - R would show up here as Delta * world / (world - 1)
     np.testing.assert_allclose(t2_ref - t2_rep, symR / D, rtol=1e-9, atol=1e-11)
+
+
+@pytest.mark.parametrize("cc2", [False, True])
+def test_update_amps_with_a_t2_that_is_not_pair_symmetric(cc2):
+    """update_amps is a public function of the reference (rmpccsd_slow.py:73) and assumes nothing about t2; a class
+    overwrite with a class list that is not closed under (i,a) <-> (j,b) produces a t2 with t2[ijab] != t2[jiba].
+    The halved particle-particle ladder needs that symmetry: it is checked, and the full ladder is used otherwise."""
+    slow, _ = ref_shim.load_reference_cc()
+    p = make_problem(4, 9, 21, seed=11)
+    t2 = p["t2"] + 0.05 * np.random.default_rng(5).standard_normal(p["t2"].shape)
+    assert np.abs(t2 - t2.transpose(1, 0, 3, 2)).max() > 0.1
+    cc = types.SimpleNamespace(cc2=cc2)
+    want1, want2 = slow.update_amps(cc, p["t1"], t2, reference_eris(p), [0, 2], [1, 3], [0], [1, 5])
+    eng, eris = _engine(p)
+    got1, got2 = rmpccsd.update_amps(cc, p["t1"], t2, eris, [0, 2], [1, 3], [0], [1, 5])
+    np.testing.assert_allclose(got1, want1, rtol=1e-11, atol=1e-12)
+    np.testing.assert_allclose(got2, want2, rtol=1e-11, atol=1e-12)
