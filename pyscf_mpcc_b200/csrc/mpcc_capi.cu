@@ -45,6 +45,7 @@ struct mpccb_ctx {
   cudaStream_t stream;
   long long launches;
   int use_tma;
+  int mapped_narrow_k;       // mpccb_gemm_nt_mapped uses 128 x 64 tiles (two CTAs per SM) up to this K (0: never)
   int xvo_generic;           // 1: keep the Xvo GEMM (:119) on the generic kernel (A/B measurements)
   char err[512];
   // bound tensors
@@ -478,6 +479,7 @@ int mpccb_create(mpccb_ctx** out, int nocc, int nvir, int naux, int a_begin, int
   c->ldk = (int)align_up(naux, 2);
   c->jp = (int)align_up(nocc, 2);
   c->use_tma = 1;
+  c->mapped_narrow_k = 1024;
   c->profile = 0;
   c->prof_ev = new std::vector<cudaEvent_t>[ST_COUNT];
   c->attr_set = new std::vector<const void*>();
@@ -542,6 +544,7 @@ int mpccb_set_option(mpccb_ctx* c, const char* name, long long value) {
   }
   if (!strcmp(name, "profile")) { c->profile = value != 0; return 0; }
   if (!strcmp(name, "xvo_generic")) { c->xvo_generic = value != 0; return 0; }
+  if (!strcmp(name, "mapped_narrow_k")) { c->mapped_narrow_k = (int)value; return 0; }
   if (!strcmp(name, "yvo_flat")) {        // 1 / -1: force the flat-K Yvo form on / off (0 = automatic; before bind_workspace)
     if (c->ws) return fail(c, "set yvo_flat before binding the workspace");
     c->yvo_flat_force = (int)value;
@@ -1736,7 +1739,10 @@ extern "C" int mpccb_gemm_nt_mapped(mpccb_ctx* c, const double* A_dev, const dou
   C.alpha = alpha; C.beta = beta;
   const bool aligned = (K % 2 == 0) && ((reinterpret_cast<uintptr_t>(A_dev) | reinterpret_cast<uintptr_t>(B_dev)) & 15) == 0;
   if (c->use_tma && aligned && K >= 16 && (double)M * N * K >= 5e8 && M >= 64 && N >= 64) {
-    constexpr int TN = TmaCfg<4>::TN;
+    // short K (the W = Leff.Leff^T product of the DF-direct ladder, K = naux): the store epilogue is a visible share of
+    // a tile's life, so 128 x 64 tiles with two CTAs per SM — one stores while the other multiplies
+    const bool narrow = K <= c->mapped_narrow_k;
+    const int TN = narrow ? TmaCfg<2>::TN : TmaCfg<4>::TN;
     CUtensorMap mA, mB;
     if (make_map_2d(c, &mA, A_dev, K, M, K, TMA_TM)) return 1;
     if (make_map_2d(c, &mB, B_dev, K, N, K, TN)) return 1;
@@ -1747,12 +1753,13 @@ extern "C" int mpccb_gemm_nt_mapped(mpccb_ctx* c, const double* A_dev, const dou
     p.tiles_m = cdiv(M, TMA_TM); p.tiles_n = cdiv(N, TN);
     p.nk = cdiv(K, TMA_TK);
     p.a_mode = 0;
-    p.a_bytes = TMA_TM * TMA_TK * 8; p.b_bytes = TN * TMA_TK * 8;
+    p.a_bytes = TMA_TM * TMA_TK * 8; p.b_bytes = (uint32_t)(TN * TMA_TK * 8);
     p.ksplit = 1;
     p.out = C;
     T2Params t;
     memset(&t, 0, sizeof(t));
-    return launch_tma<2, 4>(c, "gemm_tma_kernel<mapped>", mA, mB, p, t);
+    return narrow ? launch_tma<2, 2>(c, "gemm_tma_kernel<mapped,narrow>", mA, mB, p, t)
+                  : launch_tma<2, 4>(c, "gemm_tma_kernel<mapped>", mA, mB, p, t);
   }
   Operand A = flat_operand(A_dev, M, K, 1);
   Operand B = flat_operand(B_dev, N, K, 1);

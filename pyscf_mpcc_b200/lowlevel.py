@@ -229,6 +229,8 @@ class MPCC_LL:
         self._ctx.call("mpccb_set_option", b"tma", int(bool(use_tma)))
         if os.environ.get("MPCC_YVO_FLAT"):                     # A/B switch: 1 / -1 force the flat-K Yvo form on / off
             self._ctx.call("mpccb_set_option", b"yvo_flat", int(os.environ["MPCC_YVO_FLAT"]))
+        if os.environ.get("MPCC_MAPPED_NARROW_K"):              # A/B switch: K up to which mapped GEMMs use 128 x 64 tiles
+            self._ctx.call("mpccb_set_option", b"mapped_narrow_k", int(os.environ["MPCC_MAPPED_NARROW_K"]))
         if os.environ.get("MPCC_XVO_GENERIC", "0") != "0":      # A/B switch: Xvo GEMM (:119) on the generic kernel
             self._ctx.call("mpccb_set_option", b"xvo_generic", 1)
         if self._diis_columns:
