@@ -114,12 +114,33 @@ def _rows(t, lo, hi):
     return DTensor(t.buf[lo * inner:hi * inner], (hi - lo,) + t.shape[1:])
 
 
-def _ladder_slabs(v, na_max, rank, world):
-    """Slabs [a0, a1) of the first virtual index for this rank. One rank: pieces of na_max. Several ranks: 2*world (or a
-    multiple) equal pieces, piece s and piece n-1-s to the same rank — the work of a slab is proportional to v - a0
-    (only the blocks b >= a0 are formed), so the two halves of a folded pair add up to the same for every rank."""
+def _ladder_slabs(v, na_max, rank, world, o2=0, halve=True):
+    """Slabs [a0, a1) of the first virtual index for this rank. One rank: pieces of at most na_max, sized so that the
+    product against tau — (v - a0) * na rows, o2 columns, the larger of the slab's two GEMMs — fills whole waves of
+    128 x 128 tiles on 148 SMs (equal pieces of v/6 left 12 waves where 9.1 were needed at (32,192,576)). Several
+    ranks: 2*world (or a multiple) equal pieces, piece s and piece n-1-s to the same rank — the work of a slab is
+    proportional to v - a0 (only the blocks b >= a0 are formed), so the two halves of a folded pair add up to the same
+    for every rank."""
     if world == 1:
-        return [(a0, min(v, a0 + na_max)) for a0 in range(0, v, na_max)]
+        if not o2:
+            return [(a0, min(v, a0 + na_max)) for a0 in range(0, v, na_max)]
+        ncol = -(-o2 // 128)
+        out, a0 = [], 0
+        while a0 < v:
+            nb = (v - a0) if halve else v
+            best = None
+            for na in range(max(1, na_max // 2), min(na_max, v - a0) + 1):
+                if v - (a0 + na) < max(1, na_max // 2) and a0 + na != v:
+                    continue                      # would leave a sliver for the last slab
+                tiles = -(-(na * nb) // 128) * ncol
+                eff = round(tiles / (-(-tiles // 148) * 148.0), 6)
+                key = (eff, na if tiles <= 148 else -na)      # ties: fewer launches below one wave, fewer flops above
+                if best is None or key > best[0]:
+                    best = (key, na)
+            na = best[1] if best else min(na_max, v - a0)
+            out.append((a0, a0 + na))
+            a0 += na
+        return out
     n = 2 * world
     while -(-v // n) > na_max:
         n += 2 * world
@@ -169,14 +190,14 @@ def _pp_ladder(eng, eris, t1, tau, t2new, slab_bytes=4 << 30, group=None, ring=N
     # the blocks b >= a0 are formed (the triangle pyscf's _add_vvvv keeps, ccsd.py / dfccsd.py:54-117); the square
     # diagonal slab block holds both members of a pair and enters with weight 1/2, and the final
     # t2new += R^T(2,3,0,1) + R^T(3,2,1,0) restores everything. About (1 + 1/nslabs)/2 of the ladder flops.
-    na = max(1, min(v, int(slab_bytes // (8 * v * v * v)), -(-v // 6)))
+    na = max(1, min(v, int(slab_bytes // (8 * v * v * v)), -(-v // 4)))
     # several ranks (north_star: "the ladder ... shards naturally over ab"): every rank fills its blocks of R, one
     # all-reduce (sum with zeros) completes it.
     # halve=False (tau not pair-symmetric): every block b of a slab is formed and R enters once, untransposed; the ring
     # terms, whose symmetrisation is part of the equations, then get an accumulator of their own.
     rank, world = (0, 1) if group is None else be.rank_and_size(group)
     BIG = 1 << 30
-    for a0, a1 in _ladder_slabs(v, na, rank, world):
+    for a0, a1 in _ladder_slabs(v, na, rank, world, o2=o2, halve=halve):
         if not halve:
             n_a = a1 - a0
             W = be.empty(v * n_a * v * v)
