@@ -669,7 +669,10 @@ class MPCC_LL:
         from . import rmpccsd
         from .tensor_engine import DTensor
         if self.world_size > 1:
-            raise NotImplementedError("the CCSD-type stage runs on one rank")
+            raise NotImplementedError(
+                "the CCSD-type stage keeps its integrals replicated: build this solver on a one-rank group "
+                "(group=torch.distributed.new_group([rank])) and pass the sharding group to rmpccsd.RMPCCSD(group=...) "
+                "/ cc.group, which shards the particle-particle ladder and the ring terms (tools/cc_mgpu_check.py)")
         o, v, L = self.nocc, self.nvir, self.naux
         if fock is None:
             fock = getattr(self, "_fock_mo", None)
