@@ -228,6 +228,14 @@ int mpccb_class_overwrite(mpccb_ctx* ctx, double* tnew_dev, const double* told_d
                           const int* act_h_dev, const int* act_p_dev, unsigned class_mask);
 /* out_dev[0] = x . y (deterministic two-pass reduction) */
 int mpccb_dot(mpccb_ctx* ctx, const double* x_dev, const double* y_dev, long long n, double* out_dev);
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (CUDA graph capture, tight serving loops, harnesses that forbid it). mpccb_dot with its per-block partial sums in a
+ * file-scope device array of the library (1024 doubles = 8 KB on every GPU that loads it, held until exit) instead of
+ * the caller-allocated workspace: allocates nothing, needs no bound workspace, same kernels and block count as
+ * mpccb_dot (identical bits). Maximum n = 2^32 elements; larger n is rejected with an error. All calls on a device
+ * share the array (it keeps the last call's partials; nothing in it needs clearing): calls that overlap on the GPU
+ * race — serialise them. */
+int mpccb_dot_static(mpccb_ctx* ctx, const double* x_dev, const double* y_dev, long long n, double* out_dev);
 /* test hook: q[i] = x[i] / y[i] with the branch-free quotient of the fused t2 epilogue (replaces the IEEE division of
  * dfrmpcc_lowlevel.py:137; within 1 ulp for normal denominators — tests/test_gpu_parity.py sweeps it) */
 int mpccb_test_fast_div(mpccb_ctx* ctx, const double* x_dev, const double* y_dev, double* q_dev, long long n);

@@ -77,6 +77,7 @@ SIGNATURES = {
                                   c_double_p]),
     "mpccb_class_overwrite": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, ctypes.c_uint]),
     "mpccb_dot": (c_int, [c_void_p, c_void_p, c_void_p, c_ll, c_void_p]),
+    "mpccb_dot_static": (c_int, [c_void_p, c_void_p, c_void_p, c_ll, c_void_p]),
     "mpccb_test_fast_div": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_ll]),
     "mpccb_gemv": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_ll, c_ll, c_int, ctypes.c_double, ctypes.c_double]),
     "mpccb_gemm_nt_mapped": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_ll, c_ll,

@@ -1896,3 +1896,55 @@ extern "C" int mpccb_dot(mpccb_ctx* c, const double* x_dev, const double* y_dev,
   LAUNCH_OK(c, "k_final_sums");
   return 0;
 }
+
+// ---------------------------------------------------------------------------
+// mpccb_dot without any allocation (no counterpart in the reference; added for
+// callers that cannot call cudaMalloc: CUDA graph capture, tight serving loops, harnesses that forbid it).
+// Same two kernels and the same block count as mpccb_dot — hence the same bits — but the per-block partial sums go to a
+// file-scope device array instead of the caller-allocated workspace, so no workspace needs to be bound.
+//   * MPCCB_DOT_STATIC_PARTIALS doubles (8 KB) per GPU that loads this library, held until the process exits.
+//   * `g_dot_static` is a HOST-SIDE STAND-IN in host code, not a device address: its device address is looked up once
+//     per device, with that device current, by cudaGetSymbolAddress (dot_static_address) and that pointer is passed
+//     to the kernels.
+//   * Every call on a device shares the array. Nothing in it has to start at zero (each of the nb partials is written
+//     before the second kernel reads it), so it is not cleared; it keeps the last call's partials. Calls that overlap
+//     on the GPU (two streams, two contexts on one device) race on it: serialise them.
+// ---------------------------------------------------------------------------
+namespace {
+constexpr int MPCCB_DOT_STATIC_PARTIALS = 1024;                   // mpccb_dot uses at most 592 blocks
+constexpr long long MPCCB_DOT_STATIC_MAX_N = 1LL << 32;           // stated maximum length (34 GB per vector)
+constexpr int MPCCB_MAX_DEVICES = 64;
+static __device__ __align__(256) double g_dot_static[MPCCB_DOT_STATIC_PARTIALS];
+double* g_dot_static_addr[MPCCB_MAX_DEVICES] = {};                // device address of g_dot_static, per device
+
+// caller has made `device` current
+int dot_static_address(mpccb_ctx* c, int device, double** out) {
+  if (device < 0 || device >= MPCCB_MAX_DEVICES) return fail(c, "device %d outside the supported 0..%d", device, MPCCB_MAX_DEVICES - 1);
+  if (!g_dot_static_addr[device]) {
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_dot_static);
+    if (e != cudaSuccess || !p) return fail(c, "cudaGetSymbolAddress(g_dot_static) failed: %s", cudaGetErrorString(e));
+    g_dot_static_addr[device] = static_cast<double*>(p);
+  }
+  *out = g_dot_static_addr[device];
+  return 0;
+}
+}  // namespace
+
+extern "C" int mpccb_dot_static(mpccb_ctx* c, const double* x_dev, const double* y_dev, long long n, double* out_dev) {
+  CUDA_OK(c, enter_device(c));
+  if (!x_dev || !y_dev || !out_dev) return fail(c, "mpccb_dot_static: null pointer");
+  if (n <= 0) return fail(c, "mpccb_dot_static: n = %lld must be positive", n);
+  if (n > MPCCB_DOT_STATIC_MAX_N)
+    return fail(c, "mpccb_dot_static: n = %lld exceeds the maximum of %lld elements of the allocation-free form "
+                   "(use mpccb_dot with a bound workspace)", n, MPCCB_DOT_STATIC_MAX_N);
+  const int nb = (int)std::min<i64>(std::max<i64>(cdiv(n, 1024), 1), 592);      // the rule of mpccb_dot
+  static_assert(592 <= MPCCB_DOT_STATIC_PARTIALS, "static scratch smaller than the block count");
+  double* partial = nullptr;
+  if (dot_static_address(c, c->device, &partial)) return 1;
+  k_dot_partial<<<nb, 256, 0, c->stream>>>(x_dev, y_dev, partial, n);
+  LAUNCH_OK(c, "k_dot_partial(static)");
+  k_final_sums<<<1, 256, 0, c->stream>>>(partial, out_dev, nb, 1);
+  LAUNCH_OK(c, "k_final_sums(static)");
+  return 0;
+}
