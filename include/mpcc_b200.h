@@ -226,6 +226,14 @@ int mpccb_div_general(mpccb_ctx* ctx, double* t_dev, int rank, const int* dims, 
  * doubles; act_h_dev / act_p_dev are 0/1 int flags per occupied / virtual orbital */
 int mpccb_class_overwrite(mpccb_ctx* ctx, double* tnew_dev, const double* told_dev, int rank,
                           const int* act_h_dev, const int* act_p_dev, unsigned class_mask);
+/* lib.take_2d / lib.takebak_2d (pyscf/lib/numpy_helper.py:478-541; NPdtake_2d / NPdtakebak_2d of libnp_helper) on
+ * device buffers: out[r*ny + c] = a[idx[r]*lda + idy[c]]  and  out[idx[r]*ldo + idy[c]] += alpha * a[r*ny + c]
+ * (idx / idy: int32 device arrays without duplicates). They carry ccsd.amplitudes_to_vector_s4 / _unpack_4fold
+ * (pyscf/cc/ccsd.py:705-757) for the run_diis of the unrestricted prototype (pyscf/cc/umpcc_lowlevel.py:15-46,92-98) */
+int mpccb_take_2d(mpccb_ctx* ctx, const double* a_dev, long long lda, const int* idx_dev, int nx,
+                  const int* idy_dev, int ny, double* out_dev);
+int mpccb_takebak_2d(mpccb_ctx* ctx, double* out_dev, long long ldo, const double* a_dev, const int* idx_dev, int nx,
+                     const int* idy_dev, int ny, double alpha);
 /* out_dev[0] = x . y (deterministic two-pass reduction) */
 int mpccb_dot(mpccb_ctx* ctx, const double* x_dev, const double* y_dev, long long n, double* out_dev);
 /* No counterpart in the reference: added for callers that cannot call cudaMalloc

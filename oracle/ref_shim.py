@@ -233,6 +233,11 @@ def load_reference():
             dfn = mod("pyscf.mp.dfump2_native"); mp.dfump2_native = dfn
             dfn.DFMP2 = type("DFMP2", (), {})
             pyscf.scf = mod("pyscf.scf")                      # `from pyscf import scf, cc` at module level (:631)
+            # ccsd.py cannot be imported (libcc): the two vector helpers the prototype's run_diis calls are the
+            # restatements of oracle/cc_oracle.py (pinned to the text of ccsd.py:705-757 in test_oracle_vs_reference.py)
+            from . import cc_oracle
+            ccsd.amplitudes_to_vector_s4 = cc_oracle.amplitudes_to_vector_s4
+            ccsd.vector_to_amplitudes_s4 = cc_oracle.vector_to_amplitudes_s4
             _loaded_u = run("pyscf.cc.umpcc_lowlevel", "cc/umpcc_lowlevel.py")
         except Exception as exc:
             _loaded_u = exc

@@ -76,6 +76,8 @@ SIGNATURES = {
     "mpccb_div_general": (c_int, [c_void_p, c_void_p, c_int, ctypes.POINTER(c_int), ctypes.POINTER(c_void_p),
                                   c_double_p]),
     "mpccb_class_overwrite": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, ctypes.c_uint]),
+    "mpccb_take_2d": (c_int, [c_void_p, c_void_p, c_ll, c_void_p, c_int, c_void_p, c_int, c_void_p]),
+    "mpccb_takebak_2d": (c_int, [c_void_p, c_void_p, c_ll, c_void_p, c_void_p, c_int, c_void_p, c_int, ctypes.c_double]),
     "mpccb_dot": (c_int, [c_void_p, c_void_p, c_void_p, c_ll, c_void_p]),
     "mpccb_dot_static": (c_int, [c_void_p, c_void_p, c_void_p, c_ll, c_void_p]),
     "mpccb_test_fast_div": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_ll]),

@@ -175,3 +175,33 @@ k_div_general(double* __restrict__ t, DenomDesc d) {
   }
 }
 }  // namespace mpccb
+
+namespace mpccb {
+// out[r*ny + c] = a[idx[r]*lda + idy[c]]            (lib.take_2d, pyscf/lib/numpy_helper.py:478-504: a[idx[:,None], idy])
+// lanes along c: the reads are a gather within one row of `a`, the writes contiguous
+__global__ void __launch_bounds__(256)
+k_take_2d(const double* __restrict__ a, i64 lda, const int* __restrict__ idx, int nx, const int* __restrict__ idy,
+          int ny, double* __restrict__ out) {
+  const i64 total = (i64)nx * ny;
+  const i64 stride = (i64)gridDim.x * blockDim.x;
+  for (i64 t = (i64)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += stride) {
+    const int r = (int)(t / ny), c = (int)(t - (i64)r * ny);
+    out[t] = a[(i64)idx[r] * lda + idy[c]];
+  }
+}
+
+// out[idx[r]*ldo + idy[c]] += alpha * a[r*ny + c]   (lib.takebak_2d, numpy_helper.py:506-541; alpha = -1 is the
+// "t2tril = -t2tril" of ccsd._unpack_4fold, ccsd.py:713-716). The index sets must hold no duplicates (they are
+// triangle enumerations): every target element is touched by one thread.
+__global__ void __launch_bounds__(256)
+k_takebak_2d(double* __restrict__ out, i64 ldo, const double* __restrict__ a, const int* __restrict__ idx, int nx,
+             const int* __restrict__ idy, int ny, double alpha) {
+  const i64 total = (i64)nx * ny;
+  const i64 stride = (i64)gridDim.x * blockDim.x;
+  for (i64 t = (i64)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += stride) {
+    const int r = (int)(t / ny), c = (int)(t - (i64)r * ny);
+    const i64 off = (i64)idx[r] * ldo + idy[c];
+    out[off] = fma(alpha, a[t], out[off]);
+  }
+}
+}  // namespace mpccb

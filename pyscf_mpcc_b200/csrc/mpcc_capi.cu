@@ -1885,6 +1885,31 @@ extern "C" int mpccb_test_fast_div(mpccb_ctx* c, const double* x_dev, const doub
   return 0;
 }
 
+// lib.take_2d / lib.takebak_2d on device buffers (pyscf/lib/numpy_helper.py:478-541): the gather / scatter-add behind
+// ccsd.amplitudes_to_vector_s4 / _unpack_4fold (pyscf/cc/ccsd.py:705-757), which the unrestricted prototype's run_diis
+// uses (pyscf/cc/umpcc_lowlevel.py:15-46). idx / idy: int32 device arrays of row / column numbers.
+extern "C" int mpccb_take_2d(mpccb_ctx* c, const double* a_dev, long long lda, const int* idx_dev, int nx,
+                             const int* idy_dev, int ny, double* out_dev) {
+  CUDA_OK(c, enter_device(c));
+  if (nx < 0 || ny < 0 || lda < 0) return fail(c, "take_2d: negative size");
+  if (nx == 0 || ny == 0) return 0;
+  const int nb = (int)std::min<i64>(cdiv((i64)nx * ny, 256), NSM * 8);
+  k_take_2d<<<nb, 256, 0, c->stream>>>(a_dev, lda, idx_dev, nx, idy_dev, ny, out_dev);
+  LAUNCH_OK(c, "k_take_2d");
+  return 0;
+}
+
+extern "C" int mpccb_takebak_2d(mpccb_ctx* c, double* out_dev, long long ldo, const double* a_dev, const int* idx_dev,
+                                int nx, const int* idy_dev, int ny, double alpha) {
+  CUDA_OK(c, enter_device(c));
+  if (nx < 0 || ny < 0 || ldo < 0) return fail(c, "takebak_2d: negative size");
+  if (nx == 0 || ny == 0) return 0;
+  const int nb = (int)std::min<i64>(cdiv((i64)nx * ny, 256), NSM * 8);
+  k_takebak_2d<<<nb, 256, 0, c->stream>>>(out_dev, ldo, a_dev, idx_dev, nx, idy_dev, ny, alpha);
+  LAUNCH_OK(c, "k_takebak_2d");
+  return 0;
+}
+
 // out_dev[0] = sum_i x[i] y[i]  (deterministic two-pass reduction; needs the bound workspace)
 extern "C" int mpccb_dot(mpccb_ctx* c, const double* x_dev, const double* y_dev, long long n, double* out_dev) {
   CUDA_OK(c, enter_device(c));

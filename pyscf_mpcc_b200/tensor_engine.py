@@ -111,6 +111,16 @@ class CudaBackend:
         self.ctx.call("mpccb_dot", x.data_ptr(), y.data_ptr(), int(n), out.data_ptr())
         return float(self.download(out)[0])
 
+    def take_2d(self, a, lda, idx, idy, out):
+        """out[r, c] = a[idx[r], idy[c]] (lib.take_2d); idx / idy are int32 device arrays."""
+        self.ctx.call("mpccb_take_2d", a.data_ptr(), int(lda), idx.data_ptr(), int(idx.numel()), idy.data_ptr(),
+                      int(idy.numel()), out.data_ptr())
+
+    def takebak_2d(self, out, ldo, a, idx, idy, alpha=1.0):
+        """out[idx[r], idy[c]] += alpha * a[r, c] (lib.takebak_2d)."""
+        self.ctx.call("mpccb_takebak_2d", out.data_ptr(), int(ldo), a.data_ptr(), idx.data_ptr(), int(idx.numel()),
+                      idy.data_ptr(), int(idy.numel()), float(alpha))
+
     # -- vector layouts and DIIS of the CCSD-type stage (ccsd.py:719-735, 1269-1276) ------------------
     def pack_tril(self, mat, n, out):
         self.ctx.call("mpccb_pack_tril", mat.data_ptr(), int(n), out.data_ptr())

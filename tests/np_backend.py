@@ -81,6 +81,14 @@ class NumpyBackend:
     def dot(self, x, y, n):
         return float(np.dot(x[:n], y[:n]))
 
+    def take_2d(self, a, lda, idx, idy, out):
+        out[:len(idx) * len(idy)] = a[(idx.astype(np.int64)[:, None] * lda + idy.astype(np.int64)[None, :]).reshape(-1)]
+
+    def takebak_2d(self, out, ldo, a, idx, idy, alpha=1.0):
+        pos = (idx.astype(np.int64)[:, None] * ldo + idy.astype(np.int64)[None, :]).reshape(-1)
+        assert len(np.unique(pos)) == len(pos)          # the kernel's contract: no duplicate targets
+        out[pos] += alpha * a[:len(pos)]
+
     def pack_tril(self, mat, n, out):
         r, c = np.tril_indices(n)
         out[:r.size] = mat[:n * n].reshape(n, n)[r, c]
