@@ -655,6 +655,31 @@ class MPCC_LL:
         finally:
             self.t1 = keep
 
+    # ------------------------------------------------------------------ PySCF's to_gpu convention
+    @classmethod
+    def from_cpu(cls, other, **kwargs):
+        """GPU solver from an already constructed CPU ``MPCC_LL`` of the reference (or anything with its
+        attributes ``Loo, Lov, Lvv, foo, fvv, mo_energy``, ``dfrmpcc_lowlevel.py:29-43,66-69``): the MO-basis
+        blocks are uploaded as they are — no second AO->MO transform — and the outside pokes (``con_tol``,
+        ``max_its``, ``diis``), the mean field and the current ``t1`` are carried over. This is what
+        ``obj.to_gpu()`` means elsewhere in PySCF (``lib.to_gpu``, ``pyscf/lib/misc.py:1508-1556``); the MPCC
+        classes of the reference do not define it, so a maintainer adds
+        ``MPCC_LL.to_gpu = lambda self: pyscf_mpcc_b200.lowlevel.to_gpu(self)``."""
+        blocks = tuple(np.ascontiguousarray(getattr(other, k), dtype=np.float64)
+                       for k in ("Loo", "Lov", "Lvv", "foo", "fvv", "mo_energy"))
+        new = cls(blocks=blocks, **kwargs)
+        new.mf = getattr(other, "mf", None)
+        new.with_df = getattr(other, "with_df", None)
+        if getattr(other, "mo_coeff", None) is not None:
+            new.mo_coeff = np.asarray(other.mo_coeff, dtype=np.float64)
+        for k in ("con_tol", "max_its", "diis"):
+            if hasattr(other, k):
+                setattr(new, k, getattr(other, k))
+        t1 = getattr(other, "t1", None)
+        if t1 is not None:
+            new.t1 = np.array(t1, dtype=np.float64).reshape(new.nocc, new.nvir)
+        return new
+
     # ------------------------------------------------------------------ high-level stage (rows f1/f2)
     def tensor_engine(self):
         """Device contraction engine bound to this solver's native context (stream, workspace, orbital energies)."""
@@ -780,3 +805,9 @@ class MPCC_LL:
         self.iterations = count
         self._adiis = adiis
         return DE
+
+
+def to_gpu(cpu_lowlevel, **kwargs):
+    """``lib.to_gpu``-style conversion (``pyscf/lib/misc.py:1508-1556``) of a constructed reference
+    ``dfrmpcc_lowlevel.MPCC_LL``: see :meth:`MPCC_LL.from_cpu`."""
+    return MPCC_LL.from_cpu(cpu_lowlevel, **kwargs)

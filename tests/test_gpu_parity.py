@@ -393,6 +393,36 @@ def test_the_references_solver_object_drives_this_module(capsys):
     assert abs(obj_ref.lowlevel.t1 - ll.t1).max() <= AMP_TOL
 
 
+def test_to_gpu_of_a_constructed_reference_object():
+    """``lowlevel.to_gpu(ref_ll)`` / ``MPCC_LL.from_cpu`` (PySCF's ``obj.to_gpu()`` convention,
+    pyscf/lib/misc.py:1508-1556): the reference's own CPU object, constructed by its unmodified file, hands its MO
+    blocks and outside pokes to the GPU solver, which then reproduces the reference's ``kernel()``."""
+    from oracle import ref_shim
+    if not ref_shim.reference_available():
+        pytest.skip("no reference files (neither /root/reference nor oracle/_ref)")
+    import pyscf_mpcc_b200.lowlevel as b200_lowlevel
+    from pyscf_mpcc_b200.synthetic import SyntheticMF
+    ref_ll, _ = ref_shim.load_reference()
+    g, o, v, L, scale = _load([p for p in golden_cases() if "5_19_116" in p][0])
+    mf = SyntheticMF(o, v, L, seed=0, scale=scale)
+    cpu = ref_ll.MPCC_LL(mf)
+    cpu.con_tol, cpu.max_its = 1e-6, 50
+    gpu = b200_lowlevel.to_gpu(cpu)
+    assert isinstance(gpu, b200_lowlevel.MPCC_LL) and gpu.mf is mf and gpu.with_df is mf.with_df
+    assert (gpu.nocc, gpu.nvir, gpu.naux) == (o, v, L) and gpu.con_tol == 1e-6 and gpu.max_its == 50
+    gpu.verbose_print = False
+    dE = gpu.kernel()
+    assert gpu.iterations == int(g["iterations"])
+    assert abs(dE - g["trace_dE"][-1]) <= E_TOL
+    assert np.abs(gpu.t1 - g["final_t1"]).max() <= AMP_TOL
+    # a t1 already present on the CPU object is carried over: one more residual evaluation from the converged t1
+    cpu.t1 = gpu.t1.copy()
+    again = b200_lowlevel.MPCC_LL.from_cpu(cpu)
+    res, dE2, _, _ = again.updated_amps()
+    res_ref, dE_ref, _, _ = cpu.updated_amps()
+    assert abs(dE2 - dE_ref) <= E_TOL and abs(res - res_ref) <= 1e-10
+
+
 @pytest.mark.parametrize("layout", ["rows", "columns"])
 def test_host_vector_round_trip(layout):
     """vector_to_amplitudes(amplitudes_to_vector(t1, t2).numpy()): a HOST vector is the reference-order flat vector,
