@@ -89,8 +89,7 @@ __device__ __forceinline__ i64 k_offset(const Operand& op, int k, int kend) {
 
 // tile id -> (tm, tn): n-tiles grouped 8 wide so that the CTAs resident at one
 // time share operand tiles through L2.
-__device__ __forceinline__ void tile_coords(int id, int tiles_m, int tiles_n, int& tm, int& tn) {
-  const int gw = 8;
+__device__ __forceinline__ void tile_coords(int id, int tiles_m, int tiles_n, int& tm, int& tn, int gw = 8) {
   const int per_group = gw * tiles_m;
   const int group = id / per_group;
   const int first = group * gw;

@@ -153,6 +153,7 @@ struct TmaGemmParams {
   // stores to C + s*split_stride (partials reduced afterwards in fixed order). ksplit == 1: none.
   int ksplit, nk_split, tiles_total;
   i64 split_stride;
+  int gw;                // raster: column tiles per group of tile_coords (0 = its default of 8)
   // EPI 2: store through a two-level index map with an optional block mask (gemm_dmma.cuh, Output): the unfused
   // eris GEMM scatters e[(a,i),(b,j)] into T[a][b][i][j] and skips the blocks that arrive as somebody's mirror;
   // the tensor engine's contractions store straight into the permuted result (out.alpha / out.beta: axpby)
@@ -182,7 +183,7 @@ gemm_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
     const int2 t = sym.tiles[blockIdx.x];
     tm = t.x; tn = t.y;
   } else {
-    tile_coords(blockIdx.x - split * ntiles, p.tiles_m, p.tiles_n, tm, tn);
+    tile_coords(blockIdx.x - split * ntiles, p.tiles_m, p.tiles_n, tm, tn, p.gw > 0 ? p.gw : 8);
   }
   const int m0 = tm * p.tm_eff, n0 = tn * p.tn_eff;
   if (EPI == 2 && p.out.keep) {           // no kept block in this tile: nothing to compute (uniform over the CTA)

@@ -231,6 +231,9 @@ class MPCC_LL:
             self._ctx.call("mpccb_set_option", b"yvo_flat", int(os.environ["MPCC_YVO_FLAT"]))
         if os.environ.get("MPCC_MAPPED_NARROW_K"):              # A/B switch: K up to which mapped GEMMs use 128 x 64 tiles
             self._ctx.call("mpccb_set_option", b"mapped_narrow_k", int(os.environ["MPCC_MAPPED_NARROW_K"]))
+        for key in ("raster_yvo", "raster_eris"):               # A/B switch: column tiles per raster group (0 = default)
+            if os.environ.get("MPCC_" + key.upper()):
+                self._ctx.call("mpccb_set_option", key.encode(), int(os.environ["MPCC_" + key.upper()]))
         if os.environ.get("MPCC_XVO_GENERIC", "0") != "0":      # A/B switch: Xvo GEMM (:119) on the generic kernel
             self._ctx.call("mpccb_set_option", b"xvo_generic", 1)
         if self._diis_columns:
